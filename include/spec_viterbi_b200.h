@@ -1,0 +1,182 @@
+/* spec_viterbi_b200 -- C ABI of the B200-native (min,+) Viterbi backend.
+ *
+ * This is the drop-in boundary: a third GPU backend for IvanTyulyandin/Spec_Viterbi that
+ * replaces the CUSP and cuASR backends behind the reference's `Viterbi_impl` /
+ * `Viterbi_spec_impl` interface.  Every entry point is `extern "C"`, takes plain pointers
+ * and sizes, returns an int status (0 = SV_OK) and never throws.  The thin C++ adaptors
+ * `B200_impl` / `B200_spec_impl` (spec_viterbi_b200/host/) and the Python mirror
+ * (spec_viterbi_b200/api.py, ctypes) sit directly on these functions.
+ *
+ * Reference interfaces replaced (file:line under the reference tree):
+ *   sv_model_create      <- the per-call model build/upload of every backend
+ *                           (GraphBLAS_impl.cpp:24-45, CUSP_helper.cu:32-72 init_matrices_from_HMM,
+ *                            cuASR_helper.cu:167-225); HMM layout = Viterbi_impl/HMM.h:28-38
+ *   sv_viterbi           <- Viterbi_impl::run_Viterbi (Viterbi_impl.h:8-9; GraphBLAS_impl.cpp:4-93,
+ *                           CUSP_impl.cu:5-23, cuASR_impl.cu:6-24)
+ *   sv_viterbi_batch     <- the harness loop "one run_Viterbi call per sequence"
+ *                           (benchmark/bench_Viterbi.h:51-57), batched
+ *   sv_spec_create       <- Viterbi_spec_impl::spec_with (Viterbi_spec_impl.h:11;
+ *                           GraphBLAS_spec_impl.cpp:45-48,103-182, add_level :15-36;
+ *                           CUSP_spec_impl.cu:81-96, cuASR_spec_impl.cu:81-107)
+ *   sv_spec_run[_batch]  <- Viterbi_spec_impl::run_Viterbi_spec (Viterbi_spec_impl.h:13-14;
+ *                           GraphBLAS_spec_impl.cpp:50-97) and bench_Viterbi_spec.h:74-80
+ *   sv_io_*              <- read_HMM / read_emit_seq (Viterbi_impl/data_reader.h:8,11)
+ *
+ * Numerics contract: scores are fp32 -log2 probabilities, +inf = impossible.
+ * Plain path and every spec level are bit-exact against the same-level GraphBLAS
+ * formulation:  v'[i] = min_j fl(fl(E[o][i] + T'[i][j]) + v[j]).
+ *
+ * There is no CPU fallback: without a CUDA device every compute call fails with
+ * SV_ERR_CUDA and a message in sv_last_error().
+ */
+#ifndef SPEC_VITERBI_B200_H
+#define SPEC_VITERBI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    SV_OK = 0,
+    SV_ERR_ARG = 1,     /* bad argument (null pointer, empty sequence, symbol >= E, ...) */
+    SV_ERR_CUDA = 2,    /* CUDA runtime error, or no device */
+    SV_ERR_MEMORY = 3,  /* host or device allocation failed / table does not fit */
+    SV_ERR_IO = 4,      /* file could not be read / parsed */
+    SV_ERR_UNSUPPORTED = 5
+};
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* sv_last_error(void);
+/* Library version string, e.g. "spec_viterbi_b200 0.1 (sm_100a)". */
+const char* sv_version(void);
+/* Number of visible CUDA devices (0 on a CPU-only host; never fails). */
+int sv_device_count(void);
+
+/* ------------------------------------------------------------------ model ---- */
+typedef struct sv_model sv_model;
+
+/* Kernel selection for the plain / level-1 step (sv_model_set_kernel). */
+enum {
+    SV_KERNEL_AUTO = 0,
+    SV_KERNEL_GENERIC = 1, /* CSR in L1/L2, any model size */
+    SV_KERNEL_ES = 2       /* edge-stationary: transitions in registers, E and v in smem */
+};
+
+/* Builds the device-resident model (K0 repack) from the reference's HMM layout:
+ * COO transitions (src = HMM::trans_rows, dst = HMM::trans_cols, w = -log2 p),
+ * emissions [emits][states], sparse start vector.  Duplicate COO / start entries keep
+ * the FIRST occurrence (GrB_FIRST_FP32).  `device` is a CUDA ordinal. */
+int sv_model_create(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                    const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                    uint64_t nstart, const uint64_t* start_cols, const float* start_w, int device,
+                    sv_model** out);
+void sv_model_destroy(sv_model* m);
+int sv_model_set_kernel(sv_model* m, int kernel);
+
+typedef struct sv_model_info {
+    uint64_t states, emits, nnz;   /* nnz after duplicate removal */
+    uint64_t max_in_degree;
+    int32_t device;
+    int32_t kernel;                /* SV_KERNEL_* that sv_viterbi* will launch */
+    /* edge-stationary schedule (zeros when the model does not fit that kernel) */
+    int32_t es_threads, es_seqs_per_cta, es_ranks, es_heavy_rows;
+    uint64_t es_slots_per_thread;  /* register-resident edge slots per thread (padded) */
+    uint64_t es_gather_wavefronts; /* smem wavefronts of the v gather per step (scheduled) */
+    uint64_t es_gather_ideal;      /* same with zero bank conflicts */
+    uint64_t es_smem_bytes;
+    uint64_t es_split_states;      /* virtual states added by in-degree capping */
+} sv_model_info;
+int sv_model_get_info(const sv_model* m, sv_model_info* info);
+
+/* ------------------------------------------------ observation sequences ---- */
+/* A device-resident batch of sequences: symbols validated (< emits), packed to u8/u16,
+ * ordered longest-first for the persistent scheduler. */
+typedef struct sv_seqs sv_seqs;
+int sv_seqs_create(const sv_model* m, const uint64_t* symbols, const uint64_t* offsets,
+                   uint64_t nseq, sv_seqs** out);
+/* Same, from symbols already packed one byte each (alphabet <= 256). */
+int sv_seqs_create_u8(const sv_model* m, const uint8_t* symbols, const uint64_t* offsets,
+                      uint64_t nseq, sv_seqs** out);
+void sv_seqs_destroy(sv_seqs* s);
+uint64_t sv_seqs_count(const sv_seqs* s);
+uint64_t sv_seqs_total_symbols(const sv_seqs* s);
+
+/* ------------------------------------------------------------ plain path ---- */
+/* One sequence, host buffers: out[states].  Equivalent of run_Viterbi(hmm, seq). */
+int sv_viterbi(sv_model* m, const uint64_t* seq, uint64_t len, float* out);
+
+/* Many sequences, host buffers.  symbols = concatenated sequences, offsets[nseq+1].
+ * Any of out ([nseq][states]), best ([nseq], min final score) and best_state ([nseq],
+ * lowest state index attaining it, -1 if all +inf) may be NULL. */
+int sv_viterbi_batch(sv_model* m, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
+                     float* out, float* best, int32_t* best_state);
+
+/* Device-resident variant: `seqs` from sv_seqs_create, d_* are device pointers on the
+ * model's device (may be NULL), `stream` is a cudaStream_t (NULL = default stream).
+ * Asynchronous with respect to the host. */
+int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out, float* d_best,
+                      int32_t* d_best_state, void* stream);
+/* Kernel launches issued by the last sv_viterbi*_ / sv_spec_run* call on this model. */
+int sv_model_last_launches(const sv_model* m);
+
+/* ------------------------------------------------------ specialised path ---- */
+typedef struct sv_spec sv_spec;
+
+enum {
+    SV_SPEC_AUTO = 0,
+    SV_SPEC_DENSE_GEMM = 1, /* K3: register-blocked dense (min,+) GEMM, 2*N^3 ops / handler */
+    SV_SPEC_SPARSE_LHS = 2  /* K3': sparse level-1 matrix times dense handler, 2*nnz*N ops */
+};
+
+/* spec_with(hmm): level-1 tables, and for level > 1 the dense handler of every symbol
+ * tuple in [tuple_begin, tuple_end) (pass 0, 0 for all emits^level tuples).  Tuple index =
+ * sum_j k_j * emits^(level-j), k_1 = first consumed symbol.  If d_table is not NULL it must
+ * be a device buffer of (tuple_end-tuple_begin)*states*states floats that the caller owns
+ * (used to all-gather shards across GPUs); otherwise the table is allocated internally. */
+int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t tuple_begin,
+                   uint64_t tuple_end, float* d_table, void* stream, sv_spec** out);
+void sv_spec_destroy(sv_spec* s);
+uint64_t sv_spec_level(const sv_spec* s);
+/* Declares that tuples [tuple_begin, tuple_end) of the table are now valid (after an
+ * external all-gather into the caller-owned d_table). */
+int sv_spec_set_range(sv_spec* s, uint64_t tuple_begin, uint64_t tuple_end);
+/* Device pointer of the handler table (tuple_begin first) and its tuple range. */
+float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_t* tuple_end);
+/* Copies one dense handler (states*states floats, row = destination state) to the host. */
+int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out);
+
+int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out);
+int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
+                      float* out, float* best, int32_t* best_state);
+int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out, float* d_best,
+                       int32_t* d_best_state, void* stream);
+
+/* ---------------------------------------------------- files (host only) ---- */
+/* .chmm text / .chmmb packed (by extension).  dims = {states, emits, trans, nstart}. */
+typedef struct sv_hmm_file sv_hmm_file;
+int sv_io_hmm_open(const char* path, sv_hmm_file** out, uint64_t dims[4]);
+int sv_io_hmm_copy(const sv_hmm_file* f, uint64_t* trans_src, uint64_t* trans_dst, float* trans_w,
+                   float* emissions, uint64_t* start_cols, float* start_w);
+int sv_io_hmm_write_packed(const sv_hmm_file* f, const char* path);
+void sv_io_hmm_close(sv_hmm_file* f);
+
+/* .ess text / .essb packed (by extension). */
+typedef struct sv_ess_file sv_ess_file;
+int sv_io_ess_open(const char* path, sv_ess_file** out, uint64_t* nseq, uint64_t* total_symbols);
+int sv_io_ess_copy(const sv_ess_file* f, uint64_t* offsets /*[nseq+1]*/, uint64_t* symbols);
+int sv_io_ess_write_packed(const sv_ess_file* f, const char* path);
+void sv_io_ess_close(sv_ess_file* f);
+
+/* ------------------------------------------------------- micro-benchmarks ---- */
+/* FP32 pipe probe used to fix the non-tensor roofline: runs `iters` dependent-chain
+ * iterations of the chosen instruction mix on every SM and returns lane-instructions/s.
+ * mix: 0 = FADD, 1 = FMNMX (2-input min), 2 = FMNMX3 (3-input min), 3 = 2 FADD + 1 FMNMX3,
+ *      4 = 4 FADD + 1 FMNMX3 (the step's inner loop), 5 = LDS.32 conflict-free + 2 FADD + FMNMX */
+int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_per_s, double* sm_clock_mhz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

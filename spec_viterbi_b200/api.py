@@ -1,0 +1,374 @@
+"""Python mirror of the reference's operator interface, on top of the C ABI.
+
+Names follow the reference (Viterbi_impl/HMM.h, Viterbi_impl.h, Viterbi_spec_impl.h,
+data_reader.h): `HMM`, `read_HMM`, `read_emit_seq`, `B200_impl.run_Viterbi(hmm, seq)`,
+`B200_spec_impl(level).spec_with(hmm)` / `.run_Viterbi_spec(seq)` / `.get_level()`.
+Batched and device-resident entry points are additions (the reference is one sequence per
+call).  All compute happens in libspecviterbi_b200.so; nothing here falls back to numpy.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Iterable, Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+
+zero_prob = np.float32(np.inf)
+
+
+def _p(arr: np.ndarray, ctype):
+    return arr.ctypes.data_as(C.POINTER(ctype))
+
+
+def to_modified_prob(p) -> np.ndarray:
+    """-log2(p) in fp32, +inf for p <= 0 (reference: HMM.h:51-57)."""
+    p = np.asarray(p, dtype=np.float32)
+    out = np.full(p.shape, np.inf, dtype=np.float32)
+    pos = p > 0
+    out[pos] = -np.log2(p[pos], dtype=np.float32)
+    return out
+
+
+def almost_equal(x, y) -> bool:
+    """The reference's cross-backend tolerance: both +inf or |x-y| <= 1.0 (HMM.h:43-49)."""
+    x = np.float32(x)
+    y = np.float32(y)
+    return bool((np.isposinf(x) and np.isposinf(y)) or abs(x - y) <= 1.0)
+
+
+@dataclass
+class HMM:
+    """Same fields as the reference's HMM struct (HMM.h:28-38), as numpy arrays."""
+    states_num: int = 0
+    emit_num: int = 0
+    trans_num: int = 0
+    trans_rows: np.ndarray = field(default_factory=lambda: np.zeros(0, np.uint64))
+    trans_cols: np.ndarray = field(default_factory=lambda: np.zeros(0, np.uint64))
+    trans_probs: np.ndarray = field(default_factory=lambda: np.zeros(0, np.float32))
+    emissions: np.ndarray = field(default_factory=lambda: np.zeros((0, 0), np.float32))  # [emit][state]
+    non_zero_start_probs: int = 0
+    start_probabilities_cols: np.ndarray = field(default_factory=lambda: np.zeros(0, np.uint64))
+    start_probabilities: np.ndarray = field(default_factory=lambda: np.zeros(0, np.float32))
+
+    def normalized(self) -> "HMM":
+        return HMM(
+            int(self.states_num), int(self.emit_num), int(self.trans_num),
+            np.ascontiguousarray(self.trans_rows, np.uint64),
+            np.ascontiguousarray(self.trans_cols, np.uint64),
+            np.ascontiguousarray(self.trans_probs, np.float32),
+            np.ascontiguousarray(self.emissions, np.float32).reshape(int(self.emit_num), int(self.states_num)),
+            int(self.non_zero_start_probs),
+            np.ascontiguousarray(self.start_probabilities_cols, np.uint64),
+            np.ascontiguousarray(self.start_probabilities, np.float32),
+        )
+
+
+def read_HMM(path: str) -> HMM:
+    """.chmm text or .chmmb packed -> HMM (-log2 weights).  Raises on failure (the reference
+    returns an empty HMM, data_reader.cpp:19-22)."""
+    lib = L.lib()
+    h = C.c_void_p()
+    dims = (C.c_uint64 * 4)()
+    L.check(lib.sv_io_hmm_open(str(path).encode(), C.byref(h), dims))
+    try:
+        n, e, t, s = (int(x) for x in dims)
+        hmm = HMM(n, e, t, np.zeros(t, np.uint64), np.zeros(t, np.uint64), np.zeros(t, np.float32),
+                  np.zeros((e, n), np.float32), s, np.zeros(s, np.uint64), np.zeros(s, np.float32))
+        L.check(lib.sv_io_hmm_copy(h, _p(hmm.trans_rows, C.c_uint64), _p(hmm.trans_cols, C.c_uint64),
+                                   _p(hmm.trans_probs, C.c_float), _p(hmm.emissions, C.c_float),
+                                   _p(hmm.start_probabilities_cols, C.c_uint64),
+                                   _p(hmm.start_probabilities, C.c_float)))
+    finally:
+        lib.sv_io_hmm_close(h)
+    return hmm
+
+
+def pack_HMM_file(src: str, dst: str) -> None:
+    lib = L.lib()
+    h = C.c_void_p()
+    dims = (C.c_uint64 * 4)()
+    L.check(lib.sv_io_hmm_open(str(src).encode(), C.byref(h), dims))
+    try:
+        L.check(lib.sv_io_hmm_write_packed(h, str(dst).encode()))
+    finally:
+        lib.sv_io_hmm_close(h)
+
+
+def read_emit_seq(path: str) -> list:
+    """.ess text or .essb packed -> list of uint64 arrays."""
+    lib = L.lib()
+    h = C.c_void_p()
+    nseq = C.c_uint64()
+    total = C.c_uint64()
+    L.check(lib.sv_io_ess_open(str(path).encode(), C.byref(h), C.byref(nseq), C.byref(total)))
+    try:
+        offs = np.zeros(nseq.value + 1, np.uint64)
+        syms = np.zeros(max(total.value, 1), np.uint64)
+        L.check(lib.sv_io_ess_copy(h, _p(offs, C.c_uint64), _p(syms, C.c_uint64)))
+    finally:
+        lib.sv_io_ess_close(h)
+    return [syms[int(offs[i]):int(offs[i + 1])].copy() for i in range(nseq.value)]
+
+
+def pack_ess_file(src: str, dst: str) -> None:
+    lib = L.lib()
+    h = C.c_void_p()
+    nseq = C.c_uint64()
+    total = C.c_uint64()
+    L.check(lib.sv_io_ess_open(str(src).encode(), C.byref(h), C.byref(nseq), C.byref(total)))
+    try:
+        L.check(lib.sv_io_ess_write_packed(h, str(dst).encode()))
+    finally:
+        lib.sv_io_ess_close(h)
+
+
+def pack_sequences(seqs: Sequence[Iterable[int]]):
+    """list of sequences -> (symbols uint64[total], offsets uint64[nseq+1])."""
+    arrs = [np.ascontiguousarray(s, dtype=np.uint64) for s in seqs]
+    offs = np.zeros(len(arrs) + 1, np.uint64)
+    if arrs:
+        offs[1:] = np.cumsum([a.size for a in arrs])
+    syms = np.concatenate(arrs) if arrs else np.zeros(0, np.uint64)
+    return np.ascontiguousarray(syms), offs
+
+
+class Model:
+    """Device-resident model handle (sv_model)."""
+
+    def __init__(self, hmm: HMM, device: int = 0):
+        self._lib = L.lib()
+        self.hmm = hmm.normalized()
+        h = self.hmm
+        self._h = C.c_void_p()
+        L.check(self._lib.sv_model_create(
+            h.states_num, h.emit_num, h.trans_num, _p(h.trans_rows, C.c_uint64),
+            _p(h.trans_cols, C.c_uint64), _p(h.trans_probs, C.c_float), _p(h.emissions, C.c_float),
+            h.non_zero_start_probs, _p(h.start_probabilities_cols, C.c_uint64),
+            _p(h.start_probabilities, C.c_float), device, C.byref(self._h)))
+        self.device = device
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.sv_model_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> L.ModelInfo:
+        info = L.ModelInfo()
+        L.check(self._lib.sv_model_get_info(self._h, C.byref(info)))
+        return info
+
+    def set_kernel(self, kernel: int) -> None:
+        L.check(self._lib.sv_model_set_kernel(self._h, kernel))
+
+    def last_launches(self) -> int:
+        return int(self._lib.sv_model_last_launches(self._h))
+
+    # ---- plain path ----
+    def viterbi(self, seq) -> np.ndarray:
+        s = np.ascontiguousarray(seq, np.uint64)
+        out = np.empty(self.hmm.states_num, np.float32)
+        L.check(self._lib.sv_viterbi(self._h, _p(s, C.c_uint64), s.size, _p(out, C.c_float)))
+        return out
+
+    def viterbi_batch(self, symbols: np.ndarray, offsets: np.ndarray, want_vectors=True, want_best=True):
+        nseq = offsets.size - 1
+        out = np.empty((nseq, self.hmm.states_num), np.float32) if want_vectors else None
+        best = np.empty(nseq, np.float32) if want_best else None
+        arg = np.empty(nseq, np.int32) if want_best else None
+        L.check(self._lib.sv_viterbi_batch(
+            self._h, _p(symbols, C.c_uint64), _p(offsets, C.c_uint64), nseq,
+            _p(out, C.c_float) if out is not None else None,
+            _p(best, C.c_float) if best is not None else None,
+            _p(arg, C.c_int32) if arg is not None else None))
+        return out, best, arg
+
+    def upload(self, symbols: np.ndarray, offsets: np.ndarray) -> "Seqs":
+        return Seqs(self, symbols, offsets)
+
+    def viterbi_device(self, seqs: "Seqs", d_out: int = 0, d_best: int = 0, d_arg: int = 0, stream: int = 0):
+        """Device pointers as ints (e.g. torch.Tensor.data_ptr()); asynchronous."""
+        L.check(self._lib.sv_viterbi_device(self._h, seqs.handle, d_out or None, d_best or None,
+                                            d_arg or None, stream or None))
+
+
+class Seqs:
+    """Device-resident batch of observation sequences (sv_seqs)."""
+
+    def __init__(self, model: Model, symbols: np.ndarray, offsets: np.ndarray):
+        self._lib = L.lib()
+        self._h = C.c_void_p()
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        if symbols.dtype == np.uint8:
+            symbols = np.ascontiguousarray(symbols)
+            L.check(self._lib.sv_seqs_create_u8(model.handle, _p(symbols, C.c_uint8),
+                                                _p(offsets, C.c_uint64), offsets.size - 1, C.byref(self._h)))
+        else:
+            symbols = np.ascontiguousarray(symbols, np.uint64)
+            L.check(self._lib.sv_seqs_create(model.handle, _p(symbols, C.c_uint64),
+                                             _p(offsets, C.c_uint64), offsets.size - 1, C.byref(self._h)))
+        self.nseq = offsets.size - 1
+        self.total = int(offsets[-1])
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.sv_seqs_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Spec:
+    """Handler tables of one model at one level (sv_spec)."""
+
+    def __init__(self, model: Model, level: int, method: int = L.SPEC_AUTO, tuple_begin: int = 0,
+                 tuple_end: int = 0, d_table: int = 0, stream: int = 0):
+        self._lib = L.lib()
+        self.model = model
+        self.level = level
+        self._h = C.c_void_p()
+        L.check(self._lib.sv_spec_create(model.handle, level, method, tuple_begin, tuple_end,
+                                         d_table or None, stream or None, C.byref(self._h)))
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.sv_spec_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_range(self, b: int, e: int) -> None:
+        L.check(self._lib.sv_spec_set_range(self._h, b, e))
+
+    def handler(self, tuple_index: int) -> np.ndarray:
+        n = self.model.hmm.states_num
+        out = np.empty((n, n), np.float32)
+        L.check(self._lib.sv_spec_get_handler(self._h, tuple_index, _p(out, C.c_float)))
+        return out
+
+    def run(self, seq) -> np.ndarray:
+        s = np.ascontiguousarray(seq, np.uint64)
+        out = np.empty(self.model.hmm.states_num, np.float32)
+        L.check(self._lib.sv_spec_run(self._h, _p(s, C.c_uint64), s.size, _p(out, C.c_float)))
+        return out
+
+    def run_batch(self, symbols: np.ndarray, offsets: np.ndarray, want_vectors=True, want_best=True):
+        nseq = offsets.size - 1
+        n = self.model.hmm.states_num
+        out = np.empty((nseq, n), np.float32) if want_vectors else None
+        best = np.empty(nseq, np.float32) if want_best else None
+        arg = np.empty(nseq, np.int32) if want_best else None
+        L.check(self._lib.sv_spec_run_batch(
+            self._h, _p(symbols, C.c_uint64), _p(offsets, C.c_uint64), nseq,
+            _p(out, C.c_float) if out is not None else None,
+            _p(best, C.c_float) if best is not None else None,
+            _p(arg, C.c_int32) if arg is not None else None))
+        return out, best, arg
+
+    def run_device(self, seqs: Seqs, d_out: int = 0, d_best: int = 0, d_arg: int = 0, stream: int = 0):
+        L.check(self._lib.sv_spec_run_device(self._h, seqs.handle, d_out or None, d_best or None,
+                                             d_arg or None, stream or None))
+
+
+def _fingerprint(hmm: HMM):
+    h = hmm
+    return (h.states_num, h.emit_num, h.trans_num, h.non_zero_start_probs,
+            hash(np.ascontiguousarray(h.trans_probs).tobytes()),
+            hash(np.ascontiguousarray(h.emissions).tobytes()),
+            hash(np.ascontiguousarray(h.trans_rows).tobytes()),
+            hash(np.ascontiguousarray(h.trans_cols).tobytes()),
+            hash(np.ascontiguousarray(h.start_probabilities).tobytes()),
+            hash(np.ascontiguousarray(h.start_probabilities_cols).tobytes()))
+
+
+class B200_impl:
+    """Drop-in for a reference `Viterbi_impl` backend (Viterbi_impl.h:6-11).
+
+    The reference backends rebuild/re-upload the model on every call; this adaptor keeps the
+    device model of the last HMM it saw (keyed by a content fingerprint), so the first call
+    pays K0 + upload and later calls with the same HMM do not."""
+
+    def __init__(self, device: int = 0):
+        self.device = device
+        self._key = None
+        self._model: Optional[Model] = None
+
+    def model_for(self, hmm: HMM) -> Model:
+        key = _fingerprint(hmm)
+        if key != self._key:
+            if self._model is not None:
+                self._model.close()
+            self._model = Model(hmm, self.device)
+            self._key = key
+        return self._model
+
+    def run_Viterbi(self, hmm: HMM, seq) -> np.ndarray:
+        return self.model_for(hmm).viterbi(seq)
+
+    def run_Viterbi_batch(self, hmm: HMM, seqs: Sequence[Iterable[int]]) -> np.ndarray:
+        syms, offs = pack_sequences(seqs)
+        out, _, _ = self.model_for(hmm).viterbi_batch(syms, offs, True, False)
+        return out
+
+
+class B200_spec_impl:
+    """Drop-in for a reference `Viterbi_spec_impl` backend (Viterbi_spec_impl.h:6-24)."""
+
+    def __init__(self, level: int, device: int = 0, method: int = L.SPEC_AUTO):
+        self.level = int(level)
+        self.device = device
+        self.method = method
+        self._model: Optional[Model] = None
+        self._spec: Optional[Spec] = None
+
+    def get_level(self) -> int:
+        return self.level
+
+    def spec_with(self, hmm: HMM) -> None:
+        # drops the previous tables, then rebuilds (GraphBLAS_spec_impl.cpp:45-48)
+        if self._spec is not None:
+            self._spec.close()
+        if self._model is not None:
+            self._model.close()
+        self._model = Model(hmm, self.device)
+        self._spec = Spec(self._model, self.level, self.method)
+
+    def run_Viterbi_spec(self, seq) -> np.ndarray:
+        if self._spec is None:
+            raise RuntimeError("spec_with(hmm) must be called first")
+        return self._spec.run(seq)
+
+    def run_Viterbi_spec_batch(self, seqs: Sequence[Iterable[int]]) -> np.ndarray:
+        if self._spec is None:
+            raise RuntimeError("spec_with(hmm) must be called first")
+        syms, offs = pack_sequences(seqs)
+        out, _, _ = self._spec.run_batch(syms, offs, True, False)
+        return out

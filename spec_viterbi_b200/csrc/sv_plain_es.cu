@@ -1,0 +1,440 @@
+// Edge-stationary persistent (min,+) Viterbi step kernel for sm_100a ("ES kernel").
+//
+// The batched step  v_t[i] = min_j fl(fl(E[o_t][i] + T'[i][j]) + v_{t-1}[j])  is bound by the
+// gather of v[j] (4 B per relaxation) -- on B200 that is the shared-memory crossbar
+// (128 B/clk/SM), not HBM and not the FP32 pipes.  Everything else is therefore moved
+// OFF the crossbar:
+//   * the transitions (weight, source offset) live in REGISTERS for the whole kernel:
+//     each thread owns up to RMAX destination rows ("ranks") and holds their in-edges in a
+//     statically indexed register file slice, so the model is read from memory exactly once;
+//   * the emission table E[symbol][state] (192 KB at N=2407) is resident in shared memory
+//     and read once per (row, sequence, step);
+//   * the score vectors of Q sequences (interleaved [state][Q], double buffered) are the
+//     only gathered data; K0 (sv_es_plan.cpp) orders every thread's edges so that the 16/32
+//     lanes of one LDS hit distinct banks;
+//   * one CTA walks all time steps of its sequences with one __syncthreads per step
+//     (two when the model has block-reduced heavy rows); finished lanes pull the next
+//     sequence from a global longest-first queue, so ragged batches need no padding.
+// Per-rank trip counts are warp-uniform (rows are dealt to warps in in-degree order) and
+// dispatched through a fall-through switch, which keeps every edge register statically
+// indexed.  Rows whose in-degree exceeds the register budget are either split into
+// virtual states at K0 (exact, because fl(u + min) = min fl(u + .)) or, for the dense rows
+// of profile HMMs, spread over all threads and reduced with warp-shuffle mins.
+//
+// Reference semantics: GraphBLAS_impl.cpp:59,64-73 (add order), GraphBLAS_helper.cpp:65
+// (unreachable -> +inf).  Tensor cores are not used: (min,+) is not an MMA contraction.
+#include "sv_internal.h"
+
+#include <type_traits>
+
+namespace {
+
+__device__ __forceinline__ float pos_inf() { return __int_as_float(0x7f800000); }
+
+template <int... S> struct Shape {
+    static constexpr int R = sizeof...(S);
+    __host__ __device__ static constexpr int at(int r) {
+        constexpr int v[] = {S...};
+        return v[r];
+    }
+    __host__ __device__ static constexpr int base(int r) {
+        int b = 0;
+        for (int k = 0; k < r; ++k) b += at(k);
+        return b;
+    }
+    __host__ __device__ static constexpr int total() { return base(R); }
+};
+
+template <int Q> struct VecOf;
+template <> struct VecOf<1> {
+    using type = float;
+};
+template <> struct VecOf<2> {
+    using type = float2;
+};
+
+template <int Q>
+__device__ __forceinline__ void load_v(const unsigned char* base, uint32_t off, float (&v)[Q]) {
+    if constexpr (Q == 1) {
+        v[0] = *reinterpret_cast<const float*>(base + off);
+    } else {
+        const float2 t = *reinterpret_cast<const float2*>(base + off);
+        v[0] = t.x;
+        v[1] = t.y;
+    }
+}
+
+template <int Q>
+__device__ __forceinline__ void store_v(unsigned char* base, uint32_t off, const float (&v)[Q]) {
+    if constexpr (Q == 1) {
+        *reinterpret_cast<float*>(base + off) = v[0];
+    } else {
+        *reinterpret_cast<float2*>(base + off) = make_float2(v[0], v[1]);
+    }
+}
+
+// One relaxation per sequence lane: fl(fl(E + T') + v), then exact min.
+template <int Q>
+__device__ __forceinline__ void relax(float w, uint32_t off, const unsigned char* vcur,
+                                      const float (&e)[Q], float (&acc)[Q]) {
+    float v[Q];
+    load_v<Q>(vcur, off, v);
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+        const float u = e[q] + w;
+        acc[q] = fminf(acc[q], u + v[q]);
+    }
+}
+
+// Runs slots [0, d) of a register slice of SMAX slots starting at BASE (d <= SMAX,
+// warp-uniform).  Fall-through switch: every register index is a compile-time constant.
+template <int Q, int BASE, int SMAX, int NSLOTS>
+__device__ __forceinline__ void run_slots(int d, const float (&ew)[NSLOTS],
+                                          const uint32_t (&eo)[NSLOTS],
+                                          const unsigned char* vcur, const float (&e)[Q],
+                                          float (&acc)[Q]) {
+#define SV_SLOT(K)                                                                 \
+    if constexpr ((K) < SMAX) relax<Q>(ew[BASE + (K)], eo[BASE + (K)], vcur, e, acc);
+    switch (d) {
+    case 8: SV_SLOT(7) [[fallthrough]];
+    case 7: SV_SLOT(6) [[fallthrough]];
+    case 6: SV_SLOT(5) [[fallthrough]];
+    case 5: SV_SLOT(4) [[fallthrough]];
+    case 4: SV_SLOT(3) [[fallthrough]];
+    case 3: SV_SLOT(2) [[fallthrough]];
+    case 2: SV_SLOT(1) [[fallthrough]];
+    case 1: SV_SLOT(0) [[fallthrough]];
+    default: break;
+    }
+#undef SV_SLOT
+}
+
+template <int TPG, int Q, typename SH, int NH, int HS, typename SymT>
+__global__ void __launch_bounds__(TPG, (TPG >= 512 ? 1 : (TPG >= 256 ? 2 : 4)))
+sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict__ best,
+             int32_t* __restrict__ arg, unsigned* __restrict__ counter) {
+    constexpr int NW = TPG / 32;
+    constexpr int NL = SH::total();        // light slots
+    constexpr int NSL = NL + NH * HS;      // all register slots
+    static_assert(SH::R == SV_ES_RMAX, "shape must list SV_ES_RMAX ranks");
+    static_assert(NH <= SV_ES_NHMAX, "too many heavy rows");
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int n_int = m.n_int;
+    const uint32_t vbytes = static_cast<uint32_t>(n_int) * Q * 4u; // one v buffer
+    unsigned char* vbuf0 = smem_raw;
+    unsigned char* vbuf1 = smem_raw + ((vbytes + 15u) & ~15u);
+    float* red = reinterpret_cast<float*>(vbuf1 + ((vbytes + 15u) & ~15u)); // [NH][NW][Q]
+    const float* Es = red + (NH > 0 ? NH * NW * Q : 0);                    // [emits][n_int]
+    __shared__ unsigned s_work[2];
+    __shared__ float s_bv[NW];
+    __shared__ int s_bi[NW];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const SymT* __restrict__ sym = static_cast<const SymT*>(s.sym);
+
+    // ---- one-time loads: emission table -> smem, this thread's edges -> registers ----
+    {
+        float* Ew = const_cast<float*>(Es);
+        const int total = m.emits * n_int;
+        for (int k = tid; k < total; k += TPG) Ew[k] = m.emis_p[k];
+    }
+    float ew[NSL];
+    uint32_t eo[NSL];
+#pragma unroll
+    for (int k = 0; k < NSL; ++k) {
+        ew[k] = m.edge_w[static_cast<size_t>(k) * TPG + tid]; // K0 fills every slot (pads = +inf)
+        eo[k] = m.edge_off[static_cast<size_t>(k) * TPG + tid];
+    }
+    int deg[SV_ES_RMAX];
+#pragma unroll
+    for (int r = 0; r < SV_ES_RMAX; ++r) deg[r] = m.deg[warp * SV_ES_RMAX + r];
+    const int n_light = m.n_light;
+    const int nranks = (n_light + TPG - 1) / TPG;
+    __syncthreads();
+
+    // ---- per-lane sequence state (CTA-uniform values) ----
+    bool act[Q], init[Q];
+    uint32_t sid[Q];
+    uint64_t base[Q], len[Q], t[Q];
+    uint32_t o_cur[Q], o_n1[Q];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+        act[q] = false;
+        init[q] = false;
+        sid[q] = 0;
+        base[q] = 0;
+        len[q] = 0;
+        t[q] = 0;
+        o_cur[q] = 0;
+        o_n1[q] = 0;
+    }
+    bool drained = false;
+    unsigned char* vcur = vbuf0;
+    unsigned char* vnxt = vbuf1;
+
+    for (;;) {
+        // ---- (A) hand new sequences to idle lanes ----
+        bool want = false;
+#pragma unroll
+        for (int q = 0; q < Q; ++q) want |= !act[q];
+        if (want && !drained) {
+            if (tid == 0) {
+#pragma unroll
+                for (int q = 0; q < Q; ++q)
+                    if (!act[q]) s_work[q] = atomicAdd(counter, 1u);
+            }
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                if (!act[q]) {
+                    const unsigned w = s_work[q];
+                    if (w >= static_cast<unsigned>(s.nseq)) {
+                        drained = true;
+                    } else {
+                        sid[q] = s.order[w];
+                        base[q] = s.off[sid[q]];
+                        len[q] = s.off[sid[q] + 1] - base[q];
+                        t[q] = 0;
+                        act[q] = true;
+                        init[q] = true;
+                        o_cur[q] = sym[base[q]];
+                        o_n1[q] = sym[base[q] + 1]; // the symbol buffer is padded past the end
+                    }
+                }
+            }
+        }
+        bool any = false, any_init = false;
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+            any |= act[q];
+            any_init |= init[q];
+        }
+        if (!any) break;
+
+        // ---- (B) one time step for all lanes ----
+        uint32_t o_n2[Q];
+#pragma unroll
+        for (int q = 0; q < Q; ++q) o_n2[q] = sym[base[q] + t[q] + 2]; // consumed two steps later
+        const float* erow[Q];
+#pragma unroll
+        for (int q = 0; q < Q; ++q) erow[q] = Es + static_cast<size_t>(o_cur[q]) * n_int;
+
+        auto rank_step = [&](auto rc) {
+            constexpr int r = decltype(rc)::value;
+            if (r < nranks) {
+                const int p = tid + r * TPG;
+                const int pc = p < n_int ? p : n_int - 1;
+                float e[Q], acc[Q];
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    e[q] = erow[q][pc];
+                    acc[q] = pos_inf();
+                }
+                run_slots<Q, SH::base(r), SH::at(r), NSL>(deg[r], ew, eo, vcur, e, acc);
+                if (any_init) {
+                    const float st = m.start_p[pc];
+#pragma unroll
+                    for (int q = 0; q < Q; ++q)
+                        if (init[q]) acc[q] = e[q] + st; // v_0 = E[o_0] + start
+                }
+                if (p < n_light) store_v<Q>(vnxt, static_cast<uint32_t>(p) * Q * 4u, acc);
+            }
+        };
+        rank_step(std::integral_constant<int, 0>{});
+        rank_step(std::integral_constant<int, 1>{});
+        rank_step(std::integral_constant<int, 2>{});
+        rank_step(std::integral_constant<int, 3>{});
+        rank_step(std::integral_constant<int, 4>{});
+        static_assert(SV_ES_RMAX == 5, "rank_step calls above assume 5 ranks");
+        if constexpr (NH > 0) {
+            auto heavy_step = [&](auto hc) {
+                constexpr int h = decltype(hc)::value;
+                if (h < NH && h < m.n_heavy) {
+                    const int ph = n_light + h;
+                    float he[Q], acc[Q];
+#pragma unroll
+                    for (int q = 0; q < Q; ++q) {
+                        he[q] = erow[q][ph];
+                        acc[q] = pos_inf();
+                    }
+                    run_slots<Q, NL + (h < NH ? h : 0) * HS, HS, NSL>(m.heavy_slots[h], ew, eo, vcur,
+                                                                     he, acc);
+#pragma unroll
+                    for (int q = 0; q < Q; ++q) {
+#pragma unroll
+                        for (int d = 16; d > 0; d >>= 1)
+                            acc[q] = fminf(acc[q], __shfl_xor_sync(0xffffffffu, acc[q], d));
+                        if (lane == 0) red[(h * NW + warp) * Q + q] = acc[q];
+                    }
+                }
+            };
+            heavy_step(std::integral_constant<int, 0>{});
+            heavy_step(std::integral_constant<int, 1>{});
+            static_assert(SV_ES_NHMAX == 2, "heavy_step calls above assume 2 heavy rows");
+            if (m.n_heavy > 0) {
+                __syncthreads();
+                if (warp < m.n_heavy) {
+                    const int h = warp;
+                    const int ph = n_light + h;
+                    float acc[Q];
+#pragma unroll
+                    for (int q = 0; q < Q; ++q) {
+                        float x = lane < NW ? red[(h * NW + lane) * Q + q] : pos_inf();
+#pragma unroll
+                        for (int d = 16; d > 0; d >>= 1)
+                            x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
+                        acc[q] = x;
+                        if (init[q]) acc[q] = erow[q][ph] + m.start_p[ph];
+                    }
+                    if (lane == 0) store_v<Q>(vnxt, static_cast<uint32_t>(ph) * Q * 4u, acc);
+                }
+            }
+        }
+        __syncthreads();
+        {
+            unsigned char* sw = vcur;
+            vcur = vnxt;
+            vnxt = sw;
+        }
+
+        // ---- (C) advance lanes; emit results of finished sequences ----
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+            init[q] = false;
+            o_cur[q] = o_n1[q];
+            o_n1[q] = o_n2[q];
+            if (act[q]) {
+                t[q] += 1;
+                if (t[q] == len[q]) {
+                    act[q] = false;
+                    const float* vq = reinterpret_cast<const float*>(vcur) + q;
+                    float bv = pos_inf();
+                    int bi = 0x7fffffff;
+                    for (int i = tid; i < m.n; i += TPG) {
+                        float x = pos_inf();
+                        const uint32_t c1 = m.copy_ptr[i + 1];
+                        for (uint32_t c = m.copy_ptr[i]; c < c1; ++c)
+                            x = fminf(x, vq[m.copy_p[c] * Q]);
+                        if (out != nullptr) out[static_cast<size_t>(sid[q]) * m.n + i] = x;
+                        if (x < bv) {
+                            bv = x;
+                            bi = i;
+                        }
+                    }
+                    if (best != nullptr || arg != nullptr) {
+#pragma unroll
+                        for (int d = 16; d > 0; d >>= 1) {
+                            const float ov = __shfl_xor_sync(0xffffffffu, bv, d);
+                            const int oi = __shfl_xor_sync(0xffffffffu, bi, d);
+                            if (ov < bv || (ov == bv && oi < bi)) {
+                                bv = ov;
+                                bi = oi;
+                            }
+                        }
+                        if (lane == 0) {
+                            s_bv[warp] = bv;
+                            s_bi[warp] = bi;
+                        }
+                        __syncthreads();
+                        if (warp == 0) {
+                            bv = lane < NW ? s_bv[lane] : pos_inf();
+                            bi = lane < NW ? s_bi[lane] : 0x7fffffff;
+#pragma unroll
+                            for (int d = 16; d > 0; d >>= 1) {
+                                const float ov = __shfl_xor_sync(0xffffffffu, bv, d);
+                                const int oi = __shfl_xor_sync(0xffffffffu, bi, d);
+                                if (ov < bv || (ov == bv && oi < bi)) {
+                                    bv = ov;
+                                    bi = oi;
+                                }
+                            }
+                            if (lane == 0) {
+                                if (best != nullptr) best[sid[q]] = bv;
+                                if (arg != nullptr) arg[sid[q]] = bi == 0x7fffffff ? -1 : bi;
+                            }
+                        }
+                        __syncthreads();
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------- variant table ----
+using ShapeSparse = Shape<8, 6, 5, 4, 3>;  // random sparse models (in-degree capped at 8)
+using ShapeProfile = Shape<4, 3, 3, 2, 2>; // profile HMMs: <=2 in-edges per light row
+
+const SvEsVariant kVariants[] = {
+    // threads, q, shape, nh, hs
+    {512, 2, {8, 6, 5, 4, 3}, 0, 0},
+    {512, 1, {8, 6, 5, 4, 3}, 0, 0},
+    {256, 2, {8, 6, 5, 4, 3}, 0, 0},
+    {256, 1, {8, 6, 5, 4, 3}, 0, 0},
+    {128, 2, {8, 6, 5, 4, 3}, 0, 0},
+    {128, 1, {8, 6, 5, 4, 3}, 0, 0},
+    {512, 2, {4, 3, 3, 2, 2}, 2, 5},
+    {512, 1, {4, 3, 3, 2, 2}, 2, 5},
+    {256, 2, {4, 3, 3, 2, 2}, 2, 5},
+    {256, 1, {4, 3, 3, 2, 2}, 2, 5},
+    {128, 2, {4, 3, 3, 2, 2}, 2, 5},
+    {128, 1, {4, 3, 3, 2, 2}, 2, 5},
+};
+constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+
+template <typename SymT> const void* variant_fn(int index) {
+    switch (index) {
+    case 0: return (const void*)sv_es_kernel<512, 2, ShapeSparse, 0, 0, SymT>;
+    case 1: return (const void*)sv_es_kernel<512, 1, ShapeSparse, 0, 0, SymT>;
+    case 2: return (const void*)sv_es_kernel<256, 2, ShapeSparse, 0, 0, SymT>;
+    case 3: return (const void*)sv_es_kernel<256, 1, ShapeSparse, 0, 0, SymT>;
+    case 4: return (const void*)sv_es_kernel<128, 2, ShapeSparse, 0, 0, SymT>;
+    case 5: return (const void*)sv_es_kernel<128, 1, ShapeSparse, 0, 0, SymT>;
+    case 6: return (const void*)sv_es_kernel<512, 2, ShapeProfile, 2, 5, SymT>;
+    case 7: return (const void*)sv_es_kernel<512, 1, ShapeProfile, 2, 5, SymT>;
+    case 8: return (const void*)sv_es_kernel<256, 2, ShapeProfile, 2, 5, SymT>;
+    case 9: return (const void*)sv_es_kernel<256, 1, ShapeProfile, 2, 5, SymT>;
+    case 10: return (const void*)sv_es_kernel<128, 2, ShapeProfile, 2, 5, SymT>;
+    case 11: return (const void*)sv_es_kernel<128, 1, ShapeProfile, 2, 5, SymT>;
+    default: return nullptr;
+    }
+}
+
+} // namespace
+
+int sv_es_num_variants() { return kNumVariants; }
+const SvEsVariant& sv_es_variant(int index) { return kVariants[index]; }
+
+int sv_es_prepare(int index, size_t smem) {
+    for (int b = 0; b < 2; ++b) {
+        const void* fn = b == 0 ? variant_fn<uint8_t>(index) : variant_fn<uint16_t>(index);
+        if (fn == nullptr) return cudaErrorInvalidValue;
+        cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(smem));
+        if (e != cudaSuccess) return e;
+    }
+    return 0;
+}
+
+int sv_es_max_ctas_per_sm(int index, size_t smem) {
+    int n = 0;
+    const void* fn = variant_fn<uint8_t>(index);
+    if (fn == nullptr) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, kVariants[index].threads, smem) !=
+        cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int sv_es_launch(int index, const SvEsDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+                 int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st) {
+    const void* fn = s.sym_bytes == 1 ? variant_fn<uint8_t>(index) : variant_fn<uint16_t>(index);
+    if (fn == nullptr) return cudaErrorInvalidValue;
+    void* args[] = {(void*)&m, (void*)&s, (void*)&d_out, (void*)&d_best, (void*)&d_arg,
+                    (void*)&d_counter};
+    cudaError_t e = cudaLaunchKernel(fn, dim3(grid), dim3(kVariants[index].threads), args, smem, st);
+    return e != cudaSuccess ? e : cudaGetLastError();
+}

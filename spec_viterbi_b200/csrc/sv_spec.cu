@@ -1,0 +1,595 @@
+// Specialised path: precompute of the per-tuple handlers (K3 dense (min,+) GEMM, K3' sparse
+// left factor) and the level-L run phase (K4 handler x vector, level-1 tail steps).
+//
+// Reference: GraphBLAS_spec_impl.cpp:103-182 (initializer), :15-36 (add_level:
+// handler[key ++ i] = M_i (x) handler[key], sparse level-1 matrix on the LEFT), :50-97
+// (run: first symbol folded with the start vector, chunks of `level` symbols from index 1,
+// tail with level-1 matrices).  Handlers are stored dense (+inf = no entry): for the
+// profile HMMs they are ~99.7% dense.  Every value is a min of singly rounded sums in the
+// reference's association, so each level is bit-exact against the same-level oracle.
+//
+// Level 1 needs no tables: the plain kernels form fl(E + T') on the fly with identical bits.
+#include "sv_internal.h"
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+struct sv_spec {
+    sv_model* m = nullptr;
+    uint64_t level = 1;
+    uint64_t ntuples = 1;     // emits^level
+    uint64_t t_begin = 0, t_end = 0; // valid tuple range of the table
+    float* d_table = nullptr; // [(t_end-t_begin)][n][n]
+    uint64_t table_first = 0; // tuple index stored at d_table[0]
+    bool owns_table = false;
+    int method = SV_SPEC_SPARSE_LHS;
+    // run-phase scratch
+    float* d_v[2] = {nullptr, nullptr};
+    uint64_t v_capacity = 0;
+};
+
+namespace {
+
+__device__ __forceinline__ float pos_inf() { return __int_as_float(0x7f800000); }
+
+__device__ __forceinline__ float warp_min(float x) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
+    return x;
+}
+
+// ---------------------------------------------------------------- level 1 dense ----
+// dst[o][i][j] = +inf, then fl(E[o][i] + T'[i][j]) on the pattern (ld = leading dimension).
+__global__ void fill_inf_kernel(float* __restrict__ p, size_t count) {
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t k = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < count; k += stride)
+        p[k] = pos_inf();
+}
+
+__global__ void scatter_level1_kernel(SvGenericDev m, float* __restrict__ dst,
+                                      float* __restrict__ dst_t, size_t ld, size_t mat_stride,
+                                      int sym_begin, int sym_count) {
+    // one thread per (row, symbol): walks the row's edges
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int o = sym_begin + blockIdx.y;
+    if (i >= m.n || static_cast<int>(blockIdx.y) >= sym_count) return;
+    const float e = m.emis[static_cast<size_t>(o) * m.n + i];
+    float* row = dst + static_cast<size_t>(blockIdx.y) * mat_stride + static_cast<size_t>(i) * ld;
+    float* colT = dst_t ? dst_t + static_cast<size_t>(blockIdx.y) * mat_stride + i : nullptr;
+    for (uint32_t p = m.rowptr[i]; p < m.rowptr[i + 1]; ++p) {
+        const float v = e + m.w[p];
+        row[m.col[p]] = v;
+        if (colT) colT[static_cast<size_t>(m.col[p]) * ld] = v; // transposed copy [j][i]
+    }
+}
+
+// ------------------------------------------------------------ K3': sparse left factor ----
+// out[t][i][k] = min_{j in row i of T'} fl( fl(E[sym(t)][i] + T'[i][j]) + prev[prefix(t)][j][k] )
+// grid: x = column tile (blockDim.x * 4 columns), y = row i, z = tuple (relative)
+__global__ void __launch_bounds__(256)
+sparse_lhs_kernel(SvGenericDev m, const float* __restrict__ prev, uint64_t prev_first,
+                  float* __restrict__ out, uint64_t tuple_first, int emits) {
+    const int n = m.n;
+    const int i = blockIdx.y;
+    const uint64_t tuple = tuple_first + blockIdx.z;
+    const int symb = static_cast<int>(tuple % emits);
+    const uint64_t prefix = tuple / emits;
+    const float* __restrict__ P = prev + (prefix - prev_first) * static_cast<size_t>(n) * n;
+    float* __restrict__ O = out + static_cast<size_t>(blockIdx.z) * n * n + static_cast<size_t>(i) * n;
+    const float e = m.emis[static_cast<size_t>(symb) * n + i];
+    const uint32_t p0 = m.rowptr[i], p1 = m.rowptr[i + 1];
+    for (int k0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4; k0 < n; k0 += gridDim.x * blockDim.x * 4) {
+        float acc[4] = {pos_inf(), pos_inf(), pos_inf(), pos_inf()};
+        for (uint32_t p = p0; p < p1; ++p) {
+            const float a = e + m.w[p]; // level-1 value M_sym[i][j]
+            const float* __restrict__ prow = P + static_cast<size_t>(m.col[p]) * n + k0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (k0 + c < n) acc[c] = fminf(acc[c], a + prow[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (k0 + c < n) O[k0 + c] = acc[c];
+    }
+}
+
+// ------------------------------------------------------------ K3: dense (min,+) GEMM ----
+// C[t] = A[b] (x) B[a] for pair tuple t = a*emits + b (a consumed first).  Operands are the
+// dense level-1 matrices padded to ld = npad (multiple of 128) with +inf: B = L1[a]
+// (row-major, k x n) and A^T = L1T[b] (the transposed copy, k x m), so both tiles are plain
+// row copies.  128x128x16 CTA tile, 256 threads, 8x8 register tile, 3-stage cp.async ring.
+// Inner loop: per two k, 8 LDS.128 feed 128 FADD + 64 FMNMX3 (3-input min, sm_100).
+constexpr int GM = 128, GN = 128, GK = 16, GSTAGES = 3;
+constexpr size_t GEMM_SMEM = static_cast<size_t>(GSTAGES) * GK * (GM + GN) * sizeof(float);
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N));
+}
+
+__global__ void __launch_bounds__(256, 2)
+dense_minplus_gemm_kernel(const float* __restrict__ L1, const float* __restrict__ L1T, size_t npad,
+                          float* __restrict__ out, int n, uint64_t tuple_first, int emits) {
+    extern __shared__ __align__(16) float gsm[];
+    float(*As)[GK][GM] = reinterpret_cast<float(*)[GK][GM]>(gsm);
+    float(*Bs)[GK][GN] = reinterpret_cast<float(*)[GK][GN]>(gsm + GSTAGES * GK * GM);
+    const uint64_t tuple = tuple_first + blockIdx.z;
+    const int sa = static_cast<int>(tuple / emits); // first consumed symbol -> right factor
+    const int sb = static_cast<int>(tuple % emits); // second symbol -> left factor
+    const float* __restrict__ AT = L1T + static_cast<size_t>(sb) * npad * npad;
+    const float* __restrict__ B = L1 + static_cast<size_t>(sa) * npad * npad;
+    const int m0 = blockIdx.y * GM, n0 = blockIdx.x * GN;
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+
+    // each thread copies 2 x 16 B of the A^T tile and 2 x 16 B of the B tile per stage
+    const int c_k = tid >> 5, c_col = (tid & 31) * 4; // rows c_k and c_k + 8
+    auto issue = [&](int kt, int stage) {
+        const size_t k0 = static_cast<size_t>(kt) * GK;
+        cp_async16(&As[stage][c_k][c_col], AT + (k0 + c_k) * npad + m0 + c_col);
+        cp_async16(&As[stage][c_k + 8][c_col], AT + (k0 + c_k + 8) * npad + m0 + c_col);
+        cp_async16(&Bs[stage][c_k][c_col], B + (k0 + c_k) * npad + n0 + c_col);
+        cp_async16(&Bs[stage][c_k + 8][c_col], B + (k0 + c_k + 8) * npad + n0 + c_col);
+    };
+
+    float c[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c[i][j] = pos_inf();
+
+    const int ktiles = static_cast<int>(npad) / GK;
+#pragma unroll
+    for (int s = 0; s < GSTAGES - 1; ++s) {
+        if (s < ktiles) issue(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < ktiles; ++kt) {
+        cp_async_wait<GSTAGES - 2>();
+        __syncthreads(); // tile kt landed for everyone; stage (kt-1)%S is free again
+        if (kt + GSTAGES - 1 < ktiles) issue(kt + GSTAGES - 1, (kt + GSTAGES - 1) % GSTAGES);
+        cp_async_commit();
+        const int buf = kt % GSTAGES;
+#pragma unroll
+        for (int kk = 0; kk < GK; kk += 2) {
+            float a0[8], a1[8], b0[8], b1[8];
+            *reinterpret_cast<float4*>(&a0[0]) = *reinterpret_cast<const float4*>(&As[buf][kk][ty * 4]);
+            *reinterpret_cast<float4*>(&a0[4]) = *reinterpret_cast<const float4*>(&As[buf][kk][64 + ty * 4]);
+            *reinterpret_cast<float4*>(&a1[0]) = *reinterpret_cast<const float4*>(&As[buf][kk + 1][ty * 4]);
+            *reinterpret_cast<float4*>(&a1[4]) = *reinterpret_cast<const float4*>(&As[buf][kk + 1][64 + ty * 4]);
+            *reinterpret_cast<float4*>(&b0[0]) = *reinterpret_cast<const float4*>(&Bs[buf][kk][tx * 4]);
+            *reinterpret_cast<float4*>(&b0[4]) = *reinterpret_cast<const float4*>(&Bs[buf][kk][64 + tx * 4]);
+            *reinterpret_cast<float4*>(&b1[0]) = *reinterpret_cast<const float4*>(&Bs[buf][kk + 1][tx * 4]);
+            *reinterpret_cast<float4*>(&b1[4]) = *reinterpret_cast<const float4*>(&Bs[buf][kk + 1][64 + tx * 4]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    c[i][j] = fminf(c[i][j], fminf(a0[i] + b0[j], a1[i] + b1[j]));
+        }
+    }
+    float* __restrict__ O = out + static_cast<size_t>(blockIdx.z) * n * n;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        if (row >= n) continue;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int col = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+            if (col < n) O[static_cast<size_t>(row) * n + col] = c[i][j];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------- run phase ----
+struct RunSeqs {
+    int nseq;
+    const void* sym;
+    int sym_bytes;
+    const uint64_t* off;
+};
+
+__device__ __forceinline__ unsigned load_sym(const RunSeqs& s, uint64_t idx) {
+    return s.sym_bytes == 1 ? static_cast<const uint8_t*>(s.sym)[idx]
+                            : static_cast<const uint16_t*>(s.sym)[idx];
+}
+
+// v0[s][i] = fl(E[o_0][i] + start[i])      (GraphBLAS_spec_impl.cpp:54,153-154)
+__global__ void spec_init_kernel(SvGenericDev m, RunSeqs s, float* __restrict__ v) {
+    const int q = blockIdx.y;
+    const unsigned o = load_sym(s, s.off[q]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m.n; i += gridDim.x * blockDim.x)
+        v[static_cast<size_t>(q) * m.n + i] = m.emis[static_cast<size_t>(o) * m.n + i] + m.start[i];
+}
+
+// K4: one chunk of `level` symbols: vout[s] = H[key(s, chunk)] (x) vin[s]; sequences whose
+// chunks are exhausted copy vin -> vout.  grid: x = row tile, y = sequence; one warp per row.
+__global__ void __launch_bounds__(256)
+handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
+                    const float* __restrict__ table, uint64_t table_first,
+                    const float* __restrict__ vin, float* __restrict__ vout, int rows_per_cta) {
+    extern __shared__ float sv[];
+    const int q = blockIdx.y;
+    const uint64_t o0 = s.off[q];
+    const uint64_t len = s.off[q + 1] - o0;
+    const uint64_t nchunks = (len - 1) / level;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
+    float* __restrict__ vo = vout + static_cast<size_t>(q) * n;
+    const int r0 = blockIdx.x * rows_per_cta;
+    const int r1 = min(n, r0 + rows_per_cta);
+    if (chunk >= nchunks) {
+        for (int i = r0 + threadIdx.x; i < r1; i += blockDim.x) vo[i] = vi[i];
+        return;
+    }
+    for (int k = threadIdx.x; k < n; k += blockDim.x) sv[k] = vi[k];
+    uint64_t tuple = 0;
+    for (int j = 0; j < level; ++j) tuple = tuple * emits + load_sym(s, o0 + 1 + chunk * level + j);
+    const float* __restrict__ H = table + (tuple - table_first) * static_cast<size_t>(n) * n;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int i = r0 + warp; i < r1; i += nw) {
+        const float* __restrict__ hrow = H + static_cast<size_t>(i) * n;
+        float acc = pos_inf();
+        for (int k = lane; k < n; k += 32) acc = fminf(acc, hrow[k] + sv[k]);
+        acc = warp_min(acc);
+        if (lane == 0) vo[i] = acc;
+    }
+}
+
+// Level-1 tail step number `tail` (0-based) of every sequence that still has one
+// (GraphBLAS_spec_impl.cpp:84-89); others copy.  One CTA per sequence.
+__global__ void __launch_bounds__(1024)
+tail_step_kernel(SvGenericDev m, int level, RunSeqs s, int tail, const float* __restrict__ vin,
+                 float* __restrict__ vout) {
+    extern __shared__ float sv[];
+    const int q = blockIdx.x;
+    const uint64_t o0 = s.off[q];
+    const uint64_t len = s.off[q + 1] - o0;
+    const uint64_t nchunks = (len - 1) / level;
+    const uint64_t ntail = (len - 1) % level;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * m.n;
+    float* __restrict__ vo = vout + static_cast<size_t>(q) * m.n;
+    if (static_cast<uint64_t>(tail) >= ntail) {
+        for (int i = threadIdx.x; i < m.n; i += blockDim.x) vo[i] = vi[i];
+        return;
+    }
+    for (int k = threadIdx.x; k < m.n; k += blockDim.x) sv[k] = vi[k];
+    const unsigned o = load_sym(s, o0 + 1 + nchunks * level + tail);
+    const float* __restrict__ em = m.emis + static_cast<size_t>(o) * m.n;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    // warp per row keeps the dense rows of profile HMMs cheap; light rows cost one pass
+    for (int i = warp; i < m.n; i += nw) {
+        const float e = em[i];
+        float acc = pos_inf();
+        for (uint32_t p = m.rowptr[i] + lane; p < m.rowptr[i + 1]; p += 32) {
+            const float u = e + m.w[p];
+            acc = fminf(acc, u + sv[m.col[p]]);
+        }
+        acc = warp_min(acc);
+        if (lane == 0) vo[i] = acc;
+    }
+}
+
+// (min, lowest argmin) of each final vector; optional copy-out is done by the caller.
+__global__ void __launch_bounds__(256)
+best_state_kernel(int n, const float* __restrict__ v, float* __restrict__ best,
+                  int32_t* __restrict__ arg) {
+    __shared__ float s_bv[8];
+    __shared__ int s_bi[8];
+    const int q = blockIdx.x;
+    const float* __restrict__ x = v + static_cast<size_t>(q) * n;
+    float bv = pos_inf();
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        if (x[i] < bv) {
+            bv = x[i];
+            bi = i;
+        }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int round = 0; round < 2; ++round) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, d);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, d);
+            if (ov < bv || (ov == bv && oi < bi)) {
+                bv = ov;
+                bi = oi;
+            }
+        }
+        if (round == 0) {
+            if (lane == 0) {
+                s_bv[warp] = bv;
+                s_bi[warp] = bi;
+            }
+            __syncthreads();
+            bv = lane < 8 ? s_bv[lane] : pos_inf();
+            bi = lane < 8 ? s_bi[lane] : 0x7fffffff;
+        }
+    }
+    if (threadIdx.x == 0) {
+        if (best) best[q] = bv;
+        if (arg) arg[q] = bi == 0x7fffffff ? -1 : bi;
+    }
+}
+
+uint64_t ipow(uint64_t b, uint64_t e) {
+    uint64_t r = 1;
+    for (uint64_t k = 0; k < e; ++k) {
+        if (r > (~0ull) / b) return ~0ull;
+        r *= b;
+    }
+    return r;
+}
+
+// Builds handlers [tb, te) of level `lvl` into dst (dense, ld = n) with the sparse-left
+// kernel, recursing over the prefixes.  Level 1 = dense scatter of M_o.
+int build_sparse(sv_model* m, uint64_t lvl, uint64_t tb, uint64_t te, float* dst, cudaStream_t st) {
+    const size_t n = m->n;
+    const size_t mat = n * n;
+    if (lvl == 1) {
+        const size_t count = (te - tb) * mat;
+        fill_inf_kernel<<<std::min<size_t>((count + 255) / 256, 148 * 16), 256, 0, st>>>(dst, count);
+        dim3 grid(static_cast<unsigned>((n + 127) / 128), static_cast<unsigned>(te - tb));
+        scatter_level1_kernel<<<grid, 128, 0, st>>>(m->gen, dst, nullptr, n, mat,
+                                                    static_cast<int>(tb), static_cast<int>(te - tb));
+        SV_CUDA(cudaGetLastError());
+        return SV_OK;
+    }
+    const uint64_t pb = tb / m->emits, pe = (te - 1) / m->emits + 1;
+    float* prev = nullptr;
+    if (cudaMalloc(&prev, (pe - pb) * mat * sizeof(float)) != cudaSuccess) {
+        cudaGetLastError();
+        return sv_fail(SV_ERR_MEMORY, "spec precompute: prefix table does not fit device memory");
+    }
+    int rc = build_sparse(m, lvl - 1, pb, pe, prev, st);
+    if (rc == SV_OK) {
+        const uint64_t zmax = 32768;
+        for (uint64_t t0 = tb; t0 < te && rc == SV_OK; t0 += zmax) {
+            const uint64_t cnt = std::min(zmax, te - t0);
+            dim3 grid(static_cast<unsigned>((n + 1023) / 1024), static_cast<unsigned>(n),
+                      static_cast<unsigned>(cnt));
+            sparse_lhs_kernel<<<grid, 256, 0, st>>>(m->gen, prev, pb, dst + (t0 - tb) * mat, t0,
+                                                    static_cast<int>(m->emits));
+            if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "sparse_lhs launch failed");
+        }
+    }
+    cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(prev);
+    if (rc == SV_OK && e != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, cudaGetErrorString(e));
+    return rc;
+}
+
+int build_dense_level2(sv_model* m, uint64_t tb, uint64_t te, float* dst, cudaStream_t st) {
+    const size_t n = m->n;
+    const size_t npad = (n + GM - 1) / GM * GM;
+    float* l1 = nullptr;
+    const size_t count = 2 * m->emits * npad * npad; // row-major copy, then transposed copy
+    if (cudaMalloc(&l1, count * sizeof(float)) != cudaSuccess) {
+        cudaGetLastError();
+        return sv_fail(SV_ERR_MEMORY, "spec precompute: padded level-1 operands do not fit");
+    }
+    fill_inf_kernel<<<148 * 16, 256, 0, st>>>(l1, count);
+    dim3 sgrid(static_cast<unsigned>((n + 127) / 128), static_cast<unsigned>(m->emits));
+    float* l1t = l1 + m->emits * npad * npad;
+    scatter_level1_kernel<<<sgrid, 128, 0, st>>>(m->gen, l1, l1t, npad, npad * npad, 0,
+                                                 static_cast<int>(m->emits));
+    if (cudaFuncSetAttribute(dense_minplus_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(GEMM_SMEM)) != cudaSuccess) {
+        cudaFree(l1);
+        return sv_fail(SV_ERR_CUDA, "dense gemm: cannot reserve shared memory");
+    }
+    int rc = SV_OK;
+    const uint64_t zmax = 32768;
+    for (uint64_t t0 = tb; t0 < te && rc == SV_OK; t0 += zmax) {
+        const uint64_t cnt = std::min(zmax, te - t0);
+        dim3 grid(static_cast<unsigned>(npad / GN), static_cast<unsigned>(npad / GM),
+                  static_cast<unsigned>(cnt));
+        dense_minplus_gemm_kernel<<<grid, 256, GEMM_SMEM, st>>>(l1, l1t, npad, dst + (t0 - tb) * n * n,
+                                                        static_cast<int>(n), t0,
+                                                        static_cast<int>(m->emits));
+        if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "dense gemm launch failed");
+    }
+    cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(l1);
+    if (rc == SV_OK && e != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, cudaGetErrorString(e));
+    return rc;
+}
+
+} // namespace
+
+extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t tuple_begin,
+                              uint64_t tuple_end, float* d_table, void* stream, sv_spec** out) {
+    if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_create: out is NULL");
+    *out = nullptr;
+    if (m == nullptr || level < 1) return sv_fail(SV_ERR_ARG, "sv_spec_create: bad argument");
+    const uint64_t ntuples = ipow(m->emits, level);
+    if (ntuples == ~0ull) return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_create: emits^level overflows");
+    if (tuple_begin == 0 && tuple_end == 0) tuple_end = ntuples;
+    if (tuple_begin > tuple_end || tuple_end > ntuples)
+        return sv_fail(SV_ERR_ARG, "sv_spec_create: bad tuple range");
+    if (method == SV_SPEC_AUTO) method = SV_SPEC_SPARSE_LHS;
+    if (method != SV_SPEC_SPARSE_LHS && method != SV_SPEC_DENSE_GEMM)
+        return sv_fail(SV_ERR_ARG, "sv_spec_create: unknown method");
+    if (method == SV_SPEC_DENSE_GEMM && level != 2 && level != 1)
+        return sv_fail(SV_ERR_UNSUPPORTED, "dense (min,+) GEMM precompute is implemented for level 2");
+    SV_CUDA(cudaSetDevice(m->device));
+    sv_spec* s = new (std::nothrow) sv_spec;
+    if (s == nullptr) return sv_fail(SV_ERR_MEMORY, "sv_spec_create: out of host memory");
+    s->m = m;
+    s->level = level;
+    s->ntuples = ntuples;
+    s->method = method;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (level > 1) {
+        const size_t mat = static_cast<size_t>(m->n) * m->n;
+        s->table_first = tuple_begin;
+        s->t_begin = tuple_begin;
+        s->t_end = tuple_end;
+        if (d_table != nullptr) {
+            s->d_table = d_table;
+        } else if (tuple_end > tuple_begin) {
+            if (cudaMalloc(&s->d_table, (tuple_end - tuple_begin) * mat * sizeof(float)) != cudaSuccess) {
+                cudaGetLastError();
+                delete s;
+                return sv_fail(SV_ERR_MEMORY, "sv_spec_create: handler table does not fit device memory");
+            }
+            s->owns_table = true;
+        }
+        int rc = SV_OK;
+        if (tuple_end > tuple_begin) {
+            rc = method == SV_SPEC_DENSE_GEMM
+                     ? build_dense_level2(m, tuple_begin, tuple_end, s->d_table, st)
+                     : build_sparse(m, level, tuple_begin, tuple_end, s->d_table, st);
+        }
+        if (rc != SV_OK) {
+            sv_spec_destroy(s);
+            return rc;
+        }
+    }
+    *out = s;
+    return SV_OK;
+}
+
+extern "C" void sv_spec_destroy(sv_spec* s) {
+    if (s == nullptr) return;
+    cudaSetDevice(s->m->device);
+    if (s->owns_table && s->d_table) cudaFree(s->d_table);
+    if (s->d_v[0]) cudaFree(s->d_v[0]);
+    if (s->d_v[1]) cudaFree(s->d_v[1]);
+    delete s;
+}
+
+extern "C" uint64_t sv_spec_level(const sv_spec* s) { return s ? s->level : 0; }
+
+extern "C" int sv_spec_set_range(sv_spec* s, uint64_t tuple_begin, uint64_t tuple_end) {
+    if (s == nullptr || tuple_begin > tuple_end || tuple_end > s->ntuples)
+        return sv_fail(SV_ERR_ARG, "sv_spec_set_range: bad argument");
+    if (s->owns_table) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: table is library-owned");
+    s->t_begin = tuple_begin;
+    s->t_end = tuple_end;
+    return SV_OK;
+}
+
+extern "C" float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_t* tuple_end) {
+    if (s == nullptr) return nullptr;
+    if (tuple_begin) *tuple_begin = s->t_begin;
+    if (tuple_end) *tuple_end = s->t_end;
+    return s->d_table;
+}
+
+extern "C" int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out) {
+    if (s == nullptr || out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_get_handler: NULL");
+    if (s->level < 2 || tuple_index < s->t_begin || tuple_index >= s->t_end)
+        return sv_fail(SV_ERR_ARG, "sv_spec_get_handler: tuple not in the table");
+    const size_t mat = static_cast<size_t>(s->m->n) * s->m->n;
+    SV_CUDA(cudaSetDevice(s->m->device));
+    SV_CUDA(cudaMemcpy(out, s->d_table + (tuple_index - s->table_first) * mat, mat * sizeof(float),
+                       cudaMemcpyDeviceToHost));
+    return SV_OK;
+}
+
+extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out, float* d_best,
+                                  int32_t* d_best_state, void* stream) {
+    if (s == nullptr || seqs == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run_device: NULL");
+    sv_model* m = s->m;
+    if (s->level == 1) return sv_viterbi_device(m, seqs, d_out, d_best, d_best_state, stream);
+    if (seqs->device != m->device)
+        return sv_fail(SV_ERR_ARG, "sv_spec_run_device: sequences live on another device");
+    if (s->t_begin != 0 || s->t_end != s->ntuples)
+        return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SV_CUDA(cudaSetDevice(m->device));
+    const size_t n = m->n;
+    const uint64_t nseq = seqs->nseq;
+    if (s->v_capacity < nseq) {
+        for (int b = 0; b < 2; ++b) {
+            if (s->d_v[b]) cudaFree(s->d_v[b]);
+            s->d_v[b] = nullptr;
+            SV_CUDA(cudaMalloc(&s->d_v[b], nseq * n * sizeof(float)));
+        }
+        s->v_capacity = nseq;
+    }
+    RunSeqs rs{static_cast<int>(nseq), seqs->dev.sym, seqs->dev.sym_bytes, seqs->dev.off};
+    int launches = 0;
+    int cur = 0;
+    {
+        dim3 grid(static_cast<unsigned>((n + 255) / 256), static_cast<unsigned>(nseq));
+        spec_init_kernel<<<grid, 256, 0, st>>>(m->gen, rs, s->d_v[cur]);
+        ++launches;
+    }
+    const uint64_t max_chunks = (seqs->max_len - 1) / s->level;
+    const int rows_per_cta = 64;
+    for (uint64_t c = 0; c < max_chunks; ++c) {
+        dim3 grid(static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta),
+                  static_cast<unsigned>(nseq));
+        handler_gemv_kernel<<<grid, 256, n * sizeof(float), st>>>(
+            static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c,
+            s->d_table, s->table_first, s->d_v[cur], s->d_v[cur ^ 1], rows_per_cta);
+        cur ^= 1;
+        ++launches;
+    }
+    for (uint64_t tl = 0; tl + 1 < s->level; ++tl) {
+        tail_step_kernel<<<static_cast<unsigned>(nseq), 1024, n * sizeof(float), st>>>(
+            m->gen, static_cast<int>(s->level), rs, static_cast<int>(tl), s->d_v[cur], s->d_v[cur ^ 1]);
+        cur ^= 1;
+        ++launches;
+    }
+    if (d_out != nullptr)
+        SV_CUDA(cudaMemcpyAsync(d_out, s->d_v[cur], nseq * n * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (d_best != nullptr || d_best_state != nullptr) {
+        best_state_kernel<<<static_cast<unsigned>(nseq), 256, 0, st>>>(static_cast<int>(n), s->d_v[cur],
+                                                                      d_best, d_best_state);
+        ++launches;
+    }
+    SV_CUDA(cudaGetLastError());
+    m->last_launches = launches;
+    return SV_OK;
+}
+
+extern "C" int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets,
+                                 uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    if (s == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run_batch: NULL spec");
+    sv_model* m = s->m;
+    if (s->level == 1) return sv_viterbi_batch(m, symbols, offsets, nseq, out, best, best_state);
+    sv_seqs* seqs = nullptr;
+    int rc = sv_seqs_create(m, symbols, offsets, nseq, &seqs);
+    if (rc != SV_OK) return rc;
+    float *d_out = nullptr, *d_best = nullptr;
+    int32_t* d_arg = nullptr;
+    cudaError_t e = cudaSuccess;
+    if (out) e = cudaMalloc(&d_out, nseq * m->n * sizeof(float));
+    if (best && e == cudaSuccess) e = cudaMalloc(&d_best, nseq * sizeof(float));
+    if (best_state && e == cudaSuccess) e = cudaMalloc(&d_arg, nseq * sizeof(int32_t));
+    if (e != cudaSuccess) {
+        rc = sv_fail(SV_ERR_MEMORY, std::string("sv_spec_run_batch: ") + cudaGetErrorString(e));
+    } else {
+        rc = sv_spec_run_device(s, seqs, d_out, d_best, d_arg, m->stream);
+    }
+    if (rc == SV_OK) {
+        if (out) e = cudaMemcpyAsync(out, d_out, nseq * m->n * sizeof(float), cudaMemcpyDeviceToHost, m->stream);
+        if (best && e == cudaSuccess)
+            e = cudaMemcpyAsync(best, d_best, nseq * sizeof(float), cudaMemcpyDeviceToHost, m->stream);
+        if (best_state && e == cudaSuccess)
+            e = cudaMemcpyAsync(best_state, d_arg, nseq * sizeof(int32_t), cudaMemcpyDeviceToHost, m->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+        if (e != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, std::string("sv_spec_run_batch: ") + cudaGetErrorString(e));
+    }
+    if (d_out) cudaFree(d_out);
+    if (d_best) cudaFree(d_best);
+    if (d_arg) cudaFree(d_arg);
+    sv_seqs_destroy(seqs);
+    return rc;
+}
+
+extern "C" int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out) {
+    if (seq == nullptr || out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run: NULL");
+    const uint64_t offsets[2] = {0, len};
+    return sv_spec_run_batch(s, seq, offsets, 1, out, nullptr, nullptr);
+}

@@ -1,0 +1,78 @@
+"""Generates tests/golden/ from the reference tree (run in the build container only).
+
+  * packs the reference's input data (24 profile HMMs, 4 sequence sets, 4 tiny test cases)
+    into this repo's binary caches (.chmmb / .essb) -- weights are stored as the fp32
+    -log2 values this repo's reader produced, which tests/test_readers.py checks bit for bit
+    against the reference's own read_HMM when the reference tree is present;
+  * runs the REFERENCE's own GraphBLAS_impl / GraphBLAS_spec_impl (oracle/_ref, unmodified
+    sources on the GraphBLAS shim) and stores its outputs as golden vectors.
+
+/root/reference does not exist on the GPU box; everything the GPU tests need is written here.
+"""
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from spec_viterbi_b200 import api  # noqa: E402
+from oracle import pyoracle  # noqa: E402
+
+REF = Path("/root/reference")
+OUT = ROOT / "tests" / "golden"
+
+
+def main():
+    (OUT / "models").mkdir(parents=True, exist_ok=True)
+    (OUT / "seqs").mkdir(parents=True, exist_ok=True)
+    (OUT / "expected").mkdir(parents=True, exist_ok=True)
+    ref = pyoracle.Reference()
+
+    for chmm in sorted(REF.glob("chmm_files/*.chmm")):
+        api.pack_HMM_file(str(chmm), str(OUT / "models" / (chmm.stem + ".chmmb")))
+    for chmm in sorted(REF.glob("chmm_files/test_chmms/*.chmm")):
+        api.pack_HMM_file(str(chmm), str(OUT / "models" / (chmm.stem + ".chmmb")))
+    for ess in sorted(REF.glob("ess_files/*.ess")):
+        api.pack_ess_file(str(ess), str(OUT / "seqs" / (ess.stem + ".essb")))
+    for ess in sorted(REF.glob("ess_files/test_sequences/*.ess")):
+        api.pack_ess_file(str(ess), str(OUT / "seqs" / (ess.stem + ".essb")))
+
+    exp = {}
+    # the reference's four known-answer cases, plain and spec levels 1..3
+    for i in range(4):
+        hmm = api.read_HMM(str(OUT / "models" / f"{i}_test_chmm.chmmb"))
+        seq = api.read_emit_seq(str(OUT / "seqs" / f"{i}_test_seq.essb"))[0]
+        exp[f"tiny{i}_plain"] = ref.plain(hmm, seq)
+        for lvl in (1, 2, 3):
+            sp = ref.spec_create(hmm, lvl)
+            exp[f"tiny{i}_spec{lvl}"] = ref.spec_run(sp, seq)
+            ref.spec_destroy(sp)
+    # every shipped model x first sequence of emit_3_3500_20 (test_semantic_equality's inputs)
+    seqs = api.read_emit_seq(str(OUT / "seqs" / "emit_3_3500_20.essb"))
+    for chmm in sorted(p for p in (OUT / "models").glob("*.chmmb") if "test" not in p.stem):
+        hmm = api.read_HMM(str(chmm))
+        exp[f"{chmm.stem}_emit3_3500_seq0_plain"] = ref.plain(hmm, seqs[0])
+        print("plain", chmm.stem, flush=True)
+    # spec level 2 through the reference on the small models (dense handlers: N^2 each)
+    for name in ("100", "200"):
+        hmm = api.read_HMM(str(OUT / "models" / f"{name}.chmmb"))
+        sp = ref.spec_create(hmm, 2)
+        for k in range(3):
+            exp[f"{name}_emit3_3500_seq{k}_spec2"] = ref.spec_run(sp, seqs[k])
+        ref.spec_destroy(sp)
+        print("spec2", name, flush=True)
+    # ragged real sequences
+    cov = api.read_emit_seq(str(OUT / "seqs" / "covid-19.essb"))
+    hmm = api.read_HMM(str(OUT / "models" / "2405.chmmb"))
+    for k in (0, 4, 9):
+        exp[f"2405_covid_seq{k}_plain"] = ref.plain(hmm, cov[k])
+    hmm = api.read_HMM(str(OUT / "models" / "1200.chmmb"))
+    for k in range(3):
+        exp[f"1200_emit3_3500_seq{k}_plain"] = ref.plain(hmm, seqs[k])
+    np.savez_compressed(OUT / "expected" / "reference_outputs.npz", **exp)
+    print("wrote", len(exp), "golden vectors")
+
+
+if __name__ == "__main__":
+    main()
