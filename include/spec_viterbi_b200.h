@@ -112,6 +112,10 @@ int sv_viterbi(sv_model* m, const uint64_t* seq, uint64_t len, float* out);
  * lowest state index attaining it, -1 if all +inf) may be NULL. */
 int sv_viterbi_batch(sv_model* m, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
                      float* out, float* best, int32_t* best_state);
+/* Same with one byte per symbol (alphabet <= 256; the .essb cache layout): the symbols are
+ * copied to the device straight from the caller's buffer (pin it for full PCIe speed). */
+int sv_viterbi_batch_u8(sv_model* m, const uint8_t* symbols, const uint64_t* offsets, uint64_t nseq,
+                        float* out, float* best, int32_t* best_state);
 
 /* Device-resident variant: `seqs` from sv_seqs_create, d_* are device pointers on the
  * model's device (may be NULL), `stream` is a cudaStream_t (NULL = default stream).
@@ -150,6 +154,8 @@ int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out);
 int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out);
 int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
                       float* out, float* best, int32_t* best_state);
+int sv_spec_run_batch_u8(sv_spec* s, const uint8_t* symbols, const uint64_t* offsets, uint64_t nseq,
+                         float* out, float* best, int32_t* best_state);
 int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out, float* d_best,
                        int32_t* d_best_state, void* stream);
 

@@ -53,6 +53,7 @@ SIGNATURES = {
     "sv_seqs_total_symbols": (C.c_uint64, [vp]),
     "sv_viterbi": (C.c_int, [vp, u64p, C.c_uint64, f32p]),
     "sv_viterbi_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, f32p, f32p, i32p]),
+    "sv_viterbi_batch_u8": (C.c_int, [vp, u8p, u64p, C.c_uint64, f32p, f32p, i32p]),
     "sv_viterbi_device": (C.c_int, [vp, vp, vp, vp, vp, vp]),
     "sv_spec_create": (C.c_int, [vp, C.c_uint64, C.c_int, C.c_uint64, C.c_uint64, vp, vp,
                                  C.POINTER(vp)]),
@@ -63,6 +64,7 @@ SIGNATURES = {
     "sv_spec_get_handler": (C.c_int, [vp, C.c_uint64, f32p]),
     "sv_spec_run": (C.c_int, [vp, u64p, C.c_uint64, f32p]),
     "sv_spec_run_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, f32p, f32p, i32p]),
+    "sv_spec_run_batch_u8": (C.c_int, [vp, u8p, u64p, C.c_uint64, f32p, f32p, i32p]),
     "sv_spec_run_device": (C.c_int, [vp, vp, vp, vp, vp, vp]),
     "sv_io_hmm_open": (C.c_int, [C.c_char_p, C.POINTER(vp), u64p]),
     "sv_io_hmm_copy": (C.c_int, [vp, u64p, u64p, f32p, f32p, u64p, f32p]),

@@ -23,13 +23,22 @@ def _p(arr: np.ndarray, ctype):
     return arr.ctypes.data_as(C.POINTER(ctype))
 
 
+_libm = C.CDLL("libm.so.6")
+_libm.log2f.restype = C.c_float
+_libm.log2f.argtypes = [C.c_float]
+
+
 def to_modified_prob(p) -> np.ndarray:
-    """-log2(p) in fp32, +inf for p <= 0 (reference: HMM.h:51-57)."""
+    """-log2(p) in fp32, +inf for p <= 0 (reference: HMM.h:51-57).  Uses the C library's log2f,
+    exactly as the reference's `-1 * std::log2(float)` does (numpy's float32 log2 differs from
+    glibc's in the last bit for some inputs)."""
     p = np.asarray(p, dtype=np.float32)
-    out = np.full(p.shape, np.inf, dtype=np.float32)
-    pos = p > 0
-    out[pos] = -np.log2(p[pos], dtype=np.float32)
-    return out
+    flat = p.reshape(-1)
+    out = np.full(flat.shape, np.inf, dtype=np.float32)
+    log2f = _libm.log2f
+    for k in np.flatnonzero(flat > 0):
+        out[k] = np.float32(-1.0) * np.float32(log2f(float(flat[k])))
+    return out.reshape(p.shape)
 
 
 def almost_equal(x, y) -> bool:
@@ -183,13 +192,24 @@ class Model:
         L.check(self._lib.sv_viterbi(self._h, _p(s, C.c_uint64), s.size, _p(out, C.c_float)))
         return out
 
-    def viterbi_batch(self, symbols: np.ndarray, offsets: np.ndarray, want_vectors=True, want_best=True):
+    def viterbi_batch(self, symbols: np.ndarray, offsets: np.ndarray, want_vectors=True, want_best=True,
+                      out=None, best=None, arg=None):
+        """symbols: uint64 (reference layout) or uint8 (packed); out/best/arg may be caller-owned
+        (e.g. pinned) numpy buffers."""
         nseq = offsets.size - 1
-        out = np.empty((nseq, self.hmm.states_num), np.float32) if want_vectors else None
-        best = np.empty(nseq, np.float32) if want_best else None
-        arg = np.empty(nseq, np.int32) if want_best else None
-        L.check(self._lib.sv_viterbi_batch(
-            self._h, _p(symbols, C.c_uint64), _p(offsets, C.c_uint64), nseq,
+        if symbols.dtype != np.uint8:
+            symbols = np.ascontiguousarray(symbols, np.uint64)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        if out is None and want_vectors:
+            out = np.empty((nseq, self.hmm.states_num), np.float32)
+        if best is None and want_best:
+            best = np.empty(nseq, np.float32)
+        if arg is None and want_best:
+            arg = np.empty(nseq, np.int32)
+        fn, st = (self._lib.sv_viterbi_batch_u8, C.c_uint8) if symbols.dtype == np.uint8 else \
+                 (self._lib.sv_viterbi_batch, C.c_uint64)
+        L.check(fn(
+            self._h, _p(symbols, st), _p(offsets, C.c_uint64), nseq,
             _p(out, C.c_float) if out is not None else None,
             _p(best, C.c_float) if best is not None else None,
             _p(arg, C.c_int32) if arg is not None else None))
@@ -283,11 +303,16 @@ class Spec:
     def run_batch(self, symbols: np.ndarray, offsets: np.ndarray, want_vectors=True, want_best=True):
         nseq = offsets.size - 1
         n = self.model.hmm.states_num
+        if symbols.dtype != np.uint8:
+            symbols = np.ascontiguousarray(symbols, np.uint64)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
         out = np.empty((nseq, n), np.float32) if want_vectors else None
         best = np.empty(nseq, np.float32) if want_best else None
         arg = np.empty(nseq, np.int32) if want_best else None
-        L.check(self._lib.sv_spec_run_batch(
-            self._h, _p(symbols, C.c_uint64), _p(offsets, C.c_uint64), nseq,
+        fn, st = (self._lib.sv_spec_run_batch_u8, C.c_uint8) if symbols.dtype == np.uint8 else \
+                 (self._lib.sv_spec_run_batch, C.c_uint64)
+        L.check(fn(
+            self._h, _p(symbols, st), _p(offsets, C.c_uint64), nseq,
             _p(out, C.c_float) if out is not None else None,
             _p(best, C.c_float) if best is not None else None,
             _p(arg, C.c_int32) if arg is not None else None))

@@ -252,6 +252,10 @@ extern "C" void sv_model_destroy(sv_model* m) {
     if (m->d_blob) cudaFree(m->d_blob);
     if (m->d_es_blob) cudaFree(m->d_es_blob);
     if (m->d_counter) cudaFree(m->d_counter);
+    if (m->ws.seqs) sv_seqs_destroy(m->ws.seqs);
+    if (m->ws.d_out) cudaFree(m->ws.d_out);
+    if (m->ws.d_best) cudaFree(m->ws.d_best);
+    if (m->ws.d_arg) cudaFree(m->ws.d_arg);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -294,86 +298,153 @@ extern "C" int sv_model_last_launches(const sv_model* m) { return m ? m->last_la
 // ----------------------------------------------------------------- sequences ----
 namespace {
 
+int ensure_pinned(sv_seqs* s, size_t bytes) {
+    if (s->h_cap >= bytes) return SV_OK;
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    s->h_pinned = nullptr;
+    s->h_cap = 0;
+    const size_t want = bytes + bytes / 4 + 4096;
+    if (cudaMallocHost(&s->h_pinned, want) != cudaSuccess) {
+        cudaGetLastError();
+        return sv_fail(SV_ERR_MEMORY, "sequence upload: pinned staging allocation failed");
+    }
+    s->h_cap = want;
+    return SV_OK;
+}
+
+int ensure_device(sv_seqs* s, size_t bytes) {
+    if (s->d_cap >= bytes) return SV_OK;
+    if (s->d_blob) cudaFree(s->d_blob);
+    s->d_blob = nullptr;
+    s->d_cap = 0;
+    const size_t want = bytes + bytes / 4 + 4096;
+    if (cudaMalloc(&s->d_blob, want) != cudaSuccess) {
+        cudaGetLastError();
+        return sv_fail(SV_ERR_MEMORY, "sequence upload: device allocation failed");
+    }
+    s->d_cap = want;
+    return SV_OK;
+}
+
+// (Re)fills a sequence batch: validates, packs symbols to u8/u16, builds the longest-first
+// work order and uploads on `st` (asynchronous; the pinned staging buffer is owned by `s`, so
+// the caller must not refill `s` before the stream has consumed it).  u8 input that needs no
+// repacking is copied straight from the caller's buffer.
 template <typename SrcT>
-int seqs_create_impl(const sv_model* m, const SrcT* symbols, const uint64_t* offsets,
-                     uint64_t nseq, sv_seqs** out) {
-    if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_seqs_create: out is NULL");
-    *out = nullptr;
-    if (m == nullptr || offsets == nullptr) return sv_fail(SV_ERR_ARG, "sv_seqs_create: NULL");
-    if (nseq == 0 || nseq > 0x7fffffffu) return sv_fail(SV_ERR_ARG, "sv_seqs_create: bad nseq");
-    const uint64_t total = offsets[nseq];
-    if (total > 0 && symbols == nullptr) return sv_fail(SV_ERR_ARG, "sv_seqs_create: NULL symbols");
-    uint64_t max_len = 0;
-    for (uint64_t s = 0; s < nseq; ++s) {
-        if (offsets[s + 1] <= offsets[s])
-            return sv_fail(SV_ERR_ARG, "sv_seqs_create: empty sequence (the reference requires "
+int seqs_assign(sv_seqs* s, const sv_model* m, const SrcT* symbols, const uint64_t* offsets,
+                uint64_t nseq, cudaStream_t st) {
+    if (m == nullptr || offsets == nullptr) return sv_fail(SV_ERR_ARG, "sequence upload: NULL");
+    if (nseq == 0 || nseq > 0x7fffffffu) return sv_fail(SV_ERR_ARG, "sequence upload: bad nseq");
+    const uint64_t first = offsets[0];
+    const uint64_t total = offsets[nseq] - first;
+    if (total > 0 && symbols == nullptr) return sv_fail(SV_ERR_ARG, "sequence upload: NULL symbols");
+    uint64_t max_len = 0, min_len = ~0ull;
+    for (uint64_t q = 0; q < nseq; ++q) {
+        if (offsets[q + 1] <= offsets[q])
+            return sv_fail(SV_ERR_ARG, "sequence upload: empty sequence (the reference requires "
                                        "at least one symbol, GraphBLAS_impl.cpp:59)");
-        max_len = std::max(max_len, offsets[s + 1] - offsets[s]);
+        const uint64_t len = offsets[q + 1] - offsets[q];
+        max_len = std::max(max_len, len);
+        min_len = std::min(min_len, len);
     }
     const int sym_bytes = m->emits <= 256 ? 1 : 2;
-    std::vector<uint32_t> order(nseq);
-    std::iota(order.begin(), order.end(), 0u);
-    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
-        return (offsets[a + 1] - offsets[a]) > (offsets[b + 1] - offsets[b]);
-    });
-    size_t bytes = 0;
-    const size_t o_sym = blob_reserve<uint8_t>(&bytes, total * sym_bytes + 16);
-    const size_t o_off = blob_reserve<uint64_t>(&bytes, nseq + 1);
-    const size_t o_ord = blob_reserve<uint32_t>(&bytes, nseq);
-    bytes += 256;
-    unsigned char* host = nullptr;
-    if (cudaMallocHost(&host, bytes) != cudaSuccess) {
-        cudaGetLastError();
-        return sv_fail(SV_ERR_MEMORY, "sv_seqs_create: pinned staging allocation failed");
-    }
-    bool bad = false;
-    if (sym_bytes == 1) {
-        uint8_t* dst = host + o_sym;
+    const bool direct = sizeof(SrcT) == 1 && sym_bytes == 1; // no repacking needed
+    SV_CUDA(cudaSetDevice(m->device));
+
+    size_t dbytes = 0;
+    const size_t o_sym = blob_reserve<uint8_t>(&dbytes, total * sym_bytes + 16);
+    const size_t o_off = blob_reserve<uint64_t>(&dbytes, nseq + 1);
+    const size_t o_ord = blob_reserve<uint32_t>(&dbytes, nseq);
+    dbytes += 256;
+    // host staging: [offsets][order][symbols unless direct]
+    size_t hbytes = 0;
+    const size_t h_off = blob_reserve<uint64_t>(&hbytes, nseq + 1);
+    const size_t h_ord = blob_reserve<uint32_t>(&hbytes, nseq);
+    const size_t h_sym = blob_reserve<uint8_t>(&hbytes, direct ? 16 : total * sym_bytes + 16);
+    int rc = ensure_pinned(s, hbytes);
+    if (rc != SV_OK) return rc;
+    if ((rc = ensure_device(s, dbytes)) != SV_OK) return rc;
+    unsigned char* host = s->h_pinned;
+
+    // validation (+ packing)
+    const SrcT* src = symbols + first;
+    unsigned long long worst = 0;
+    if (direct) {
+        unsigned mx = 0;
+        for (uint64_t k = 0; k < total; ++k) mx = std::max<unsigned>(mx, static_cast<unsigned>(src[k]));
+        worst = mx;
+    } else if (sym_bytes == 1) {
+        uint8_t* dst = host + h_sym;
         for (uint64_t k = 0; k < total; ++k) {
-            const uint64_t v = symbols[k];
-            bad |= v >= m->emits;
+            const unsigned long long v = src[k];
+            worst = std::max(worst, v);
             dst[k] = static_cast<uint8_t>(v);
         }
+        std::memset(dst + total, 0, 16);
     } else {
-        uint16_t* dst = reinterpret_cast<uint16_t*>(host + o_sym);
+        uint16_t* dst = reinterpret_cast<uint16_t*>(host + h_sym);
         for (uint64_t k = 0; k < total; ++k) {
-            const uint64_t v = symbols[k];
-            bad |= v >= m->emits;
+            const unsigned long long v = src[k];
+            worst = std::max(worst, v);
             dst[k] = static_cast<uint16_t>(v);
         }
+        std::memset(dst + total, 0, 16);
     }
-    if (bad) {
-        cudaFreeHost(host);
-        return sv_fail(SV_ERR_ARG, "sv_seqs_create: symbol >= emit_num");
-    }
-    std::memset(host + o_sym + total * sym_bytes, 0, 16);
-    std::memcpy(host + o_off, offsets, (nseq + 1) * sizeof(uint64_t));
-    std::memcpy(host + o_ord, order.data(), nseq * sizeof(uint32_t));
+    if (total > 0 && worst >= m->emits) return sv_fail(SV_ERR_ARG, "sequence upload: symbol >= emit_num");
 
-    sv_seqs* s = new (std::nothrow) sv_seqs;
-    if (s == nullptr) {
-        cudaFreeHost(host);
-        return sv_fail(SV_ERR_MEMORY, "sv_seqs_create: out of host memory");
+    uint64_t* hoff = reinterpret_cast<uint64_t*>(host + h_off);
+    for (uint64_t q = 0; q <= nseq; ++q) hoff[q] = offsets[q] - first;
+    uint32_t* hord = reinterpret_cast<uint32_t*>(host + h_ord);
+    std::iota(hord, hord + nseq, 0u);
+    if (min_len != max_len) {
+        std::stable_sort(hord, hord + nseq, [&](uint32_t a, uint32_t b) {
+            return (offsets[a + 1] - offsets[a]) > (offsets[b + 1] - offsets[b]);
+        });
     }
+
+    auto* base = static_cast<unsigned char*>(s->d_blob);
+    if (direct) {
+        SV_CUDA(cudaMemcpyAsync(base + o_sym, src, total, cudaMemcpyHostToDevice, st));
+        SV_CUDA(cudaMemsetAsync(base + o_sym + total, 0, 16, st));
+    } else {
+        SV_CUDA(cudaMemcpyAsync(base + o_sym, host + h_sym, total * sym_bytes + 16,
+                                cudaMemcpyHostToDevice, st));
+    }
+    SV_CUDA(cudaMemcpyAsync(base + o_off, hoff, (nseq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    SV_CUDA(cudaMemcpyAsync(base + o_ord, hord, nseq * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     s->device = m->device;
     s->nseq = nseq;
     s->total = total;
     s->max_len = max_len;
-    cudaError_t e = cudaSetDevice(m->device);
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_blob, bytes);
-    if (e == cudaSuccess) e = cudaMemcpy(s->d_blob, host, bytes, cudaMemcpyHostToDevice);
-    cudaFreeHost(host);
-    if (e != cudaSuccess) {
-        if (s->d_blob) cudaFree(s->d_blob);
-        delete s;
-        return sv_fail(SV_ERR_CUDA, std::string("sv_seqs_create: ") + cudaGetErrorString(e));
-    }
-    auto* base = static_cast<unsigned char*>(s->d_blob);
+    s->h2d_bytes = total * sym_bytes + (nseq + 1) * sizeof(uint64_t) + nseq * sizeof(uint32_t);
     s->dev.nseq = static_cast<int>(nseq);
     s->dev.sym_bytes = sym_bytes;
     s->dev.sym = base + o_sym;
     s->dev.off = reinterpret_cast<const uint64_t*>(base + o_off);
     s->dev.order = reinterpret_cast<const uint32_t*>(base + o_ord);
+    return SV_OK;
+}
+
+template <typename SrcT>
+int seqs_create_impl(const sv_model* m, const SrcT* symbols, const uint64_t* offsets,
+                     uint64_t nseq, sv_seqs** out) {
+    if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_seqs_create: out is NULL");
+    *out = nullptr;
+    if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_seqs_create: NULL model");
+    sv_seqs* s = new (std::nothrow) sv_seqs;
+    if (s == nullptr) return sv_fail(SV_ERR_MEMORY, "sv_seqs_create: out of host memory");
+    s->device = m->device;
+    int rc = seqs_assign(s, m, symbols, offsets, nseq, nullptr);
+    if (rc == SV_OK && cudaStreamSynchronize(nullptr) != cudaSuccess)
+        rc = sv_fail(SV_ERR_CUDA, "sv_seqs_create: upload failed");
+    if (rc != SV_OK) {
+        sv_seqs_destroy(s);
+        return rc;
+    }
+    // the staging buffer is only needed for refills
+    cudaFreeHost(s->h_pinned);
+    s->h_pinned = nullptr;
+    s->h_cap = 0;
     *out = s;
     return SV_OK;
 }
@@ -392,10 +463,70 @@ extern "C" void sv_seqs_destroy(sv_seqs* s) {
     if (s == nullptr) return;
     cudaSetDevice(s->device);
     if (s->d_blob) cudaFree(s->d_blob);
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
     delete s;
 }
 extern "C" uint64_t sv_seqs_count(const sv_seqs* s) { return s ? s->nseq : 0; }
 extern "C" uint64_t sv_seqs_total_symbols(const sv_seqs* s) { return s ? s->total : 0; }
+
+// Host-buffer workspace of a model: sequence batch + result buffers, grown on demand and
+// reused by every sv_viterbi / sv_viterbi_batch* / sv_spec_run* call on that model.
+int sv_ws_results(sv_model* m, uint64_t nseq, bool want_out, float** d_out, float** d_best,
+                  int32_t** d_arg) {
+    SvWorkspace& w = m->ws;
+    if (want_out && w.out_cap < nseq * m->n) {
+        if (w.d_out) cudaFree(w.d_out);
+        w.d_out = nullptr;
+        w.out_cap = 0;
+        if (cudaMalloc(&w.d_out, nseq * m->n * sizeof(float)) != cudaSuccess) {
+            cudaGetLastError();
+            return sv_fail(SV_ERR_MEMORY, "result buffer does not fit device memory");
+        }
+        w.out_cap = nseq * m->n;
+    }
+    if (w.best_cap < nseq) {
+        if (w.d_best) cudaFree(w.d_best);
+        if (w.d_arg) cudaFree(w.d_arg);
+        w.d_best = nullptr;
+        w.d_arg = nullptr;
+        w.best_cap = 0;
+        if (cudaMalloc(&w.d_best, nseq * sizeof(float)) != cudaSuccess ||
+            cudaMalloc(&w.d_arg, nseq * sizeof(int32_t)) != cudaSuccess) {
+            cudaGetLastError();
+            return sv_fail(SV_ERR_MEMORY, "result buffer does not fit device memory");
+        }
+        w.best_cap = nseq;
+    }
+    *d_out = want_out ? w.d_out : nullptr;
+    *d_best = w.d_best;
+    *d_arg = w.d_arg;
+    return SV_OK;
+}
+
+template <typename SrcT>
+int sv_ws_upload(sv_model* m, const SrcT* symbols, const uint64_t* offsets, uint64_t nseq) {
+    if (m->ws.seqs == nullptr) {
+        m->ws.seqs = new (std::nothrow) sv_seqs;
+        if (m->ws.seqs == nullptr) return sv_fail(SV_ERR_MEMORY, "out of host memory");
+        m->ws.seqs->device = m->device;
+    }
+    return seqs_assign(m->ws.seqs, m, symbols, offsets, nseq, m->stream);
+}
+template int sv_ws_upload<uint64_t>(sv_model*, const uint64_t*, const uint64_t*, uint64_t);
+template int sv_ws_upload<uint8_t>(sv_model*, const uint8_t*, const uint64_t*, uint64_t);
+
+int sv_ws_download(sv_model* m, uint64_t nseq, const float* d_out, const float* d_best,
+                   const int32_t* d_arg, float* out, float* best, int32_t* best_state) {
+    cudaError_t e = cudaSuccess;
+    if (out) e = cudaMemcpyAsync(out, d_out, nseq * m->n * sizeof(float), cudaMemcpyDeviceToHost, m->stream);
+    if (best && e == cudaSuccess)
+        e = cudaMemcpyAsync(best, d_best, nseq * sizeof(float), cudaMemcpyDeviceToHost, m->stream);
+    if (best_state && e == cudaSuccess)
+        e = cudaMemcpyAsync(best_state, d_arg, nseq * sizeof(int32_t), cudaMemcpyDeviceToHost, m->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+    if (e != cudaSuccess) return sv_fail(SV_ERR_CUDA, std::string("result download: ") + cudaGetErrorString(e));
+    return SV_OK;
+}
 
 // ---------------------------------------------------------------- plain path ----
 extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out, float* d_best,
@@ -423,45 +554,31 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
     return SV_OK;
 }
 
+namespace {
+template <typename SrcT>
+int viterbi_batch_impl(sv_model* m, const SrcT* symbols, const uint64_t* offsets, uint64_t nseq,
+                       float* out, float* best, int32_t* best_state) {
+    if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_viterbi_batch: NULL model");
+    int rc = sv_ws_upload(m, symbols, offsets, nseq);
+    if (rc != SV_OK) return rc;
+    float *d_out, *d_best;
+    int32_t* d_arg;
+    if ((rc = sv_ws_results(m, nseq, out != nullptr, &d_out, &d_best, &d_arg)) != SV_OK) return rc;
+    rc = sv_viterbi_device(m, m->ws.seqs, d_out, best ? d_best : nullptr,
+                           best_state ? d_arg : nullptr, m->stream);
+    if (rc != SV_OK) return rc;
+    return sv_ws_download(m, nseq, d_out, d_best, d_arg, out, best, best_state);
+}
+} // namespace
+
 extern "C" int sv_viterbi_batch(sv_model* m, const uint64_t* symbols, const uint64_t* offsets,
                                 uint64_t nseq, float* out, float* best, int32_t* best_state) {
-    if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_viterbi_batch: NULL model");
-    sv_seqs* seqs = nullptr;
-    int rc = sv_seqs_create(m, symbols, offsets, nseq, &seqs);
-    if (rc != SV_OK) return rc;
-    float *d_out = nullptr, *d_best = nullptr;
-    int32_t* d_arg = nullptr;
-    auto cleanup = [&]() {
-        if (d_out) cudaFree(d_out);
-        if (d_best) cudaFree(d_best);
-        if (d_arg) cudaFree(d_arg);
-        sv_seqs_destroy(seqs);
-    };
-    cudaError_t e = cudaSuccess;
-    if (out && e == cudaSuccess) e = cudaMalloc(&d_out, nseq * m->n * sizeof(float));
-    if (best && e == cudaSuccess) e = cudaMalloc(&d_best, nseq * sizeof(float));
-    if (best_state && e == cudaSuccess) e = cudaMalloc(&d_arg, nseq * sizeof(int32_t));
-    if (e != cudaSuccess) {
-        cleanup();
-        return sv_fail(SV_ERR_MEMORY, std::string("sv_viterbi_batch: ") + cudaGetErrorString(e));
-    }
-    rc = sv_viterbi_device(m, seqs, d_out, d_best, d_arg, m->stream);
-    if (rc == SV_OK) {
-        if (out)
-            e = cudaMemcpyAsync(out, d_out, nseq * m->n * sizeof(float), cudaMemcpyDeviceToHost,
-                                m->stream);
-        if (best && e == cudaSuccess)
-            e = cudaMemcpyAsync(best, d_best, nseq * sizeof(float), cudaMemcpyDeviceToHost,
-                                m->stream);
-        if (best_state && e == cudaSuccess)
-            e = cudaMemcpyAsync(best_state, d_arg, nseq * sizeof(int32_t), cudaMemcpyDeviceToHost,
-                                m->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
-        if (e != cudaSuccess)
-            rc = sv_fail(SV_ERR_CUDA, std::string("sv_viterbi_batch: ") + cudaGetErrorString(e));
-    }
-    cleanup();
-    return rc;
+    return viterbi_batch_impl(m, symbols, offsets, nseq, out, best, best_state);
+}
+
+extern "C" int sv_viterbi_batch_u8(sv_model* m, const uint8_t* symbols, const uint64_t* offsets,
+                                   uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    return viterbi_batch_impl(m, symbols, offsets, nseq, out, best, best_state);
 }
 
 extern "C" int sv_viterbi(sv_model* m, const uint64_t* seq, uint64_t len, float* out) {

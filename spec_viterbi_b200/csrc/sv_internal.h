@@ -113,6 +113,17 @@ struct SvHostCsr {
     std::vector<float> w;
 };
 
+struct sv_seqs;
+// Reusable buffers behind the host-pointer entry points (sv_viterbi*, sv_spec_run*).
+struct SvWorkspace {
+    sv_seqs* seqs = nullptr;
+    float* d_out = nullptr;
+    size_t out_cap = 0; // floats
+    float* d_best = nullptr;
+    int32_t* d_arg = nullptr;
+    size_t best_cap = 0; // sequences
+};
+
 struct sv_model {
     int device = 0;
     int sm_count = 0;
@@ -133,14 +144,27 @@ struct sv_model {
     int last_launches = 0;
     // scratch for host-buffer entry points
     cudaStream_t stream = nullptr;
+    SvWorkspace ws;
 };
 
 struct sv_seqs {
     int device = 0;
     uint64_t nseq = 0, total = 0, max_len = 0;
+    uint64_t h2d_bytes = 0; // bytes the last (re)fill copied to the device
     SvSeqsDev dev;
     void* d_blob = nullptr;
+    size_t d_cap = 0;
+    unsigned char* h_pinned = nullptr; // staging for offsets / order / repacked symbols
+    size_t h_cap = 0;
 };
+
+// host-buffer workspace helpers (sv_api.cu)
+template <typename SrcT>
+int sv_ws_upload(sv_model* m, const SrcT* symbols, const uint64_t* offsets, uint64_t nseq);
+int sv_ws_results(sv_model* m, uint64_t nseq, bool want_out, float** d_out, float** d_best,
+                  int32_t** d_arg);
+int sv_ws_download(sv_model* m, uint64_t nseq, const float* d_out, const float* d_best,
+                   const int32_t* d_arg, float* out, float* best, int32_t* best_state);
 
 // K0: build the edge-stationary schedule (sv_es_plan.cpp); plan.valid=false if no variant fits.
 void sv_es_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,

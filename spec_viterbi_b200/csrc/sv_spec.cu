@@ -553,39 +553,32 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     return SV_OK;
 }
 
-extern "C" int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets,
-                                 uint64_t nseq, float* out, float* best, int32_t* best_state) {
+namespace {
+template <typename SrcT>
+int spec_run_batch_impl(sv_spec* s, const SrcT* symbols, const uint64_t* offsets, uint64_t nseq,
+                        float* out, float* best, int32_t* best_state) {
     if (s == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run_batch: NULL spec");
     sv_model* m = s->m;
-    if (s->level == 1) return sv_viterbi_batch(m, symbols, offsets, nseq, out, best, best_state);
-    sv_seqs* seqs = nullptr;
-    int rc = sv_seqs_create(m, symbols, offsets, nseq, &seqs);
+    int rc = sv_ws_upload(m, symbols, offsets, nseq);
     if (rc != SV_OK) return rc;
-    float *d_out = nullptr, *d_best = nullptr;
-    int32_t* d_arg = nullptr;
-    cudaError_t e = cudaSuccess;
-    if (out) e = cudaMalloc(&d_out, nseq * m->n * sizeof(float));
-    if (best && e == cudaSuccess) e = cudaMalloc(&d_best, nseq * sizeof(float));
-    if (best_state && e == cudaSuccess) e = cudaMalloc(&d_arg, nseq * sizeof(int32_t));
-    if (e != cudaSuccess) {
-        rc = sv_fail(SV_ERR_MEMORY, std::string("sv_spec_run_batch: ") + cudaGetErrorString(e));
-    } else {
-        rc = sv_spec_run_device(s, seqs, d_out, d_best, d_arg, m->stream);
-    }
-    if (rc == SV_OK) {
-        if (out) e = cudaMemcpyAsync(out, d_out, nseq * m->n * sizeof(float), cudaMemcpyDeviceToHost, m->stream);
-        if (best && e == cudaSuccess)
-            e = cudaMemcpyAsync(best, d_best, nseq * sizeof(float), cudaMemcpyDeviceToHost, m->stream);
-        if (best_state && e == cudaSuccess)
-            e = cudaMemcpyAsync(best_state, d_arg, nseq * sizeof(int32_t), cudaMemcpyDeviceToHost, m->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
-        if (e != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, std::string("sv_spec_run_batch: ") + cudaGetErrorString(e));
-    }
-    if (d_out) cudaFree(d_out);
-    if (d_best) cudaFree(d_best);
-    if (d_arg) cudaFree(d_arg);
-    sv_seqs_destroy(seqs);
-    return rc;
+    float *d_out, *d_best;
+    int32_t* d_arg;
+    if ((rc = sv_ws_results(m, nseq, out != nullptr, &d_out, &d_best, &d_arg)) != SV_OK) return rc;
+    rc = sv_spec_run_device(s, m->ws.seqs, d_out, best ? d_best : nullptr,
+                            best_state ? d_arg : nullptr, m->stream);
+    if (rc != SV_OK) return rc;
+    return sv_ws_download(m, nseq, d_out, d_best, d_arg, out, best, best_state);
+}
+} // namespace
+
+extern "C" int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets,
+                                 uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    return spec_run_batch_impl(s, symbols, offsets, nseq, out, best, best_state);
+}
+
+extern "C" int sv_spec_run_batch_u8(sv_spec* s, const uint8_t* symbols, const uint64_t* offsets,
+                                    uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    return spec_run_batch_impl(s, symbols, offsets, nseq, out, best, best_state);
 }
 
 extern "C" int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out) {

@@ -1,0 +1,89 @@
+"""GPU parity, specialised path: handler precompute (K3 dense (min,+) GEMM, K3' sparse-LHS) and
+the level-L run (K4), bit-exact against the same-level oracle.  Reference:
+GraphBLAS_spec_impl.cpp:15-36,50-97,103-182; tests/test_helper.h:59-73 (levels 1..3)."""
+import numpy as np
+import pytest
+
+from conftest import same_bits
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("i", range(4))
+@pytest.mark.parametrize("level", [1, 2, 3])
+def test_reference_known_answers(i, level, api, load_model, load_seqs, golden):
+    impl = api.B200_spec_impl(level)
+    impl.spec_with(load_model(f"{i}_test_chmm"))
+    v = impl.run_Viterbi_spec(load_seqs(f"{i}_test_seq")[0])
+    assert impl.get_level() == level
+    assert same_bits(v, golden[f"tiny{i}_spec{level}"])
+
+
+@pytest.mark.parametrize("method", ["sparse", "dense"])
+@pytest.mark.parametrize("name", ["100", "200"])
+def test_level2_reference_fixture(name, method, api, load_model, load_seqs, golden):
+    from spec_viterbi_b200 import _lib
+    impl = api.B200_spec_impl(2, method=_lib.SPEC_DENSE_GEMM if method == "dense" else _lib.SPEC_SPARSE_LHS)
+    impl.spec_with(load_model(name))
+    out = impl.run_Viterbi_spec_batch(load_seqs("emit_3_3500_20"))
+    for k in range(3):
+        assert same_bits(out[k], golden[f"{name}_emit3_3500_seq{k}_spec2"])
+
+
+@pytest.mark.parametrize("name", ["100", "300"])
+def test_handlers_bit_exact(name, api, oracle, load_model):
+    """Every compared pair handler equals the oracle's M_b (x) M_a, for both precompute kernels."""
+    from spec_viterbi_b200 import _lib
+    hmm = load_model(name)
+    m = api.Model(hmm)
+    osp = oracle.spec(hmm, 2)
+    sparse = api.Spec(m, 2, _lib.SPEC_SPARSE_LHS)
+    dense = api.Spec(m, 2, _lib.SPEC_DENSE_GEMM)
+    for t in (0, 1, 19, 20, 57, 211, 399):
+        exp = osp.handler(t)
+        assert same_bits(sparse.handler(t), exp), t
+        assert same_bits(dense.handler(t), exp), t
+
+
+def test_random_model_levels(api, oracle):
+    from spec_viterbi_b200 import generators, _lib
+    hmm = generators.random_hmm(states_num=130, seed=9)
+    rng = np.random.default_rng(1)
+    seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 50, 301)]
+    for level, method in ((1, _lib.SPEC_AUTO), (2, _lib.SPEC_SPARSE_LHS), (2, _lib.SPEC_DENSE_GEMM)):
+        impl = api.B200_spec_impl(level, method=method)
+        impl.spec_with(hmm)
+        out = impl.run_Viterbi_spec_batch(seqs)
+        osp = oracle.spec(hmm, level)
+        for k, s in enumerate(seqs):
+            assert same_bits(out[k], osp.run(s)), (level, k)
+
+
+def test_level3_small_alphabet(api, oracle):
+    rng = np.random.default_rng(3)
+    n, e = 40, 4
+    src = rng.integers(0, n, 160).astype(np.uint64)
+    dst = rng.integers(0, n, 160).astype(np.uint64)
+    hmm = api.HMM(n, e, 160, src, dst, rng.uniform(0.1, 5, 160).astype(np.float32),
+                  rng.uniform(0.1, 5, (e, n)).astype(np.float32), 2, np.array([0, 5], np.uint64),
+                  np.array([1.0, 2.0], np.float32))
+    impl = api.B200_spec_impl(3)
+    impl.spec_with(hmm)
+    osp = oracle.spec(hmm, 3)
+    for L in (1, 2, 3, 4, 5, 6, 7, 8, 100):
+        s = rng.integers(0, e, L).astype(np.uint64)
+        assert same_bits(impl.run_Viterbi_spec(s), osp.run(s)), L
+
+
+def test_spec_vs_plain_cross_path(api, load_model, load_seqs):
+    """Across paths the reference's own criterion holds (abs <= 1.0, HMM.h:43-49); the fp32
+    re-association gap is reported, argmin must match."""
+    hmm = load_model("300")
+    seqs = load_seqs("emit_3_3500_20")
+    plain = api.B200_impl().run_Viterbi_batch(hmm, seqs)
+    impl = api.B200_spec_impl(2)
+    impl.spec_with(hmm)
+    spec = impl.run_Viterbi_spec_batch(seqs)
+    assert np.all(np.abs(plain - spec) <= 1.0)
+    assert np.max(np.abs(plain - spec) / plain) < 5e-5
+    assert np.array_equal(plain.argmin(1), spec.argmin(1))
