@@ -181,6 +181,10 @@ void sv_io_ess_close(sv_ess_file* f);
  * mix: 0 = FADD, 1 = FMNMX (2-input min), 2 = FMNMX3 (3-input min), 3 = 2 FADD + 1 FMNMX3,
  *      4 = 4 FADD + 1 FMNMX3 (the step's inner loop), 5 = LDS.32 conflict-free + 2 FADD + FMNMX */
 int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_per_s, double* sm_clock_mhz);
+/* Tensor-memory probe: fills all 512 TMEM columns of every SM through tcgen05.st, reads them
+ * back with run-time (warp-uniform) column addresses -- the access pattern of the emission
+ * lookup in the lockstep step kernel -- and reports mismatches and the tcgen05.ld read rate. */
+int sv_probe_tmem(int device, int iters, unsigned* errors, double* bytes_per_clk_per_sm);
 
 #ifdef __cplusplus
 }

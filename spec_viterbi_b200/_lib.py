@@ -74,6 +74,7 @@ SIGNATURES = {
     "sv_io_ess_copy": (C.c_int, [vp, u64p, u64p]),
     "sv_io_ess_write_packed": (C.c_int, [vp, C.c_char_p]),
     "sv_io_ess_close": (None, [vp]),
+    "sv_probe_tmem": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]),
     "sv_probe_fp32": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
                                 C.POINTER(C.c_double)]),
 }

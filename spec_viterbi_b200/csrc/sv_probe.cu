@@ -129,3 +129,103 @@ extern "C" int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_
     if (sm_clock_mhz != nullptr) *sm_clock_mhz = clk[1] ? double(clk[0]) / double(clk[1]) * 1e3 : 0;
     return SV_OK;
 }
+
+// ------------------------------------------------------------------ TMEM probe ----
+// Checks that tensor memory can serve as a per-SM lookup table for the emission scores
+// (tcgen05.alloc / st / ld with a warp-uniform, run-time column) and measures the read rate.
+namespace {
+
+__device__ __forceinline__ void tmem_alloc_cols(uint32_t* smem_slot, uint32_t ncols) {
+    const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(smem_slot));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(512, 1)
+sv_probe_tmem_kernel(int iters, unsigned* errors, unsigned long long* clk, float* sink) {
+    __shared__ uint32_t s_taddr;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (warp == 0) tmem_alloc_cols(&s_taddr, 512);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = s_taddr;
+    const uint32_t quad = static_cast<uint32_t>(warp & 3) * 32u;   // TMEM lanes this warp may touch
+    const uint32_t grp = static_cast<uint32_t>(warp >> 2);          // 4 warps share a quadrant
+    const uint32_t my = tbase + (quad << 16) + grp * 128u;          // 128 columns per warp
+    // fill: value encodes (tid, column)
+    for (uint32_t c = 0; c < 128; ++c) {
+        const uint32_t v = (static_cast<uint32_t>(tid) << 8) | c;
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(my + c), "r"(v) : "memory");
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    __syncthreads();
+    // check with run-time columns, x1 and x4 forms
+    unsigned bad = 0;
+    for (uint32_t c = 0; c < 128; ++c) {
+        uint32_t r;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(my + c) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        bad += r != ((static_cast<uint32_t>(tid) << 8) | c);
+    }
+    for (uint32_t c = 0; c + 4 <= 128; c += 3) {
+        uint32_t r0, r1, r2, r3;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(my + c) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const uint32_t e = (static_cast<uint32_t>(tid) << 8) | c;
+        bad += (r0 != e) + (r1 != e + 1) + (r2 != e + 2) + (r3 != e + 3);
+    }
+    if (bad) atomicAdd(errors, bad);
+    __syncthreads();
+    // throughput: every warp streams x4 loads with a run-time column (like a symbol lookup)
+    unsigned long long c0 = clock64();
+    uint32_t acc = 0, col = 0;
+    for (int it = 0; it < iters; ++it) {
+        uint32_t r0, r1, r2, r3;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(my + col) : "memory");
+        col = (col + 4) & 124u;
+        uint32_t q0, q1, q2, q3;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(my + col) : "memory");
+        col = (col + 4) & 124u;
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        acc += r0 ^ r1 ^ r2 ^ r3 ^ q0 ^ q1 ^ q2 ^ q3;
+    }
+    unsigned long long c1 = clock64();
+    if (acc == 0x12345u) sink[0] = 1.f;
+    if (blockIdx.x == 0 && tid == 0) clk[0] = c1 - c0;
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(512u) : "memory");
+}
+
+} // namespace
+
+extern "C" int sv_probe_tmem(int device, int iters, unsigned* errors, double* bytes_per_clk_per_sm) {
+    if (errors == nullptr || bytes_per_clk_per_sm == nullptr || iters < 1)
+        return sv_fail(SV_ERR_ARG, "sv_probe_tmem: bad argument");
+    SV_CUDA(cudaSetDevice(device));
+    int sms = 0;
+    SV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    unsigned* d_err = nullptr;
+    unsigned long long* d_clk = nullptr;
+    float* d_sink = nullptr;
+    SV_CUDA(cudaMalloc(&d_err, sizeof(unsigned)));
+    SV_CUDA(cudaMalloc(&d_clk, sizeof(unsigned long long)));
+    SV_CUDA(cudaMalloc(&d_sink, sizeof(float)));
+    SV_CUDA(cudaMemset(d_err, 0, sizeof(unsigned)));
+    sv_probe_tmem_kernel<<<sms, 512>>>(iters, d_err, d_clk, d_sink);
+    cudaError_t e = cudaDeviceSynchronize();
+    unsigned long long clk = 1;
+    cudaMemcpy(errors, d_err, sizeof(unsigned), cudaMemcpyDeviceToHost);
+    cudaMemcpy(&clk, d_clk, sizeof(clk), cudaMemcpyDeviceToHost);
+    cudaFree(d_err);
+    cudaFree(d_clk);
+    cudaFree(d_sink);
+    if (e != cudaSuccess) return sv_fail(SV_ERR_CUDA, std::string("sv_probe_tmem: ") + cudaGetErrorString(e));
+    // per iteration each of the 16 warps reads 2 x (32 lanes x 4 columns x 4 B)
+    *bytes_per_clk_per_sm = double(iters) * 16.0 * 2.0 * 512.0 / double(clk ? clk : 1);
+    return SV_OK;
+}
