@@ -221,6 +221,8 @@ def run_b200(args):
         model.set_kernel(_lib.KERNEL_GENERIC)
     elif args.kernel == "es":
         model.set_kernel(_lib.KERNEL_ES)
+    elif args.kernel == "ls":
+        model.set_kernel(_lib.KERNEL_LS)
     info = model.info()
     seqs = model.upload(syms, offs)
     d_out = torch.empty((nseq, n), dtype=torch.float32, device=dev)
@@ -312,7 +314,7 @@ def run_b200(args):
         peak = 2.0 * sm_count * 128 * mhz * 1e6 / 1.5 / 1e12
         roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                     "frac": achieved / peak, "traffic": None,
-                    "kernel": "sv_es_kernel" if info.kernel == _lib.KERNEL_ES else "sv_plain_generic_kernel",
+                    "kernel": {_lib.KERNEL_ES: "sv_es_kernel", _lib.KERNEL_LS: "sv_ls_kernel"}.get(info.kernel, "sv_plain_generic_kernel"),
                     "relaxations_per_launch": relax, "relax_per_clk_per_sm": relax / kernel_s / (sm_count * mhz * 1e6),
                     "peak_source": f"{sm_count} SMs x 128 lanes x {mhz:.0f} MHz (NVML median during the run) / 1.5 issue "
                                    f"slots per (min,+) MAC; MEASURED_PEAKS.json ({peak_kind}) holds only HBM/bf16 peaks",
@@ -328,6 +330,10 @@ def run_b200(args):
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
             "kernel": {"name": roofline["kernel"], "es_threads": int(info.es_threads),
                        "es_seqs_per_cta": int(info.es_seqs_per_cta), "es_smem_bytes": int(info.es_smem_bytes),
+                       "ls_seqs_per_cta": int(info.ls_seqs_per_cta), "ls_smem_bytes": int(info.ls_smem_bytes),
+                       "ls_tmem_cols": int(info.ls_tmem_cols),
+                       "ls_gather_wavefronts": int(info.ls_gather_wavefronts),
+                       "ls_gather_ideal": int(info.ls_gather_ideal),
                        "step_ms": step_ms},
         }
         if not args.no_cpu:
@@ -345,7 +351,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="synthetic2405", choices=sorted(WORKLOADS))
-    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "es"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "es", "ls"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -61,7 +61,9 @@ typedef struct sv_model sv_model;
 enum {
     SV_KERNEL_AUTO = 0,
     SV_KERNEL_GENERIC = 1, /* CSR in L1/L2, any model size */
-    SV_KERNEL_ES = 2       /* edge-stationary: transitions in registers, E and v in smem */
+    SV_KERNEL_ES = 2,      /* edge-stationary: transitions in registers, E and v in smem */
+    SV_KERNEL_LS = 3       /* lockstep: 4/8 sequences per CTA, transitions in registers, v in
+                              smem as float4, E in tensor memory (the batched throughput kernel) */
 };
 
 /* Builds the device-resident model (K0 repack) from the reference's HMM layout:
@@ -87,6 +89,14 @@ typedef struct sv_model_info {
     uint64_t es_gather_ideal;      /* same with zero bank conflicts */
     uint64_t es_smem_bytes;
     uint64_t es_split_states;      /* virtual states added by in-degree capping */
+    /* lockstep schedule (zeros when the model does not fit that kernel) */
+    int32_t ls_threads, ls_seqs_per_cta, ls_ranks, ls_heavy_rows;
+    int32_t ls_tmem_cols, ls_reserved;
+    uint64_t ls_gather_wavefronts; /* LDS.128 wavefronts of the v gather per step and float4 group */
+    uint64_t ls_gather_ideal;      /* same with zero bank conflicts */
+    uint64_t ls_smem_bytes;
+    uint64_t ls_split_states;
+    uint64_t ls_colour_cost_before, ls_colour_cost_after; /* K0 bank-colouring search */
 } sv_model_info;
 int sv_model_get_info(const sv_model* m, sv_model_info* info);
 
@@ -185,6 +195,18 @@ int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_per_s, doub
  * back with run-time (warp-uniform) column addresses -- the access pattern of the emission
  * lookup in the lockstep step kernel -- and reports mismatches and the tcgen05.ld read rate. */
 int sv_probe_tmem(int device, int iters, unsigned* errors, double* bytes_per_clk_per_sm);
+
+
+/* K0 self-check (host only, no GPU, NOT a compute path): builds the lockstep schedule of a model
+ * and replays its register images for one sequence the way a CTA would, so the K0
+ * transformation can be verified against the oracle without a device.  stats[12] = {valid,
+ * threads, sequences per CTA, ranks, heavy rows, split states, gather wavefronts, ideal
+ * wavefronts, colour cost before / after the search, smem bytes, tmem columns}.  seq/out may be
+ * NULL to get the statistics only. */
+int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                         const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                         uint64_t nstart, const uint64_t* start_cols, const float* start_w,
+                         const uint64_t* seq, uint64_t len, float* out, uint64_t stats[12]);
 
 #ifdef __cplusplus
 }

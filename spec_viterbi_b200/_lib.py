@@ -12,7 +12,7 @@ _PKG = Path(__file__).resolve().parent
 LIB_PATH = _PKG / "libspecviterbi_b200.so"
 
 SV_OK = 0
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_ES = 0, 1, 2
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_ES, KERNEL_LS = 0, 1, 2, 3
 SPEC_AUTO, SPEC_DENSE_GEMM, SPEC_SPARSE_LHS = 0, 1, 2
 
 u64p = C.POINTER(C.c_uint64)
@@ -32,6 +32,12 @@ class ModelInfo(C.Structure):
         ("es_slots_per_thread", C.c_uint64),
         ("es_gather_wavefronts", C.c_uint64), ("es_gather_ideal", C.c_uint64),
         ("es_smem_bytes", C.c_uint64), ("es_split_states", C.c_uint64),
+        ("ls_threads", C.c_int32), ("ls_seqs_per_cta", C.c_int32),
+        ("ls_ranks", C.c_int32), ("ls_heavy_rows", C.c_int32),
+        ("ls_tmem_cols", C.c_int32), ("ls_reserved", C.c_int32),
+        ("ls_gather_wavefronts", C.c_uint64), ("ls_gather_ideal", C.c_uint64),
+        ("ls_smem_bytes", C.c_uint64), ("ls_split_states", C.c_uint64),
+        ("ls_colour_cost_before", C.c_uint64), ("ls_colour_cost_after", C.c_uint64),
     ]
 
 
@@ -74,6 +80,8 @@ SIGNATURES = {
     "sv_io_ess_copy": (C.c_int, [vp, u64p, u64p]),
     "sv_io_ess_write_packed": (C.c_int, [vp, C.c_char_p]),
     "sv_io_ess_close": (None, [vp]),
+    "sv_k0_lockstep_check": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
+                                       C.c_uint64, u64p, f32p, u64p, C.c_uint64, f32p, u64p]),
     "sv_probe_tmem": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]),
     "sv_probe_fp32": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
                                 C.POINTER(C.c_double)]),

@@ -144,6 +144,27 @@ def pack_sequences(seqs: Sequence[Iterable[int]]):
     return np.ascontiguousarray(syms), offs
 
 
+def k0_lockstep_check(hmm: "HMM", seq=None):
+    """Host-only K0 diagnostic: (stats dict, replayed final vector or None).  Not a compute path."""
+    lib = L.lib()
+    h = hmm.normalized()
+    stats = np.zeros(12, np.uint64)
+    out = None
+    sp, sl = None, 0
+    if seq is not None:
+        s = np.ascontiguousarray(seq, np.uint64)
+        out = np.empty(h.states_num, np.float32)
+        sp, sl = _p(s, C.c_uint64), s.size
+    L.check(lib.sv_k0_lockstep_check(
+        h.states_num, h.emit_num, h.trans_num, _p(h.trans_rows, C.c_uint64), _p(h.trans_cols, C.c_uint64),
+        _p(h.trans_probs, C.c_float), _p(h.emissions, C.c_float), h.non_zero_start_probs,
+        _p(h.start_probabilities_cols, C.c_uint64), _p(h.start_probabilities, C.c_float),
+        sp, sl, _p(out, C.c_float) if out is not None else None, _p(stats, C.c_uint64)))
+    names = ["valid", "threads", "seqs_per_cta", "ranks", "heavy_rows", "split_states", "wavefronts",
+             "ideal_wavefronts", "colour_cost_before", "colour_cost_after", "smem_bytes", "tmem_cols"]
+    return dict(zip(names, (int(x) for x in stats))), out
+
+
 class Model:
     """Device-resident model handle (sv_model)."""
 

@@ -18,9 +18,11 @@ SOURCES = [
     "csrc/sv_api.cu",
     "csrc/sv_plain_generic.cu",
     "csrc/sv_plain_es.cu",
+    "csrc/sv_plain_ls.cu",
     "csrc/sv_spec.cu",
     "csrc/sv_probe.cu",
     "csrc/sv_es_plan.cpp",
+    "csrc/sv_ls_plan.cpp",
     "csrc/sv_io.cpp",
     "host/data_reader.cpp",
 ]

@@ -157,9 +157,60 @@ int upload_es(sv_model* m) {
     return SV_OK;
 }
 
-int chosen_kernel(const sv_model* m) {
-    if (m->kernel_pref == SV_KERNEL_GENERIC) return SV_KERNEL_GENERIC;
+int upload_ls(sv_model* m) {
+    const SvLsPlan& p = m->ls;
+    size_t bytes = 0;
+    const size_t o_w = blob_reserve<float>(&bytes, p.edge_w.size());
+    const size_t o_off = blob_reserve<uint32_t>(&bytes, p.edge_off.size());
+    const size_t o_deg = blob_reserve<uint8_t>(&bytes, p.deg.size());
+    const size_t o_emis = blob_reserve<float>(&bytes, p.emis_p.size());
+    const size_t o_start = blob_reserve<float>(&bytes, p.start_p.size());
+    const size_t o_cptr = blob_reserve<uint32_t>(&bytes, p.copy_ptr.size());
+    const size_t o_cp = blob_reserve<uint32_t>(&bytes, p.copy_p.size());
+    bytes += 256;
+    std::vector<unsigned char> host(bytes, 0);
+    std::memcpy(host.data() + o_w, p.edge_w.data(), p.edge_w.size() * 4);
+    std::memcpy(host.data() + o_off, p.edge_off.data(), p.edge_off.size() * 4);
+    std::memcpy(host.data() + o_deg, p.deg.data(), p.deg.size());
+    std::memcpy(host.data() + o_emis, p.emis_p.data(), p.emis_p.size() * 4);
+    std::memcpy(host.data() + o_start, p.start_p.data(), p.start_p.size() * 4);
+    std::memcpy(host.data() + o_cptr, p.copy_ptr.data(), p.copy_ptr.size() * 4);
+    std::memcpy(host.data() + o_cp, p.copy_p.data(), p.copy_p.size() * 4);
+    SV_CUDA(cudaMalloc(&m->d_ls_blob, bytes));
+    SV_CUDA(cudaMemcpy(m->d_ls_blob, host.data(), bytes, cudaMemcpyHostToDevice));
+    auto* base = static_cast<unsigned char*>(m->d_ls_blob);
+    SvLsDev& d = m->lsdev;
+    d.n = static_cast<int>(m->n);
+    d.n_int = p.n_int;
+    d.n_lpad = p.n_lpad;
+    d.n_pad = p.n_pad;
+    d.n_heavy = p.n_heavy;
+    d.emits = static_cast<int>(m->emits);
+    d.ranks = p.ranks;
+    d.tmem_cols = p.tmem_cols;
+    d.edge_w = reinterpret_cast<const float*>(base + o_w);
+    d.edge_off = reinterpret_cast<const uint32_t*>(base + o_off);
+    d.deg = reinterpret_cast<const uint8_t*>(base + o_deg);
+    for (int h = 0; h < SV_ES_NHMAX; ++h) d.heavy_slots[h] = p.heavy_slots[h];
+    d.emis_p = reinterpret_cast<const float*>(base + o_emis);
+    d.start_p = reinterpret_cast<const float*>(base + o_start);
+    d.copy_ptr = reinterpret_cast<const uint32_t*>(base + o_cptr);
+    d.copy_p = reinterpret_cast<const uint32_t*>(base + o_cp);
+    return SV_OK;
+}
+
+// Kernel a launch over `nseq` sequences will use.  AUTO: the lockstep kernel when the batch
+// can fill its sequence lanes on every SM, else one sequence per CTA (ES), else generic.
+int chosen_kernel(const sv_model* m, uint64_t nseq) {
+    switch (m->kernel_pref) {
+    case SV_KERNEL_GENERIC: return SV_KERNEL_GENERIC;
+    case SV_KERNEL_ES: return m->es.valid ? SV_KERNEL_ES : SV_KERNEL_GENERIC;
+    case SV_KERNEL_LS: return m->ls.valid ? SV_KERNEL_LS : SV_KERNEL_GENERIC;
+    default: break;
+    }
+    if (m->ls.valid && nseq >= static_cast<uint64_t>(2) * m->sm_count) return SV_KERNEL_LS;
     if (m->es.valid) return SV_KERNEL_ES;
+    if (m->ls.valid) return SV_KERNEL_LS;
     return SV_KERNEL_GENERIC;
 }
 
@@ -242,6 +293,14 @@ extern "C" int sv_model_create(uint64_t states, uint64_t emits, uint64_t trans,
             m->es.valid = false; // kernel attribute rejected: keep the generic kernel
         }
     }
+    sv_ls_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->ls);
+    if (m->ls.valid) {
+        if ((rc = upload_ls(m)) != SV_OK) return fail(rc);
+        if (sv_ls_prepare(m->ls.variant_index, m->ls.smem_bytes) != 0) {
+            cudaGetLastError();
+            m->ls.valid = false;
+        }
+    }
     *out = m;
     return SV_OK;
 }
@@ -251,6 +310,7 @@ extern "C" void sv_model_destroy(sv_model* m) {
     cudaSetDevice(m->device);
     if (m->d_blob) cudaFree(m->d_blob);
     if (m->d_es_blob) cudaFree(m->d_es_blob);
+    if (m->d_ls_blob) cudaFree(m->d_ls_blob);
     if (m->d_counter) cudaFree(m->d_counter);
     if (m->ws.seqs) sv_seqs_destroy(m->ws.seqs);
     if (m->ws.d_out) cudaFree(m->ws.d_out);
@@ -264,7 +324,9 @@ extern "C" int sv_model_set_kernel(sv_model* m, int kernel) {
     if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_model_set_kernel: NULL model");
     if (kernel == SV_KERNEL_ES && !m->es.valid)
         return sv_fail(SV_ERR_UNSUPPORTED, "model does not fit the edge-stationary kernel");
-    if (kernel < SV_KERNEL_AUTO || kernel > SV_KERNEL_ES)
+    if (kernel == SV_KERNEL_LS && !m->ls.valid)
+        return sv_fail(SV_ERR_UNSUPPORTED, "model does not fit the lockstep kernel");
+    if (kernel < SV_KERNEL_AUTO || kernel > SV_KERNEL_LS)
         return sv_fail(SV_ERR_ARG, "sv_model_set_kernel: unknown kernel");
     m->kernel_pref = kernel;
     return SV_OK;
@@ -278,7 +340,7 @@ extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
     info->nnz = m->nnz;
     info->max_in_degree = m->max_deg;
     info->device = m->device;
-    info->kernel = chosen_kernel(m);
+    info->kernel = chosen_kernel(m, m->last_nseq ? m->last_nseq : ~0ull);
     if (m->es.valid) {
         info->es_threads = m->es.var.threads;
         info->es_seqs_per_cta = m->es.var.q;
@@ -289,6 +351,19 @@ extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
         info->es_gather_ideal = m->es.gather_ideal;
         info->es_smem_bytes = m->es.smem_bytes;
         info->es_split_states = m->es.split_states;
+    }
+    if (m->ls.valid) {
+        info->ls_threads = m->ls.var.threads;
+        info->ls_seqs_per_cta = 4 * m->ls.var.nq4;
+        info->ls_ranks = m->ls.ranks;
+        info->ls_heavy_rows = m->ls.n_heavy;
+        info->ls_tmem_cols = m->ls.tmem_cols;
+        info->ls_gather_wavefronts = m->ls.gather_wavefronts;
+        info->ls_gather_ideal = m->ls.gather_ideal;
+        info->ls_smem_bytes = m->ls.smem_bytes;
+        info->ls_split_states = m->ls.split_states;
+        info->ls_colour_cost_before = m->ls.colour_cost_before;
+        info->ls_colour_cost_after = m->ls.colour_cost_after;
     }
     return SV_OK;
 }
@@ -538,7 +613,16 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
     SV_CUDA(cudaSetDevice(m->device));
     SV_CUDA(cudaMemsetAsync(m->d_counter, 0, sizeof(unsigned), st));
     int rc;
-    if (chosen_kernel(m) == SV_KERNEL_ES) {
+    const int kernel = chosen_kernel(m, seqs->nseq);
+    m->last_nseq = seqs->nseq;
+    m->last_kernel = kernel;
+    if (kernel == SV_KERNEL_LS) {
+        const int q = 4 * m->ls.var.nq4;
+        const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
+        const int grid = static_cast<int>(std::min<int64_t>(want, m->sm_count));
+        rc = sv_ls_launch(m->ls.variant_index, m->lsdev, seqs->dev, d_out, d_best, d_best_state,
+                          m->d_counter, grid, m->ls.smem_bytes, st);
+    } else if (kernel == SV_KERNEL_ES) {
         const int per_sm = std::max(1, sv_es_max_ctas_per_sm(m->es.variant_index, m->es.smem_bytes));
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + m->es.var.q - 1) / m->es.var.q;
         const int grid = static_cast<int>(std::min<int64_t>(want, int64_t(m->sm_count) * per_sm));

@@ -106,6 +106,60 @@ int sv_es_launch(int index, const SvEsDev& m, const SvSeqsDev& s, float* d_out, 
 int sv_es_max_ctas_per_sm(int index, size_t smem);
 int sv_es_prepare(int index, size_t smem); // sets the dynamic smem attribute
 
+// ------------------------------------------------------ lockstep (LS) kernel ----
+// Edge-stationary like the ES kernel, but 4 or 8 sequences advance in lockstep per CTA
+// (score vectors interleaved [state][4] so one LDS.128 feeds four relaxations) and the
+// emission table lives in TENSOR MEMORY (tcgen05.ld lookup), which frees the shared memory
+// for the score vectors.  K0 colours the states so that the 8 lanes of every LDS.128 phase hit
+// 8 distinct 16-byte bank groups.
+constexpr int SV_LS_RSTRIDE = SV_ES_RMAX; // TMEM columns per symbol (one per rank)
+
+struct SvLsVariant {
+    int threads;                 // threads per CTA
+    int nq4;                     // float4 groups of sequences: Q = 4 * nq4
+    int shape[SV_ES_RMAX];       // max register slots per rank
+    int nh;                      // heavy rows supported
+    int hs;                      // register slots per heavy row per thread
+};
+
+struct SvLsPlan {
+    bool valid = false;
+    SvLsVariant var{};
+    int variant_index = -1;
+    int n_int = 0;    // internal states (after splitting), light + heavy
+    int n_lpad = 0;   // light positions = ranks * threads (holes included)
+    int n_pad = 0;    // positions per score buffer (n_lpad + heavy, rounded up to 8)
+    int n_heavy = 0, nslots = 0, ranks = 0, tmem_cols = 0;
+    uint64_t gather_wavefronts = 0, gather_ideal = 0, smem_bytes = 0, split_states = 0;
+    uint64_t colour_cost_before = 0, colour_cost_after = 0; // excess bank-group loads (K0 search)
+    std::vector<float> edge_w;       // [nslots][threads]
+    std::vector<uint32_t> edge_off;  // [nslots][threads] byte offset of v[src] in a buffer: p * 16
+    std::vector<uint8_t> deg;        // [warps][RMAX]
+    std::vector<uint8_t> heavy_slots;
+    std::vector<float> emis_p;       // [emits][n_pad]
+    std::vector<float> start_p;      // [n_pad]
+    std::vector<uint32_t> copy_ptr;  // [n+1]
+    std::vector<uint32_t> copy_p;    // [n_int]
+};
+
+struct SvLsDev {
+    int n = 0, n_int = 0, n_lpad = 0, n_pad = 0, n_heavy = 0, emits = 0, ranks = 0, tmem_cols = 0;
+    const float* edge_w = nullptr;
+    const uint32_t* edge_off = nullptr;
+    const uint8_t* deg = nullptr;
+    uint8_t heavy_slots[SV_ES_NHMAX] = {0, 0};
+    const float* emis_p = nullptr;
+    const float* start_p = nullptr;
+    const uint32_t* copy_ptr = nullptr;
+    const uint32_t* copy_p = nullptr;
+};
+
+int sv_ls_num_variants();
+const SvLsVariant& sv_ls_variant(int index);
+int sv_ls_prepare(int index, size_t smem);
+int sv_ls_launch(int index, const SvLsDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+                 int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
+
 // ----------------------------------------------------------- host model ----
 struct SvHostCsr {
     uint64_t n = 0;
@@ -140,8 +194,14 @@ struct sv_model {
     SvEsPlan es;
     SvEsDev esdev;
     void* d_es_blob = nullptr;
+    // lockstep plan
+    SvLsPlan ls;
+    SvLsDev lsdev;
+    void* d_ls_blob = nullptr;
     int kernel_pref = SV_KERNEL_AUTO;
     int last_launches = 0;
+    int last_kernel = 0;
+    uint64_t last_nseq = 0;
     // scratch for host-buffer entry points
     cudaStream_t stream = nullptr;
     SvWorkspace ws;
@@ -170,6 +230,11 @@ int sv_ws_download(sv_model* m, uint64_t nseq, const float* d_out, const float* 
 void sv_es_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
                       const std::vector<float>& start, uint64_t emits, size_t smem_limit,
                       SvEsPlan* plan);
+
+// K0 for the lockstep kernel (sv_ls_plan.cpp); plan.valid=false if the model does not fit.
+void sv_ls_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
+                      const std::vector<float>& start, uint64_t emits, size_t smem_limit,
+                      SvLsPlan* plan);
 
 // generic kernel launcher (sv_plain_generic.cu)
 int sv_generic_launch(const SvGenericDev& m, const SvSeqsDev& s, float* d_out, float* d_best,

@@ -8,7 +8,7 @@ from conftest import PROFILE_MODELS, best_state, same_bits
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = ["generic", "es"]
+KERNELS = ["generic", "es", "ls"]
 
 
 def _model(api, hmm, kernel):
@@ -20,6 +20,10 @@ def _model(api, hmm, kernel):
         if m.info().es_threads == 0:
             pytest.skip("model does not fit the edge-stationary kernel")
         m.set_kernel(_lib.KERNEL_ES)
+    elif kernel == "ls":
+        if m.info().ls_threads == 0:
+            pytest.skip("model does not fit the lockstep kernel")
+        m.set_kernel(_lib.KERNEL_LS)
     return m
 
 
