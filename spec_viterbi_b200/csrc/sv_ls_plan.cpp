@@ -365,7 +365,10 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     const int n_pad = static_cast<int>((n_lpad + n_heavy + 7) / 8 * 8);
 
     // ---- shared memory: 2 buffers x nq4 groups x n_pad float4, heavy reduction scratch ----
-    const size_t smem = static_cast<size_t>(2) * var.nq4 * n_pad * 16 +
+    // (static layout: every float4 group is sized for the largest model the variant takes)
+    const size_t npad_max = static_cast<size_t>(SV_ES_RMAX) * TPG + 8;
+    if (static_cast<size_t>(n_pad) > npad_max) return false;
+    const size_t smem = static_cast<size_t>(2) * var.nq4 * npad_max * 16 +
                         static_cast<size_t>(var.nh) * NW * Q * 4;
     if (smem + 1024 > smem_limit) return false;
 

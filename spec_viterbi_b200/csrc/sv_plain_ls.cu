@@ -58,60 +58,110 @@ __device__ __forceinline__ void tmem_st1(uint32_t taddr, float v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(__float_as_uint(v))
                  : "memory");
 }
-__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
-    uint32_t r;
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr) : "memory");
-    return r;
+// E of one sequence for ranks 0..3 (x4) and rank 4 (x1): 5 consecutive TMEM columns.
+__device__ __forceinline__ void tmem_ld5(uint32_t taddr, uint32_t (&r)[5]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr)
+                 : "memory");
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r[4]) : "r"(taddr + 4u) : "memory");
 }
-// Waits for the outstanding tcgen05.ld's; the loaded registers are operands so that no use of
-// them can be scheduled above the wait.
-__device__ __forceinline__ void tmem_wait4(uint32_t (&r)[4]) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3])::"memory");
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&r)[5]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr)
+                 : "memory");
+    r[4] = 0;
 }
-
 // Per-step control block published by the manager lanes.
 struct alignas(16) LsCtl {
-    uint32_t col[8];   // TMEM column offset of each sequence's current symbol: symbol * RSTRIDE
+    uint32_t col[8];    // TMEM column offset of each sequence's current symbol: symbol * RSTRIDE
     uint32_t init_mask; // sequences whose step is v_0 = E[o_0] + start
     uint32_t fin_mask;  // sequences for which this step is the last one
     uint32_t any_act;   // sequences that take part in this step (0 = CTA is done)
     uint32_t pad;
 };
 
-template <int Q>
-__device__ __forceinline__ void relax4(float w, const float4 v, const float* e, float* acc) {
-    // fl(fl(E + T') + v), exact min -- never re-associated
-    acc[0] = fminf(acc[0], (e[0] + w) + v.x);
-    acc[1] = fminf(acc[1], (e[1] + w) + v.y);
-    acc[2] = fminf(acc[2], (e[2] + w) + v.z);
-    acc[3] = fminf(acc[3], (e[3] + w) + v.w);
+// Sequence-manager state of one sequence slot (owned by lane q of warp 0, kept in shared memory
+// so that it does not occupy registers in all 512 threads).
+struct alignas(16) LsMgr {
+    unsigned long long cur, nxt; // packed symbol words: current and next 8 symbols
+    unsigned long long idx;      // index of the NEXT step's symbol in the packed array
+    uint32_t t, len, sid, act;
+};
+
+// fl(fl(E + T') + v) -- the two adds are never re-associated (GraphBLAS_impl.cpp:65,69)
+__device__ __forceinline__ float relax1(float e, float w, float v) { return (e + w) + v; }
+
+// One pair of slots for 4 sequences: acc = min(acc, x0, x1) is a single 3-input FMNMX3.
+template <bool FIRST>
+__device__ __forceinline__ void pair4(float w0, float w1, const float4 a, const float4 b, const float* e,
+                                      float* acc) {
+    const float x0 = fminf(relax1(e[0], w0, a.x), relax1(e[0], w1, b.x));
+    const float x1 = fminf(relax1(e[1], w0, a.y), relax1(e[1], w1, b.y));
+    const float x2 = fminf(relax1(e[2], w0, a.z), relax1(e[2], w1, b.z));
+    const float x3 = fminf(relax1(e[3], w0, a.w), relax1(e[3], w1, b.w));
+    if (FIRST) {
+        acc[0] = x0; acc[1] = x1; acc[2] = x2; acc[3] = x3;
+    } else {
+        acc[0] = fminf(acc[0], x0); acc[1] = fminf(acc[1], x1);
+        acc[2] = fminf(acc[2], x2); acc[3] = fminf(acc[3], x3);
+    }
+}
+template <bool FIRST>
+__device__ __forceinline__ void single4(float w0, const float4 a, const float* e, float* acc) {
+    const float x0 = relax1(e[0], w0, a.x), x1 = relax1(e[1], w0, a.y);
+    const float x2 = relax1(e[2], w0, a.z), x3 = relax1(e[3], w0, a.w);
+    if (FIRST) {
+        acc[0] = x0; acc[1] = x1; acc[2] = x2; acc[3] = x3;
+    } else {
+        acc[0] = fminf(acc[0], x0); acc[1] = fminf(acc[1], x1);
+        acc[2] = fminf(acc[2], x2); acc[3] = fminf(acc[3], x3);
+    }
 }
 
-// Runs slots [0, d) of the register slice [BASE, BASE + SMAX) (d warp-uniform).  Fall-through
-// switch: every register index is a compile-time constant.
-template <int NQ4, int BASE, int SMAX, int NSLOTS>
+// Runs slots [0, d) of the register slice [BASE, BASE + SMAX) (d warp-uniform) as a chain of
+// nested uniform branches over slot PAIRS; every register index is a compile-time constant and
+// every shared-memory address is register + immediate (vbase is a constant expression).
+template <int NQ4, int GS, int BASE, int SMAX, int NSLOTS, int K = 0>
 __device__ __forceinline__ void ls_run_slots(int d, const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS],
-                                             const unsigned char* vcur, uint32_t gstride,
-                                             const float (&e)[4 * NQ4], float (&acc)[4 * NQ4]) {
-#define SV_LS_SLOT(K)                                                                           \
-    if constexpr ((K) < SMAX) {                                                                 \
-        const unsigned char* src = vcur + eo[BASE + (K)];                                       \
-        _Pragma("unroll") for (int g = 0; g < NQ4; ++g)                                         \
-            relax4<4>(ew[BASE + (K)], *reinterpret_cast<const float4*>(src + g * gstride),      \
-                      &e[4 * g], &acc[4 * g]);                                                  \
+                                             const unsigned char* vbase, const float (&e)[4 * NQ4],
+                                             float (&acc)[4 * NQ4]) {
+    if constexpr (K >= SMAX) {
+        if constexpr (K == 0) {
+#pragma unroll
+            for (int q = 0; q < 4 * NQ4; ++q) acc[q] = pos_inf();
+        }
+        return;
+    } else if constexpr (K + 1 >= SMAX) { // a single slot is left in the slice
+        if (d > K) {
+#pragma unroll
+            for (int g = 0; g < NQ4; ++g)
+                single4<K == 0>(ew[BASE + K], *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K]),
+                                &e[4 * g], &acc[4 * g]);
+        } else if constexpr (K == 0) {
+#pragma unroll
+            for (int q = 0; q < 4 * NQ4; ++q) acc[q] = pos_inf();
+        }
+    } else {
+        if (d > K + 1) {
+#pragma unroll
+            for (int g = 0; g < NQ4; ++g)
+                pair4<K == 0>(ew[BASE + K], ew[BASE + K + 1],
+                              *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K]),
+                              *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K + 1]), &e[4 * g],
+                              &acc[4 * g]);
+            ls_run_slots<NQ4, GS, BASE, SMAX, NSLOTS, K + 2>(d, ew, eo, vbase, e, acc);
+        } else if (d > K) {
+#pragma unroll
+            for (int g = 0; g < NQ4; ++g)
+                single4<K == 0>(ew[BASE + K], *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K]),
+                                &e[4 * g], &acc[4 * g]);
+        } else if constexpr (K == 0) {
+#pragma unroll
+            for (int q = 0; q < 4 * NQ4; ++q) acc[q] = pos_inf();
+        }
     }
-    switch (d) {
-    case 8: SV_LS_SLOT(7) [[fallthrough]];
-    case 7: SV_LS_SLOT(6) [[fallthrough]];
-    case 6: SV_LS_SLOT(5) [[fallthrough]];
-    case 5: SV_LS_SLOT(4) [[fallthrough]];
-    case 4: SV_LS_SLOT(3) [[fallthrough]];
-    case 3: SV_LS_SLOT(2) [[fallthrough]];
-    case 2: SV_LS_SLOT(1) [[fallthrough]];
-    case 1: SV_LS_SLOT(0) [[fallthrough]];
-    default: break;
-    }
-#undef SV_LS_SLOT
 }
 
 } // namespace
@@ -127,16 +177,16 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     constexpr int NL = SH::total();
     constexpr int NSL = NL + NH * HS;
     constexpr int RS = SV_LS_RSTRIDE;
-    static_assert(SH::R == SV_ES_RMAX, "shape must list SV_ES_RMAX ranks");
-    static_assert(NH <= SV_ES_NHMAX, "too many heavy rows");
+    constexpr int NPAD = SV_ES_RMAX * TPG + 8; // positions per float4 group (static layout)
+    constexpr int GS = NPAD * 16;              // bytes of one float4 group
+    constexpr int BS = NQ4 * GS;               // bytes of one score buffer
+    static_assert(SH::R == SV_ES_RMAX && SV_ES_RMAX == 5, "five ranks");
+    static_assert(NH <= SV_ES_NHMAX && NH <= 2, "too many heavy rows");
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int n_pad = m.n_pad;
-    const uint32_t gstride = static_cast<uint32_t>(n_pad) * 16u;  // one float4 group
-    const uint32_t bstride = gstride * NQ4;                       // one buffer
-    float* red = reinterpret_cast<float*>(smem_raw + 2u * bstride); // [NH][NW][Q]
+    float* red = reinterpret_cast<float*>(smem_raw + 2 * BS); // [NH][NW][Q]
     __shared__ LsCtl ctl[2];
-    __shared__ uint32_t s_sid[8];
+    __shared__ LsMgr mgr[8];
     __shared__ uint32_t s_taddr;
     __shared__ float s_bv[NW];
     __shared__ int s_bi[NW];
@@ -144,6 +194,7 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned long long* __restrict__ sym64 = static_cast<const unsigned long long*>(s.sym);
     const int nranks = m.ranks;
+    const int n_pad = m.n_pad;
 
     // ---- one-time: tensor memory <- emission table, registers <- this thread's edges ----
     if (warp == 0) tmem_alloc(&s_taddr, static_cast<uint32_t>(m.tmem_cols));
@@ -155,9 +206,9 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     const uint32_t tE = tbase + (static_cast<uint32_t>(warp & 3) << 21) +
                         static_cast<uint32_t>(warp >> 2) * static_cast<uint32_t>(m.emits * RS);
     for (int o = 0; o < m.emits; ++o) {
-        for (int r = 0; r < nranks; ++r)
+        for (int r = 0; r < RS; ++r)
             tmem_st1(tE + static_cast<uint32_t>(o * RS + r),
-                     m.emis_p[static_cast<size_t>(o) * n_pad + r * TPG + tid]);
+                     r < nranks ? m.emis_p[static_cast<size_t>(o) * n_pad + r * TPG + tid] : 0.f);
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 
@@ -168,46 +219,39 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         ew[k] = m.edge_w[static_cast<size_t>(k) * TPG + tid];
         eo[k] = m.edge_off[static_cast<size_t>(k) * TPG + tid];
     }
-    int deg[SV_ES_RMAX];
+    uint32_t degs = 0; // 4 bits per rank
 #pragma unroll
-    for (int r = 0; r < SV_ES_RMAX; ++r) deg[r] = m.deg[warp * SV_ES_RMAX + r];
+    for (int r = 0; r < SV_ES_RMAX; ++r) degs |= static_cast<uint32_t>(m.deg[warp * SV_ES_RMAX + r]) << (4 * r);
+    const uint32_t own16 = static_cast<uint32_t>(tid) * 16u;
 
-    // ---- sequence managers: lane q of warp 0 owns sequence slot q ----
-    bool m_act = false;
-    uint32_t m_t = 0, m_len = 0, m_sid = 0;
-    uint64_t m_i = 0;                    // index (into the packed symbols) of the NEXT step's symbol
-    unsigned long long m_cur = 0, m_nxt = 0;
-    auto next_symbol = [&]() -> uint32_t {
-        const uint32_t sy = static_cast<uint32_t>(m_cur >> ((m_i & 7u) * 8u)) & 0xffu;
-        ++m_i;
-        if ((m_i & 7u) == 0) {
-            m_cur = m_nxt;
-            m_nxt = sym64[(m_i >> 3) + 1];
-        }
-        return sy;
-    };
     // Hands new sequences to the manager lanes in `mask` and patches the control block of the
     // coming step (fresh: overwrite it).  Called by all lanes of warp 0.
     auto refill = [&](uint32_t mask, LsCtl& dst, bool fresh) {
         bool started = false, one = false;
         uint32_t colv = 0;
         if (lane < Q && ((mask >> lane) & 1u)) {
-            m_act = false;
+            LsMgr g;
+            g.act = 0;
+            g.t = g.len = g.sid = 0;
+            g.cur = g.nxt = g.idx = 0;
             const unsigned w = atomicAdd(counter, 1u);
             if (w < static_cast<unsigned>(s.nseq)) {
-                m_sid = s.order[w];
-                const uint64_t b = s.off[m_sid];
-                m_len = static_cast<uint32_t>(s.off[m_sid + 1] - b);
-                m_t = 0;
-                m_i = b;
-                m_cur = sym64[m_i >> 3];
-                m_nxt = sym64[(m_i >> 3) + 1];
-                colv = next_symbol() * RS;
-                m_act = true;
+                g.sid = s.order[w];
+                const uint64_t b = s.off[g.sid];
+                g.len = static_cast<uint32_t>(s.off[g.sid + 1] - b);
+                g.cur = sym64[b >> 3];
+                g.nxt = sym64[(b >> 3) + 1];
+                colv = (static_cast<uint32_t>(g.cur >> ((b & 7u) * 8u)) & 0xffu) * RS;
+                g.idx = b + 1;
+                if ((g.idx & 7u) == 0) {
+                    g.cur = g.nxt;
+                    g.nxt = sym64[(g.idx >> 3) + 1];
+                }
+                g.act = 1;
                 started = true;
-                one = m_len == 1;
-                s_sid[lane] = m_sid;
+                one = g.len == 1;
             }
+            mgr[lane] = g;
         }
         const uint32_t startm = __ballot_sync(0xffffffffu, started);
         const uint32_t onem = __ballot_sync(0xffffffffu, one);
@@ -226,55 +270,59 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         __syncwarp();
     };
     if (warp == 0) refill((1u << Q) - 1u, ctl[0], true);
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
-    unsigned char* vcur = smem_raw;
-    unsigned char* vnxt = smem_raw + bstride;
-
-    for (uint32_t step = 0;; ++step) {
-        const LsCtl& c = ctl[step & 1u];
-        const uint32_t any_act = c.any_act;
-        if (any_act == 0) break;
+    // One time step.  B = parity of the step = index of the score buffer that is read and of the
+    // control block that is consumed; everything addressed through B is a compile-time constant.
+    auto step_body = [&](auto bc) -> bool {
+        constexpr int B = decltype(bc)::value;
+        const unsigned char* vc = smem_raw + B * BS;
+        unsigned char* vn = smem_raw + (1 - B) * BS;
+        const LsCtl& c = ctl[B];
+        if (c.any_act == 0) return false;
         const uint32_t init_mask = c.init_mask, fin_mask = c.fin_mask;
-        uint32_t col[Q];
+
+        // ---- emission scores of this step: E[o_q][own row of every rank] from tensor memory ----
+        uint32_t et[Q][5];
         {
+            uint32_t col[Q];
             const uint4 c0 = *reinterpret_cast<const uint4*>(&c.col[0]);
             col[0] = c0.x; col[1] = c0.y; col[2] = c0.z; col[3] = c0.w;
             if constexpr (NQ4 == 2) {
                 const uint4 c1 = *reinterpret_cast<const uint4*>(&c.col[4]);
                 col[4] = c1.x; col[5] = c1.y; col[6] = c1.z; col[7] = c1.w;
             }
+            if (nranks == 5) {
+#pragma unroll
+                for (int q = 0; q < Q; ++q) tmem_ld5(tE + col[q], et[q]);
+            } else {
+#pragma unroll
+                for (int q = 0; q < Q; ++q) tmem_ld4(tE + col[q], et[q]);
+            }
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int q = 0; q < Q; ++q) // ties the loaded registers to the wait above
+                asm volatile("" : "+r"(et[q][0]), "+r"(et[q][1]), "+r"(et[q][2]), "+r"(et[q][3]), "+r"(et[q][4]));
         }
 
         // ---- light rows ----
         auto rank_step = [&](auto rc) {
             constexpr int r = decltype(rc)::value;
             if (r < nranks) {
-                const uint32_t p = static_cast<uint32_t>(tid + r * TPG);
                 float e[Q], acc[Q];
 #pragma unroll
-                for (int g = 0; g < NQ4; ++g) {
-                    uint32_t t4[4];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) t4[k] = tmem_ld1(tE + col[4 * g + k] + r);
-                    tmem_wait4(t4);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) e[4 * g + k] = __uint_as_float(t4[k]);
-                }
-#pragma unroll
-                for (int q = 0; q < Q; ++q) acc[q] = pos_inf();
-                ls_run_slots<NQ4, SH::base(r), SH::at(r), NSL>(deg[r], ew, eo, vcur, gstride, e, acc);
+                for (int q = 0; q < Q; ++q) e[q] = __uint_as_float(et[q][r]);
+                ls_run_slots<NQ4, GS, SH::base(r), SH::at(r), NSL>(static_cast<int>((degs >> (4 * r)) & 15u), ew,
+                                                                   eo, vc, e, acc);
                 if (init_mask != 0) {
-                    const float st = m.start_p[p];
+                    const float st = m.start_p[tid + r * TPG];
 #pragma unroll
                     for (int q = 0; q < Q; ++q)
                         if ((init_mask >> q) & 1u) acc[q] = e[q] + st; // v_0 = E[o_0] + start
                 }
 #pragma unroll
                 for (int g = 0; g < NQ4; ++g)
-                    *reinterpret_cast<float4*>(vnxt + g * gstride + p * 16u) =
+                    *reinterpret_cast<float4*>(vn + g * GS + r * TPG * 16 + own16) =
                         make_float4(acc[4 * g], acc[4 * g + 1], acc[4 * g + 2], acc[4 * g + 3]);
             }
         };
@@ -283,7 +331,6 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         rank_step(std::integral_constant<int, 2>{});
         rank_step(std::integral_constant<int, 3>{});
         rank_step(std::integral_constant<int, 4>{});
-        static_assert(SV_ES_RMAX == 5, "rank_step calls above assume 5 ranks");
 
         // ---- heavy rows: every thread relaxes a slice, block-wide min ----
         if constexpr (NH > 0) {
@@ -294,11 +341,9 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                         const int ph = m.n_lpad + h;
                         float he[Q], acc[Q];
 #pragma unroll
-                        for (int q = 0; q < Q; ++q) {
-                            he[q] = m.emis_p[static_cast<size_t>(col[q] / RS) * n_pad + ph];
-                            acc[q] = pos_inf();
-                        }
-                        ls_run_slots<NQ4, NL + h * HS, HS, NSL>(m.heavy_slots[h], ew, eo, vcur, gstride, he, acc);
+                        for (int q = 0; q < Q; ++q)
+                            he[q] = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + ph];
+                        ls_run_slots<NQ4, GS, NL + h * HS, HS, NSL>(m.heavy_slots[h], ew, eo, vc, he, acc);
 #pragma unroll
                         for (int q = 0; q < Q; ++q) {
 #pragma unroll
@@ -313,7 +358,6 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 };
                 heavy_step(std::integral_constant<int, 0>{});
                 if constexpr (NH > 1) heavy_step(std::integral_constant<int, 1>{});
-                static_assert(NH <= 2, "heavy_step calls above assume <= 2 heavy rows");
                 __syncthreads();
                 if (warp < m.n_heavy) {
                     // lane l: sequence q = l / LPQ, partials of warps (l % LPQ) + j * LPQ
@@ -326,22 +370,31 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     if ((init_mask >> q) & 1u)
                         x = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + ph] + m.start_p[ph];
                     if (lane % LPQ == 0)
-                        reinterpret_cast<float*>(vnxt + (q >> 2) * gstride + static_cast<uint32_t>(ph) * 16u)[q & 3] = x;
+                        reinterpret_cast<float*>(vn + (q >> 2) * GS + ph * 16)[q & 3] = x;
                 }
             }
         }
 
         // ---- managers: publish the control block of the next step ----
         if (warp == 0) {
-            LsCtl& nx = ctl[(step + 1u) & 1u];
+            LsCtl& nx = ctl[1 - B];
             bool cont = false, last = false;
             uint32_t colv = 0;
-            if (lane < Q && m_act) {
-                if (m_t + 1u < m_len) {
+            if (lane < Q) {
+                LsMgr& g = mgr[lane];
+                const uint32_t t = g.t, len = g.len;
+                if (g.act != 0 && t + 1u < len) {
                     cont = true;
-                    colv = next_symbol() * RS;
-                    last = m_t + 2u == m_len;
-                    m_t += 1u;
+                    unsigned long long idx = g.idx;
+                    colv = (static_cast<uint32_t>(g.cur >> ((idx & 7u) * 8u)) & 0xffu) * RS;
+                    ++idx;
+                    if ((idx & 7u) == 0) {
+                        g.cur = g.nxt;
+                        g.nxt = sym64[(idx >> 3) + 1];
+                    }
+                    g.idx = idx;
+                    last = t + 2u == len;
+                    g.t = t + 1u;
                 }
             }
             const uint32_t contm = __ballot_sync(0xffffffffu, cont);
@@ -354,18 +407,13 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
             }
         }
         __syncthreads();
-        {
-            unsigned char* sw = vcur;
-            vcur = vnxt;
-            vnxt = sw;
-        }
 
         // ---- rare path: write out finished sequences, hand out new ones ----
         if (fin_mask != 0) {
             for (int q = 0; q < Q; ++q) {
                 if (!((fin_mask >> q) & 1u)) continue;
-                const uint32_t sid = s_sid[q];
-                const float* vq = reinterpret_cast<const float*>(vcur + (q >> 2) * gstride) + (q & 3);
+                const uint32_t sid = mgr[q].sid;
+                const float* vq = reinterpret_cast<const float*>(vn + (q >> 2) * GS) + (q & 3);
                 float bv = pos_inf();
                 int bi = 0x7fffffff;
                 for (int i = tid; i < m.n; i += TPG) {
@@ -413,9 +461,15 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     __syncthreads();
                 }
             }
-            if (warp == 0) refill(fin_mask, ctl[(step + 1u) & 1u], false);
+            if (warp == 0) refill(fin_mask, ctl[1 - B], false);
             __syncthreads();
         }
+        return true;
+    };
+
+    for (;;) {
+        if (!step_body(std::integral_constant<int, 0>{})) break;
+        if (!step_body(std::integral_constant<int, 1>{})) break;
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
