@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""Spec path numbers (BASELINE.json configs[2]): 2405.chmm x emit_50_3500_20, level 2.
+Prints one JSON line: precompute ms for K3 (dense (min,+) GEMM) and K3' (sparse LHS), run ms
+(K4), achieved FP32 / HBM fractions.  CUDA events via torch on the library's own stream are not
+visible, so wall clock around synchronous C-ABI calls is used (calls block until done)."""
+import json, sys, time
+from pathlib import Path
+import numpy as np
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from spec_viterbi_b200 import api, _lib  # noqa: E402
+
+def main():
+    name = sys.argv[1] if len(sys.argv) > 1 else "2405"
+    hmm = api.read_HMM(str(ROOT / "tests/golden/models" / f"{name}.chmmb"))
+    seqs = api.read_emit_seq(str(ROOT / "tests/golden/seqs/emit_50_3500_20.essb"))
+    syms, offs = api.pack_sequences(seqs)
+    n, E = hmm.states_num, hmm.emit_num
+    m = api.Model(hmm)
+    nnz = int(m.info().nnz)
+    res = {"model": name, "states": n, "nnz": nnz, "handlers": E * E, "table_GB": E * E * n * n * 4 / 1e9}
+    peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {"hbm_gbs": 6650.0}
+    for label, method in (("sparse_lhs", _lib.SPEC_SPARSE_LHS), ("dense_gemm", _lib.SPEC_DENSE_GEMM)):
+        ts = []
+        sp = None
+        for _ in range(3):
+            if sp is not None:
+                sp.close()
+            t0 = time.perf_counter()
+            sp = api.Spec(m, 2, method)
+            ts.append((time.perf_counter() - t0) * 1e3)
+        res[f"precompute_ms_{label}"] = min(ts)
+        if label == "dense_gemm":
+            npad = (n + 127) // 128 * 128
+            res["dense_gemm_mac_per_s"] = E * E * float(npad) ** 3 / (min(ts) * 1e-3)
+            res["dense_gemm_frac_of_fp32_mac_peak"] = res["dense_gemm_mac_per_s"] / (148 * 128 * 1.965e9 / 1.5)
+        else:
+            res["sparse_lhs_write_GBs"] = res["table_GB"] / (min(ts) * 1e-3)
+            res["sparse_lhs_frac_of_hbm"] = res["sparse_lhs_write_GBs"] / peaks["hbm_gbs"]
+        if label == "sparse_lhs":
+            rt = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                out, best, arg = sp.run_batch(syms, offs)
+                rt.append((time.perf_counter() - t0) * 1e3)
+            res["run_ms_level2"] = min(rt)
+            chunks = sum((len(s) - 1) // 2 for s in seqs)
+            res["run_handler_read_GBs"] = chunks * n * n * 4 / 1e9 / (min(rt) * 1e-3)
+            res["run_frac_of_hbm"] = res["run_handler_read_GBs"] / peaks["hbm_gbs"]
+            res["run_state_updates_per_s"] = sum(len(s) for s in seqs) * n / (min(rt) * 1e-3)
+            # plain path on the same input for the honest comparison
+            pt = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                pout, _, _ = m.viterbi_batch(syms, offs)
+                pt.append((time.perf_counter() - t0) * 1e3)
+            res["plain_ms_same_input"] = min(pt)
+            res["max_rel_spec2_vs_plain"] = float(np.max(np.abs(out - pout) / np.abs(pout)))
+            res["argmin_equal"] = bool(np.array_equal(out.argmin(1), pout.argmin(1)))
+        sp.close()
+    print(json.dumps(res))
+
+if __name__ == "__main__":
+    main()
