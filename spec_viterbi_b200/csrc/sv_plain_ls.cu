@@ -58,7 +58,7 @@ __device__ __forceinline__ void tmem_st1(uint32_t taddr, float v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(__float_as_uint(v))
                  : "memory");
 }
-// E of one sequence for ranks 0..3 (x4) and rank 4 (x1): 5 consecutive TMEM columns.
+// E[o][own rows of ranks 0..4] of one sequence: 5 consecutive TMEM columns at a run-time address.
 __device__ __forceinline__ void tmem_ld5(uint32_t taddr, uint32_t (&r)[5]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
@@ -66,12 +66,12 @@ __device__ __forceinline__ void tmem_ld5(uint32_t taddr, uint32_t (&r)[5]) {
                  : "memory");
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r[4]) : "r"(taddr + 4u) : "memory");
 }
-__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&r)[5]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-                 : "r"(taddr)
+// v'[own row] of 4 sequences: 32-bit shared address + immediate (no generic-pointer arithmetic)
+template <int IMM>
+__device__ __forceinline__ void sts128(uint32_t addr, const float (&a)[4]) {
+    asm volatile("st.shared.v4.f32 [%0+%1], {%2,%3,%4,%5};" ::"r"(addr), "n"(IMM), "f"(a[0]), "f"(a[1]), "f"(a[2]),
+                 "f"(a[3])
                  : "memory");
-    r[4] = 0;
 }
 // Per-step control block published by the manager lanes.
 struct alignas(16) LsCtl {
@@ -120,47 +120,86 @@ __device__ __forceinline__ void single4(float w0, const float4 a, const float* e
     }
 }
 
-// Runs slots [0, d) of the register slice [BASE, BASE + SMAX) (d warp-uniform) as a chain of
-// nested uniform branches over slot PAIRS; every register index is a compile-time constant and
-// every shared-memory address is register + immediate (vbase is a constant expression).
-template <int NQ4, int GS, int BASE, int SMAX, int NSLOTS, int K = 0>
-__device__ __forceinline__ void ls_run_slots(int d, const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS],
-                                             const unsigned char* vbase, const float (&e)[4 * NQ4],
-                                             float (&acc)[4 * NQ4]) {
-    if constexpr (K >= SMAX) {
-        if constexpr (K == 0) {
+// Gather of one slot: volatile, so the software pipeline below is emitted in the order written
+// (the relaxations float freely around the loads).  addr = absolute shared address of v[src] in
+// buffer 0 + parity offset (a uniform register); the float4-group offset is an immediate.
+template <int IMM>
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4+%5];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(addr), "n"(IMM)
+                 : "memory");
+    return v;
+}
+
+// Gathered scores of one slot pair (4 sequences).
+struct LsPair {
+    float4 a, b;
+};
+
+// k / both are compile-time constants after unrolling (register indices stay static).
+template <int GOFF, int NSLOTS>
+__device__ __forceinline__ void ls_gather(const uint32_t (&eo)[NSLOTS], uint32_t pofs, LsPair& d, int k, bool both) {
+    d.a = lds128<GOFF>(eo[k] + pofs);
+    if (both) d.b = lds128<GOFF>(eo[k + 1] + pofs);
+}
+
+// D slots (compile-time) of the register slice [BASE, BASE + D) for the 4 sequences of the float4
+// group at byte offset GOFF, as straight-line code, slot PAIRS at a time with register double
+// buffering: the gathers of pair p + 1 are issued before the relaxations of pair p, and before the
+// last pair the FIRST pair of the next slice (NBASE >= 0: next rank, or rank 0 of the next group,
+// at group offset NGOFF) is issued, so that only the first gather of a time step is exposed.
+// `io` holds this slice's first pair on entry and the next slice's first pair on exit.
+template <int GOFF, int BASE, int D, int NGOFF, int NBASE, bool NBOTH, int NSLOTS>
+__device__ __forceinline__ void ls_fixed(const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS], uint32_t pofs,
+                                         const float (&e)[4], float (&acc)[4], LsPair& io) {
+    if constexpr (D == 0) {
 #pragma unroll
-            for (int q = 0; q < 4 * NQ4; ++q) acc[q] = pos_inf();
-        }
-        return;
-    } else if constexpr (K + 1 >= SMAX) { // a single slot is left in the slice
-        if (d > K) {
-#pragma unroll
-            for (int g = 0; g < NQ4; ++g)
-                single4<K == 0>(ew[BASE + K], *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K]),
-                                &e[4 * g], &acc[4 * g]);
-        } else if constexpr (K == 0) {
-#pragma unroll
-            for (int q = 0; q < 4 * NQ4; ++q) acc[q] = pos_inf();
-        }
+        for (int q = 0; q < 4; ++q) acc[q] = pos_inf();
+        if constexpr (NBASE >= 0) ls_gather<NGOFF>(eo, pofs, io, NBASE, NBOTH);
     } else {
-        if (d > K + 1) {
+        constexpr int NP = (D + 1) / 2;
+        LsPair buf[NP + 1];
+        buf[0] = io;
 #pragma unroll
-            for (int g = 0; g < NQ4; ++g)
-                pair4<K == 0>(ew[BASE + K], ew[BASE + K + 1],
-                              *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K]),
-                              *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K + 1]), &e[4 * g],
-                              &acc[4 * g]);
-            ls_run_slots<NQ4, GS, BASE, SMAX, NSLOTS, K + 2>(d, ew, eo, vbase, e, acc);
-        } else if (d > K) {
-#pragma unroll
-            for (int g = 0; g < NQ4; ++g)
-                single4<K == 0>(ew[BASE + K], *reinterpret_cast<const float4*>(vbase + g * GS + eo[BASE + K]),
-                                &e[4 * g], &acc[4 * g]);
-        } else if constexpr (K == 0) {
-#pragma unroll
-            for (int q = 0; q < 4 * NQ4; ++q) acc[q] = pos_inf();
+        for (int p = 0; p < NP; ++p) {
+            if (p + 1 < NP)
+                ls_gather<GOFF>(eo, pofs, buf[p + 1], BASE + 2 * p + 2, 2 * p + 3 < D);
+            else if (NBASE >= 0)
+                ls_gather<NGOFF>(eo, pofs, buf[p + 1], NBASE, NBOTH);
+            const int k = BASE + 2 * p;
+            if (2 * p + 1 < D) {
+                if (p == 0)
+                    pair4<true>(ew[k], ew[k + 1], buf[p].a, buf[p].b, e, acc);
+                else
+                    pair4<false>(ew[k], ew[k + 1], buf[p].a, buf[p].b, e, acc);
+            } else {
+                if (p == 0)
+                    single4<true>(ew[k], buf[p].a, e, acc);
+                else
+                    single4<false>(ew[k], buf[p].a, e, acc);
+            }
         }
+        if constexpr (NBASE >= 0) io = buf[NP];
+    }
+}
+
+// Runs slots [0, d) of the register slice [BASE, BASE + SMAX).  d is warp-uniform and lies in
+// [LO, HI]: a binary tree of uniform branches into straight-line code (a jump table costs a
+// constant-bank load and an indirect branch per slice).
+template <int GOFF, int BASE, int LO, int HI, int NGOFF, int NBASE, bool NBOTH, int NSLOTS>
+__device__ __forceinline__ void ls_run_slots(int d, const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS],
+                                             uint32_t pofs, const float (&e)[4], float (&acc)[4], LsPair& io) {
+    static_assert(HI <= 8, "at most 8 slots per rank");
+    if constexpr (LO == HI) {
+        ls_fixed<GOFF, BASE, LO, NGOFF, NBASE, NBOTH, NSLOTS>(ew, eo, pofs, e, acc, io);
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (d <= MID)
+            ls_run_slots<GOFF, BASE, LO, MID, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, e, acc, io);
+        else
+            ls_run_slots<GOFF, BASE, MID + 1, HI, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, e, acc, io);
     }
 }
 
@@ -174,6 +213,7 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
              int32_t* __restrict__ arg, unsigned* __restrict__ counter) {
     constexpr int Q = 4 * NQ4;
     constexpr int NW = TPG / 32;
+    constexpr int MW = NW - 1; // manager warp: the one K0 gives the fewest slots
     constexpr int NL = SH::total();
     constexpr int NSL = NL + NH * HS;
     constexpr int RS = SV_LS_RSTRIDE;
@@ -191,7 +231,9 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     __shared__ float s_bv[NW];
     __shared__ int s_bi[NW];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // provably warp-uniform (uniform registers / uniform branches for everything derived from it)
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const unsigned long long* __restrict__ sym64 = static_cast<const unsigned long long*>(s.sym);
     const int nranks = m.ranks;
     const int n_pad = m.n_pad;
@@ -212,17 +254,18 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 
+    const uint32_t sbase = static_cast<uint32_t>(__cvta_generic_to_shared(smem_raw));
     float ew[NSL];
     uint32_t eo[NSL];
 #pragma unroll
     for (int k = 0; k < NSL; ++k) {
         ew[k] = m.edge_w[static_cast<size_t>(k) * TPG + tid];
-        eo[k] = m.edge_off[static_cast<size_t>(k) * TPG + tid];
+        eo[k] = m.edge_off[static_cast<size_t>(k) * TPG + tid] + sbase; // absolute address in buffer 0
     }
     uint32_t degs = 0; // 4 bits per rank
 #pragma unroll
     for (int r = 0; r < SV_ES_RMAX; ++r) degs |= static_cast<uint32_t>(m.deg[warp * SV_ES_RMAX + r]) << (4 * r);
-    const uint32_t own16 = static_cast<uint32_t>(tid) * 16u;
+    const uint32_t own_s = sbase + static_cast<uint32_t>(tid) * 16u; // own row of rank 0, group 0, buffer 0
 
     // Hands new sequences to the manager lanes in `mask` and patches the control block of the
     // coming step (fresh: overwrite it).  Called by all lanes of warp 0.
@@ -269,115 +312,36 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         }
         __syncwarp();
     };
-    if (warp == 0) refill((1u << Q) - 1u, ctl[0], true);
+    if (warp == MW) refill((1u << Q) - 1u, ctl[0], true);
     __syncthreads();
 
-    // One time step.  B = parity of the step = index of the score buffer that is read and of the
-    // control block that is consumed; everything addressed through B is a compile-time constant.
-    auto step_body = [&](auto bc) -> bool {
-        constexpr int B = decltype(bc)::value;
-        const unsigned char* vc = smem_raw + B * BS;
-        unsigned char* vn = smem_raw + (1 - B) * BS;
-        const LsCtl& c = ctl[B];
-        if (c.any_act == 0) return false;
+    // Time loop.  par = parity of the step = index of the score buffer that is read and of the
+    // control block that is consumed (a uniform register: addresses stay reg + ureg + imm).
+    uint32_t par = 0;
+    for (;;) {
+        const uint32_t pofs = par * BS;
+        unsigned char* vn = smem_raw + (par ^ 1u) * BS;
+        // first gathers of the step (group 0, rank 0, slots 0-1) go out before anything else
+        LsPair io;
+        ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2);
+        const LsCtl& c = ctl[par];
+        if (c.any_act == 0) break;
         const uint32_t init_mask = c.init_mask, fin_mask = c.fin_mask;
-
-        // ---- emission scores of this step: E[o_q][own row of every rank] from tensor memory ----
-        uint32_t et[Q][5];
+        uint32_t col[Q];
         {
-            uint32_t col[Q];
             const uint4 c0 = *reinterpret_cast<const uint4*>(&c.col[0]);
             col[0] = c0.x; col[1] = c0.y; col[2] = c0.z; col[3] = c0.w;
             if constexpr (NQ4 == 2) {
                 const uint4 c1 = *reinterpret_cast<const uint4*>(&c.col[4]);
                 col[4] = c1.x; col[5] = c1.y; col[6] = c1.z; col[7] = c1.w;
             }
-            if (nranks == 5) {
 #pragma unroll
-                for (int q = 0; q < Q; ++q) tmem_ld5(tE + col[q], et[q]);
-            } else {
-#pragma unroll
-                for (int q = 0; q < Q; ++q) tmem_ld4(tE + col[q], et[q]);
-            }
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-            for (int q = 0; q < Q; ++q) // ties the loaded registers to the wait above
-                asm volatile("" : "+r"(et[q][0]), "+r"(et[q][1]), "+r"(et[q][2]), "+r"(et[q][3]), "+r"(et[q][4]));
+            for (int q = 0; q < Q; ++q) col[q] += tE;
         }
 
-        // ---- light rows ----
-        auto rank_step = [&](auto rc) {
-            constexpr int r = decltype(rc)::value;
-            if (r < nranks) {
-                float e[Q], acc[Q];
-#pragma unroll
-                for (int q = 0; q < Q; ++q) e[q] = __uint_as_float(et[q][r]);
-                ls_run_slots<NQ4, GS, SH::base(r), SH::at(r), NSL>(static_cast<int>((degs >> (4 * r)) & 15u), ew,
-                                                                   eo, vc, e, acc);
-                if (init_mask != 0) {
-                    const float st = m.start_p[tid + r * TPG];
-#pragma unroll
-                    for (int q = 0; q < Q; ++q)
-                        if ((init_mask >> q) & 1u) acc[q] = e[q] + st; // v_0 = E[o_0] + start
-                }
-#pragma unroll
-                for (int g = 0; g < NQ4; ++g)
-                    *reinterpret_cast<float4*>(vn + g * GS + r * TPG * 16 + own16) =
-                        make_float4(acc[4 * g], acc[4 * g + 1], acc[4 * g + 2], acc[4 * g + 3]);
-            }
-        };
-        rank_step(std::integral_constant<int, 0>{});
-        rank_step(std::integral_constant<int, 1>{});
-        rank_step(std::integral_constant<int, 2>{});
-        rank_step(std::integral_constant<int, 3>{});
-        rank_step(std::integral_constant<int, 4>{});
-
-        // ---- heavy rows: every thread relaxes a slice, block-wide min ----
-        if constexpr (NH > 0) {
-            if (m.n_heavy > 0) {
-                auto heavy_step = [&](auto hc) {
-                    constexpr int h = decltype(hc)::value;
-                    if (h < m.n_heavy) {
-                        const int ph = m.n_lpad + h;
-                        float he[Q], acc[Q];
-#pragma unroll
-                        for (int q = 0; q < Q; ++q)
-                            he[q] = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + ph];
-                        ls_run_slots<NQ4, GS, NL + h * HS, HS, NSL>(m.heavy_slots[h], ew, eo, vc, he, acc);
-#pragma unroll
-                        for (int q = 0; q < Q; ++q) {
-#pragma unroll
-                            for (int d = 16; d > 0; d >>= 1)
-                                acc[q] = fminf(acc[q], __shfl_xor_sync(0xffffffffu, acc[q], d));
-                        }
-                        if (lane == 0) {
-#pragma unroll
-                            for (int q = 0; q < Q; ++q) red[(h * NW + warp) * Q + q] = acc[q];
-                        }
-                    }
-                };
-                heavy_step(std::integral_constant<int, 0>{});
-                if constexpr (NH > 1) heavy_step(std::integral_constant<int, 1>{});
-                __syncthreads();
-                if (warp < m.n_heavy) {
-                    // lane l: sequence q = l / LPQ, partials of warps (l % LPQ) + j * LPQ
-                    constexpr int LPQ = 32 / Q;
-                    const int h = warp, q = lane / LPQ, ph = m.n_lpad + h;
-                    float x = pos_inf();
-                    for (int w = lane % LPQ; w < NW; w += LPQ) x = fminf(x, red[(h * NW + w) * Q + q]);
-#pragma unroll
-                    for (int d = LPQ / 2; d > 0; d >>= 1) x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
-                    if ((init_mask >> q) & 1u)
-                        x = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + ph] + m.start_p[ph];
-                    if (lane % LPQ == 0)
-                        reinterpret_cast<float*>(vn + (q >> 2) * GS + ph * 16)[q & 3] = x;
-                }
-            }
-        }
-
-        // ---- managers: publish the control block of the next step ----
-        if (warp == 0) {
-            LsCtl& nx = ctl[1 - B];
+        // ---- managers first (off the tail of the step): control block of the NEXT step ----
+        if (warp == MW) {
+            LsCtl& nx = ctl[par ^ 1u];
             bool cont = false, last = false;
             uint32_t colv = 0;
             if (lane < Q) {
@@ -404,6 +368,114 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 nx.init_mask = 0;
                 nx.fin_mask = lastm;
                 nx.any_act = contm;
+            }
+        }
+
+        // ---- light rows, one float4 group of 4 sequences at a time: slices (g, r) in order
+        //      (0,0) (0,1) .. (0,4) (1,0) ..; E[o_q][own rows] of a group = 8 tensor-memory loads,
+        //      those of group 1 are issued before the last slice of group 0 ----
+        uint32_t et[NQ4][4][5];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tmem_ld5(col[j], et[0][j]);
+        const uint32_t ownn = own_s + (pofs ^ BS); // own row, rank 0, group 0 of the buffer being written
+        auto slice_step = [&](auto gc, auto rc) {
+            constexpr int g = decltype(gc)::value;
+            constexpr int r = decltype(rc)::value;
+            constexpr int i = g * SH::R + r; // slice index
+            constexpr bool has_next = i + 1 < NQ4 * SH::R;
+            constexpr int ng = (i + 1) / SH::R, nr = (i + 1) % SH::R;
+            if constexpr (r == 0) {
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 4; ++j) // ties the loaded registers to the wait above
+                    asm volatile("" : "+r"(et[g][j][0]), "+r"(et[g][j][1]), "+r"(et[g][j][2]), "+r"(et[g][j][3]),
+                                 "+r"(et[g][j][4]));
+            }
+            if constexpr (r == SH::R - 1 && g + 1 < NQ4) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) tmem_ld5(col[4 * (g + 1 < NQ4 ? g + 1 : 0) + j], et[g + 1 < NQ4 ? g + 1 : 0][j]);
+            }
+            float e[4], acc[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) e[j] = __uint_as_float(et[g][j][r]);
+            ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), (has_next ? ng : 0) * GS, (has_next ? SH::base(nr) : -1),
+                         (SH::at(nr) >= 2), NSL>(static_cast<int>((degs >> (4 * r)) & 15u), ew, eo, pofs, e, acc, io);
+            if (r < nranks) sts128<g * GS + r * TPG * 16>(ownn, acc);
+        };
+        auto group_step = [&](auto gc) {
+            slice_step(gc, std::integral_constant<int, 0>{});
+            slice_step(gc, std::integral_constant<int, 1>{});
+            slice_step(gc, std::integral_constant<int, 2>{});
+            slice_step(gc, std::integral_constant<int, 3>{});
+            slice_step(gc, std::integral_constant<int, 4>{});
+        };
+        group_step(std::integral_constant<int, 0>{});
+        if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
+
+        // ---- rare: first step of a sequence, v_0 = E[o_0] + start overwrites the relaxed scores
+        //      (same thread, program order) -- kept out of the hot path as a real branch ----
+        if (init_mask != 0) {
+#pragma unroll 1
+            for (int r = 0; r < nranks; ++r) {
+                const int p = r * TPG + tid;
+                const float st = m.start_p[p];
+#pragma unroll 1
+                for (int q = 0; q < Q; ++q) {
+                    if (!((init_mask >> q) & 1u)) continue;
+                    const float ev = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + p];
+                    reinterpret_cast<float*>(vn + (q >> 2) * GS + p * 16)[q & 3] = ev + st;
+                }
+            }
+        }
+
+        // ---- heavy rows: every thread relaxes a slice, block-wide min ----
+        if constexpr (NH > 0) {
+            if (m.n_heavy > 0) {
+                auto heavy_step = [&](auto hc, auto gc) {
+                    constexpr int h = decltype(hc)::value;
+                    constexpr int g = decltype(gc)::value;
+                    if (h < m.n_heavy) {
+                        const int ph = m.n_lpad + h;
+                        float he[4], acc[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            he[j] = m.emis_p[static_cast<size_t>(c.col[4 * g + j] / RS) * n_pad + ph];
+                        LsPair hio;
+                        ls_gather<g * GS>(eo, pofs, hio, NL + h * HS, HS >= 2);
+                        ls_run_slots<g * GS, NL + h * HS, 0, HS, 0, -1, false, NSL>(m.heavy_slots[h], ew, eo, pofs, he, acc, hio);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                            for (int d = 16; d > 0; d >>= 1)
+                                acc[j] = fminf(acc[j], __shfl_xor_sync(0xffffffffu, acc[j], d));
+                        }
+                        if (lane == 0) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) red[(h * NW + warp) * Q + 4 * g + j] = acc[j];
+                        }
+                    }
+                };
+                heavy_step(std::integral_constant<int, 0>{}, std::integral_constant<int, 0>{});
+                if constexpr (NQ4 == 2) heavy_step(std::integral_constant<int, 0>{}, std::integral_constant<int, 1>{});
+                if constexpr (NH > 1) {
+                    heavy_step(std::integral_constant<int, 1>{}, std::integral_constant<int, 0>{});
+                    if constexpr (NQ4 == 2)
+                        heavy_step(std::integral_constant<int, 1>{}, std::integral_constant<int, 1>{});
+                }
+                __syncthreads();
+                if (warp < m.n_heavy) {
+                    // lane l: sequence q = l / LPQ, partials of warps (l % LPQ) + j * LPQ
+                    constexpr int LPQ = 32 / Q;
+                    const int h = warp, q = lane / LPQ, ph = m.n_lpad + h;
+                    float x = pos_inf();
+                    for (int w = lane % LPQ; w < NW; w += LPQ) x = fminf(x, red[(h * NW + w) * Q + q]);
+#pragma unroll
+                    for (int d = LPQ / 2; d > 0; d >>= 1) x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
+                    if ((init_mask >> q) & 1u)
+                        x = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + ph] + m.start_p[ph];
+                    if (lane % LPQ == 0)
+                        reinterpret_cast<float*>(vn + (q >> 2) * GS + ph * 16)[q & 3] = x;
+                }
             }
         }
         __syncthreads();
@@ -461,15 +533,10 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     __syncthreads();
                 }
             }
-            if (warp == 0) refill(fin_mask, ctl[1 - B], false);
+            if (warp == MW) refill(fin_mask, ctl[par ^ 1u], false);
             __syncthreads();
         }
-        return true;
-    };
-
-    for (;;) {
-        if (!step_body(std::integral_constant<int, 0>{})) break;
-        if (!step_body(std::integral_constant<int, 1>{})) break;
+        par ^= 1u;
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -482,12 +549,17 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 // ------------------------------------------------------------- variant table ----
 namespace {
 
+using LsSparseT = LShape<8, 4, 3, 2, 1>; // random sparse models, tight staircase (chmm_gen k = 3)
+using LsSparseM = LShape<8, 5, 4, 3, 2>;
 using LsSparse = LShape<8, 6, 5, 4, 3>;  // random sparse models (in-degree capped at 8)
 using LsProfile = LShape<4, 3, 3, 2, 2>; // profile HMMs: <= 2 in-edges per light row + 2 dense rows
 
-// order = order of preference in sv_ls_build_plan
+// order = order of preference in sv_ls_build_plan: fewer register slots first (the registers a
+// tighter staircase frees hold gathers in flight)
 const SvLsVariant kLsVariants[] = {
     // threads, nq4, shape, nh, hs
+    {512, 2, {8, 4, 3, 2, 1}, 0, 0},
+    {512, 2, {8, 5, 4, 3, 2}, 0, 0},
     {512, 2, {8, 6, 5, 4, 3}, 0, 0},
     {512, 2, {4, 3, 3, 2, 2}, 2, 5},
     {512, 1, {8, 6, 5, 4, 3}, 0, 0},
@@ -497,10 +569,12 @@ constexpr int kNumLsVariants = sizeof(kLsVariants) / sizeof(kLsVariants[0]);
 
 const void* ls_variant_fn(int index) {
     switch (index) {
-    case 0: return (const void*)sv_ls_kernel<512, 2, LsSparse, 0, 0>;
-    case 1: return (const void*)sv_ls_kernel<512, 2, LsProfile, 2, 5>;
-    case 2: return (const void*)sv_ls_kernel<512, 1, LsSparse, 0, 0>;
-    case 3: return (const void*)sv_ls_kernel<512, 1, LsProfile, 2, 5>;
+    case 0: return (const void*)sv_ls_kernel<512, 2, LsSparseT, 0, 0>;
+    case 1: return (const void*)sv_ls_kernel<512, 2, LsSparseM, 0, 0>;
+    case 2: return (const void*)sv_ls_kernel<512, 2, LsSparse, 0, 0>;
+    case 3: return (const void*)sv_ls_kernel<512, 2, LsProfile, 2, 5>;
+    case 4: return (const void*)sv_ls_kernel<512, 1, LsSparse, 0, 0>;
+    case 5: return (const void*)sv_ls_kernel<512, 1, LsProfile, 2, 5>;
     default: return nullptr;
     }
 }
