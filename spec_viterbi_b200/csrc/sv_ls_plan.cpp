@@ -121,16 +121,34 @@ struct Colouring {
     std::vector<uint16_t> cnt;      // [octets][8]
     std::vector<uint16_t> hrefs;    // [octets][n_heavy] readers of heavy source h in the octet
     int64_t cost = 0;               // sum over (octet, colour) of max(0, cnt - D)
+    std::vector<uint32_t> hot;      // over-full (octet, colour) cells, as octet * 8 + colour
+    std::vector<int32_t> hot_at;    // [octets * 8] index into hot, -1 = not over-full
 
     int octetD(int oct) const { return cellD[oct >> 2]; }
     void bump(int oct, int col, int delta) {
         uint16_t& c = cnt[static_cast<size_t>(oct) * 8 + col];
         const int D = octetD(oct);
+        const uint32_t cell = static_cast<uint32_t>(oct) * 8u + static_cast<uint32_t>(col);
         if (delta > 0) {
-            if (c >= D) ++cost;
+            if (c >= D) {
+                ++cost;
+                if (c == D && !hot_at.empty()) { // becomes over-full
+                    hot_at[cell] = static_cast<int32_t>(hot.size());
+                    hot.push_back(cell);
+                }
+            }
             ++c;
         } else {
-            if (c > D) --cost;
+            if (c > D) {
+                --cost;
+                if (c == D + 1 && !hot_at.empty()) { // no longer over-full: swap-remove
+                    const int32_t k = hot_at[cell];
+                    hot_at[hot.back()] = k;
+                    hot[static_cast<size_t>(k)] = hot.back();
+                    hot.pop_back();
+                    hot_at[cell] = -1;
+                }
+            }
             --c;
         }
     }
@@ -176,6 +194,82 @@ void swap_positions(Colouring& c, uint32_t pa, uint32_t pb, std::vector<uint32_t
     for (const uint32_t e : scratch) c.apply_edge(e, +1);
 }
 
+// Cost change of swapping the rows at positions pa and pb, evaluated WITHOUT touching the
+// counters (most proposals are rejected).  Only for graphs without heavy sources.  Fills
+// cells/deltas (merged per cell) so that an accepted move can be applied directly.
+struct SwapDelta {
+    static constexpr int kMax = 96;
+    uint32_t cell[kMax];
+    int16_t dv[kMax];
+    int n = 0;
+    bool overflow = false;
+    void add(uint32_t c, int d) {
+        for (int i = 0; i < n; ++i)
+            if (cell[i] == c) {
+                dv[i] = static_cast<int16_t>(dv[i] + d);
+                return;
+            }
+        if (n == kMax) {
+            overflow = true;
+            return;
+        }
+        cell[n] = c;
+        dv[n++] = static_cast<int16_t>(d);
+    }
+};
+
+int64_t swap_delta(const Colouring& c, uint32_t pa, uint32_t pb, SwapDelta& sd) {
+    const LGraph& g = *c.g;
+    const int32_t a = c.at_pos[pa], b = c.at_pos[pb];
+    sd.n = 0;
+    sd.overflow = false;
+    auto newpos = [&](uint32_t y) -> uint32_t {
+        if (static_cast<int32_t>(y) == a) return pb;
+        if (static_cast<int32_t>(y) == b) return pa;
+        return c.pos_of[y];
+    };
+    for (int k = 0; k < 2; ++k) {
+        const int32_t x = k == 0 ? a : b;
+        if (x < 0) continue;
+        const uint32_t px = k == 0 ? pa : pb, nx = k == 0 ? pb : pa;
+        // x as destination: all its in-edges (both endpoints at their new positions)
+        for (const uint32_t e : g.in[x]) {
+            const uint32_t s = g.edges[e].src;
+            sd.add((px >> 3) * 8u + (c.pos_of[s] & 7u), -1);
+            sd.add((nx >> 3) * 8u + (newpos(s) & 7u), +1);
+        }
+        // x as source: out-edges to rows that do not move themselves
+        for (const uint32_t e : g.out[x]) {
+            const uint32_t t = g.edges[e].dst;
+            if (static_cast<int32_t>(t) == a || static_cast<int32_t>(t) == b) continue;
+            const uint32_t ot = c.pos_of[t] >> 3;
+            sd.add(ot * 8u + (px & 7u), -1);
+            sd.add(ot * 8u + (nx & 7u), +1);
+        }
+    }
+    int64_t delta = 0;
+    for (int i = 0; i < sd.n; ++i) {
+        if (sd.dv[i] == 0) continue;
+        const int D = c.octetD(static_cast<int>(sd.cell[i] >> 3));
+        const int c0 = c.cnt[sd.cell[i]], c1 = c0 + sd.dv[i];
+        delta += std::max(0, c1 - D) - std::max(0, c0 - D);
+    }
+    return delta;
+}
+
+void apply_swap_delta(Colouring& c, uint32_t pa, uint32_t pb, const SwapDelta& sd) {
+    for (int i = 0; i < sd.n; ++i) {
+        const int oct = static_cast<int>(sd.cell[i] >> 3), colr = static_cast<int>(sd.cell[i] & 7u);
+        for (int d = sd.dv[i]; d > 0; --d) c.bump(oct, colr, +1);
+        for (int d = sd.dv[i]; d < 0; ++d) c.bump(oct, colr, -1);
+    }
+    const int32_t a = c.at_pos[pa], b = c.at_pos[pb];
+    c.at_pos[pa] = b;
+    c.at_pos[pb] = a;
+    if (a >= 0) c.pos_of[a] = pb;
+    if (b >= 0) c.pos_of[b] = pa;
+}
+
 // Simulated annealing over position swaps; keeps every row inside a cell whose trip count
 // covers its in-degree.  Deterministic (fixed seed).
 void anneal(Colouring& c, uint64_t iters, uint64_t seed) {
@@ -183,29 +277,35 @@ void anneal(Colouring& c, uint64_t iters, uint64_t seed) {
     if (c.cost == 0 || iters == 0) return;
     Rng rng(seed);
     std::vector<uint32_t> scratch;
+    SwapDelta sd;
     const uint32_t npos = static_cast<uint32_t>(c.n_lpad);
-    const uint32_t nedges = static_cast<uint32_t>(g.edges.size());
     auto degree = [&](int32_t x) { return x < 0 ? size_t(0) : g.in[x].size(); };
-    const double t0 = 0.6, t1 = 0.03;
+    double t0 = 0.6, t1 = 0.03;
+    if (const char* e0 = std::getenv("SV_LS_SA_T0")) t0 = std::atof(e0);
+    if (const char* e1 = std::getenv("SV_LS_SA_T1")) t1 = std::atof(e1);
+    double temp = t0;
     for (uint64_t it = 0; it < iters && c.cost > 0; ++it) {
-        const double temp = t0 * std::pow(t1 / t0, static_cast<double>(it) / static_cast<double>(iters));
-        // pick a row to move: the source of an edge sitting in an over-full (octet, colour)
+        if ((it & 255u) == 0) temp = t0 * std::pow(t1 / t0, static_cast<double>(it) / static_cast<double>(iters));
+        // pick a row to move: an end of an edge sitting in an over-full (octet, colour), taken
+        // from the explicit list of over-full cells (every iteration is a useful attempt)
         uint32_t pa;
-        {
-            const uint32_t e = rng.below(nedges);
-            const LEdge& ed = g.edges[e];
-            bool hot = false;
-            if (!g.heavy[ed.dst] && !g.heavy[ed.src]) {
-                const int oct = static_cast<int>(c.pos_of[ed.dst] >> 3);
-                const int col = static_cast<int>(c.pos_of[ed.src] & 7u);
-                hot = c.cnt[static_cast<size_t>(oct) * 8 + col] > c.octetD(oct);
+        if ((rng.next() & 15u) != 0 && !c.hot.empty()) {
+            const uint32_t cell = c.hot[rng.below(static_cast<uint32_t>(c.hot.size()))];
+            const uint32_t oct = cell >> 3, colr = cell & 7u;
+            uint32_t cand[64];
+            uint32_t nc = 0;
+            for (uint32_t l = 0; l < 8; ++l) {
+                const int32_t row = c.at_pos[oct * 8 + l];
+                if (row < 0) continue;
+                for (const uint32_t e : g.in[row])
+                    if ((c.pos_of[g.edges[e].src] & 7u) == colr && nc < 64) cand[nc++] = e;
             }
-            if (hot) {
-                pa = (rng.next() & 1u) ? c.pos_of[ed.src] : c.pos_of[ed.dst];
-            } else {
-                if ((rng.next() & 7u) != 0) continue;
-                pa = rng.below(npos);
-            }
+            if (nc == 0) continue;
+            const LEdge& ed = g.edges[cand[rng.below(nc)]];
+            pa = (rng.next() & 3u) ? c.pos_of[ed.src] : c.pos_of[ed.dst];
+            if (pa >= npos) continue; // heavy source: not movable
+        } else {
+            pa = rng.below(npos);
         }
         // partner: same octet (pure recolouring) half of the time, anywhere otherwise
         uint32_t pb;
@@ -218,6 +318,14 @@ void anneal(Colouring& c, uint64_t iters, uint64_t seed) {
         const int32_t a = c.at_pos[pa], b = c.at_pos[pb];
         if (a < 0 && b < 0) continue;
         if (degree(a) > c.cellD[pb >> 5] || degree(b) > c.cellD[pa >> 5]) continue;
+        if (c.n_heavy == 0) {
+            const int64_t delta = swap_delta(c, pa, pb, sd);
+            if (!sd.overflow) {
+                if (delta <= 0 || rng.unit() < std::exp(-static_cast<double>(delta) / temp))
+                    apply_swap_delta(c, pa, pb, sd);
+                continue;
+            }
+        }
         const int64_t before = c.cost;
         swap_positions(c, pa, pb, scratch);
         const int64_t delta = c.cost - before;
@@ -385,13 +493,33 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
             if (!g.heavy[i]) light.push_back(i);
         std::stable_sort(light.begin(), light.end(),
                          [&](uint32_t a, uint32_t b) { return g.in[a].size() > g.in[b].size(); });
-        for (size_t k = 0; k < light.size(); ++k) {
-            const int r = static_cast<int>(k / TPG);
-            const int c = static_cast<int>((k % TPG) / 32);
-            const int w = (r % 2 == 0) ? c : NW - 1 - c;
-            const uint32_t p = static_cast<uint32_t>(r * TPG + w * 32 + static_cast<int>(k % 32));
-            col.pos_of[light[k]] = p;
-            col.at_pos[p] = static_cast<int32_t>(light[k]);
+        // cells of 32 consecutive rows of the degree-sorted list; the 16 cells of a rank are dealt
+        // to the warps so that the per-warp slot totals stay level (heaviest cell -> lightest warp):
+        // the step ends when the slowest warp reaches the barrier.  The manager warp (the last
+        // one) starts with one slot of handicap for its bookkeeping.
+        std::vector<int> load(NW, 0);
+        load[NW - 1] = 1;
+        for (int r = 0; r * static_cast<size_t>(TPG) < light.size(); ++r) {
+            std::vector<int> cellD(NW, 0), cells(NW), warps(NW);
+            for (int c = 0; c < NW; ++c) {
+                const size_t k0 = static_cast<size_t>(r) * TPG + static_cast<size_t>(c) * 32;
+                cellD[c] = k0 < light.size() ? static_cast<int>(g.in[light[k0]].size()) : 0;
+                cells[c] = c;
+                warps[c] = c;
+            }
+            std::stable_sort(cells.begin(), cells.end(), [&](int a, int b) { return cellD[a] > cellD[b]; });
+            std::stable_sort(warps.begin(), warps.end(), [&](int a, int b) { return load[a] < load[b]; });
+            for (int i = 0; i < NW; ++i) {
+                const int c = cells[i], w = warps[i];
+                load[w] += cellD[c];
+                for (int l = 0; l < 32; ++l) {
+                    const size_t k = static_cast<size_t>(r) * TPG + static_cast<size_t>(c) * 32 + l;
+                    if (k >= light.size()) break;
+                    const uint32_t p = static_cast<uint32_t>(r * TPG + w * 32 + l);
+                    col.pos_of[light[k]] = p;
+                    col.at_pos[p] = static_cast<int32_t>(light[k]);
+                }
+            }
         }
         for (size_t h = 0; h < n_heavy; ++h) col.pos_of[heavy_rows[h]] = static_cast<uint32_t>(n_lpad + h);
     }
@@ -414,6 +542,8 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     col.cnt.assign(static_cast<size_t>(n_lpad / 8) * 8, 0);
     col.hrefs.assign(static_cast<size_t>(n_lpad / 8) * std::max<size_t>(n_heavy, 1), 0);
     col.cost = 0;
+    col.hot.clear();
+    col.hot_at.assign(col.cnt.size(), -1);
     for (uint32_t e = 0; e < g.edges.size(); ++e) col.apply_edge(e, +1);
     plan->colour_cost_before = static_cast<uint64_t>(col.cost);
     anneal(col, sa_iters, 0x5eed0000ull + n * 131u + vindex);
@@ -549,7 +679,7 @@ void sv_ls_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->valid = false;
     int want_nq4 = 0;
     if (const char* env = std::getenv("SV_LS_NQ4")) want_nq4 = std::atoi(env);
-    uint64_t sa_iters = std::min<uint64_t>(6000000ull, 2500ull * csr.n);
+    uint64_t sa_iters = std::min<uint64_t>(8000000ull, 3300ull * csr.n);
     if (const char* env = std::getenv("SV_LS_SA_ITERS")) sa_iters = std::strtoull(env, nullptr, 10);
     // variants are listed in order of preference; the first that fits wins
     for (int v = 0; v < sv_ls_num_variants(); ++v) {
