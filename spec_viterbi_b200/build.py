@@ -65,6 +65,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
                "-c", str(PKG / s), "-o", str(obj)]
         if verbose:
             cmd += ["-Xptxas", "-v"]
+        cmd += os.environ.get("SV_NVCC_EXTRA", "").split()  # e.g. -DSV_LS_DEBUG (instrumented build)
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(str(obj))
     failed = False

@@ -499,6 +499,7 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
         // one) starts with one slot of handicap for its bookkeeping.
         std::vector<int> load(NW, 0);
         load[NW - 1] = 1;
+        if (const char* env = std::getenv("SV_LS_MGR_HANDICAP")) load[NW - 1] = std::atoi(env);
         for (int r = 0; r * static_cast<size_t>(TPG) < light.size(); ++r) {
             std::vector<int> cellD(NW, 0), cells(NW), warps(NW);
             for (int c = 0; c < NW; ++c) {

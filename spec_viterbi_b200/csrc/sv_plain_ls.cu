@@ -73,6 +73,39 @@ __device__ __forceinline__ void sts128(uint32_t addr, const float (&a)[4]) {
                  "f"(a[3])
                  : "memory");
 }
+// ---- split-phase CTA barriers (one per float4 group): arrive after the group's stores, wait
+//      only before the group's buffer is gathered again -- one whole phase later ----
+__device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t addr) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(addr) : "memory");
+}
+#ifdef SV_LS_DEBUG
+__device__ unsigned long long g_ls_dbg[148 * 16 * 4];
+__device__ unsigned long long g_ls_trace[16 * 8 * 8];
+#define SV_TRACE(ev)                                                                                   \
+    do {                                                                                               \
+        if (blockIdx.x == 5 && lane == 0 && tau >= 1000 && tau < 1008)                                  \
+            g_ls_trace[(warp * 8 + (tau - 1000)) * 8 + (ev)] = clock64();                              \
+    } while (0)
+#define SV_DBG_T0() const long long dbg_t0 = clock64()
+#define SV_DBG_ACC(x) (x) += clock64() - dbg_t0
+#else
+#define SV_DBG_T0()
+#define SV_DBG_ACC(x)
+#define SV_TRACE(ev)
+#endif
+__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done)
+                     : "r"(addr), "r"(parity)
+                     : "memory");
+    } while (done == 0);
+}
+
 // Per-step control block published by the manager lanes.
 struct alignas(16) LsCtl {
     uint32_t col[8];    // TMEM column offset of each sequence's current symbol: symbol * RSTRIDE
@@ -82,12 +115,12 @@ struct alignas(16) LsCtl {
     uint32_t pad;
 };
 
-// Sequence-manager state of one sequence slot (owned by lane q of warp 0, kept in shared memory
-// so that it does not occupy registers in all 512 threads).
-struct alignas(16) LsMgr {
-    unsigned long long cur, nxt; // packed symbol words: current and next 8 symbols
-    unsigned long long idx;      // index of the NEXT step's symbol in the packed array
-    uint32_t t, len, sid, act;
+// Sequence-manager state of one sequence slot lives in REGISTERS of lane q of the manager warp:
+// under load a shared-memory round trip takes hundreds of cycles (the crossbar queue is deep), and
+// a manager that chases its state through shared memory falls a thousand cycles behind the other
+// warps every step.  Only the sequence id (needed on the rare write-out path) is kept in memory.
+struct LsMgr {
+    uint32_t sid;
 };
 
 // fl(fl(E + T') + v) -- the two adds are never re-associated (GraphBLAS_impl.cpp:65,69)
@@ -153,11 +186,11 @@ __device__ __forceinline__ void ls_gather(const uint32_t (&eo)[NSLOTS], uint32_t
 // `io` holds this slice's first pair on entry and the next slice's first pair on exit.
 template <int GOFF, int BASE, int D, int NGOFF, int NBASE, bool NBOTH, int NSLOTS>
 __device__ __forceinline__ void ls_fixed(const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS], uint32_t pofs,
-                                         const float (&e)[4], float (&acc)[4], LsPair& io) {
+                                         uint32_t npofs, const float (&e)[4], float (&acc)[4], LsPair& io) {
     if constexpr (D == 0) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) acc[q] = pos_inf();
-        if constexpr (NBASE >= 0) ls_gather<NGOFF>(eo, pofs, io, NBASE, NBOTH);
+        if constexpr (NBASE >= 0) ls_gather<NGOFF>(eo, npofs, io, NBASE, NBOTH);
     } else {
         constexpr int NP = (D + 1) / 2;
         LsPair buf[NP + 1];
@@ -167,7 +200,7 @@ __device__ __forceinline__ void ls_fixed(const float (&ew)[NSLOTS], const uint32
             if (p + 1 < NP)
                 ls_gather<GOFF>(eo, pofs, buf[p + 1], BASE + 2 * p + 2, 2 * p + 3 < D);
             else if (NBASE >= 0)
-                ls_gather<NGOFF>(eo, pofs, buf[p + 1], NBASE, NBOTH);
+                ls_gather<NGOFF>(eo, npofs, buf[p + 1], NBASE, NBOTH);
             const int k = BASE + 2 * p;
             if (2 * p + 1 < D) {
                 if (p == 0)
@@ -190,16 +223,17 @@ __device__ __forceinline__ void ls_fixed(const float (&ew)[NSLOTS], const uint32
 // constant-bank load and an indirect branch per slice).
 template <int GOFF, int BASE, int LO, int HI, int NGOFF, int NBASE, bool NBOTH, int NSLOTS>
 __device__ __forceinline__ void ls_run_slots(int d, const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS],
-                                             uint32_t pofs, const float (&e)[4], float (&acc)[4], LsPair& io) {
+                                             uint32_t pofs, uint32_t npofs, const float (&e)[4], float (&acc)[4],
+                                             LsPair& io) {
     static_assert(HI <= 8, "at most 8 slots per rank");
     if constexpr (LO == HI) {
-        ls_fixed<GOFF, BASE, LO, NGOFF, NBASE, NBOTH, NSLOTS>(ew, eo, pofs, e, acc, io);
+        ls_fixed<GOFF, BASE, LO, NGOFF, NBASE, NBOTH, NSLOTS>(ew, eo, pofs, npofs, e, acc, io);
     } else {
         constexpr int MID = (LO + HI) / 2;
         if (d <= MID)
-            ls_run_slots<GOFF, BASE, LO, MID, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, e, acc, io);
+            ls_run_slots<GOFF, BASE, LO, MID, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, npofs, e, acc, io);
         else
-            ls_run_slots<GOFF, BASE, MID + 1, HI, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, e, acc, io);
+            ls_run_slots<GOFF, BASE, MID + 1, HI, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, npofs, e, acc, io);
     }
 }
 
@@ -214,6 +248,11 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     constexpr int Q = 4 * NQ4;
     constexpr int NW = TPG / 32;
     constexpr int MW = NW - 1; // manager warp: the one K0 gives the fewest slots
+#ifdef SV_LS_NO_OVL
+    constexpr bool OVL = false;
+#else
+    constexpr bool OVL = NQ4 == 2 && NH == 0; // split-phase barriers (no block-reduced heavy rows)
+#endif
     constexpr int NL = SH::total();
     constexpr int NSL = NL + NH * HS;
     constexpr int RS = SV_LS_RSTRIDE;
@@ -225,7 +264,8 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* red = reinterpret_cast<float*>(smem_raw + 2 * BS); // [NH][NW][Q]
-    __shared__ LsCtl ctl[2];
+    __shared__ LsCtl ctl[4];
+    __shared__ __align__(8) unsigned long long mbar[2];
     __shared__ LsMgr mgr[8];
     __shared__ uint32_t s_taddr;
     __shared__ float s_bv[NW];
@@ -269,32 +309,34 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 
     // Hands new sequences to the manager lanes in `mask` and patches the control block of the
     // coming step (fresh: overwrite it).  Called by all lanes of warp 0.
+    unsigned long long mg_cur = 0, mg_nxt = 0;       // current / next 8 packed symbols
+    const unsigned long long* mg_ptr = sym64;        // word that follows mg_nxt
+    uint32_t mg_pos = 0, mg_t = 0, mg_len = 0;       // byte phase of the next symbol, local step, length (0 = idle)
     auto refill = [&](uint32_t mask, LsCtl& dst, bool fresh) {
         bool started = false, one = false;
         uint32_t colv = 0;
         if (lane < Q && ((mask >> lane) & 1u)) {
-            LsMgr g;
-            g.act = 0;
-            g.t = g.len = g.sid = 0;
-            g.cur = g.nxt = g.idx = 0;
+            mg_len = 0;
+            mg_t = 0;
+            uint32_t sid = 0;
             const unsigned w = atomicAdd(counter, 1u);
             if (w < static_cast<unsigned>(s.nseq)) {
-                g.sid = s.order[w];
-                const uint64_t b = s.off[g.sid];
-                g.len = static_cast<uint32_t>(s.off[g.sid + 1] - b);
-                g.cur = sym64[b >> 3];
-                g.nxt = sym64[(b >> 3) + 1];
-                colv = (static_cast<uint32_t>(g.cur >> ((b & 7u) * 8u)) & 0xffu) * RS;
-                g.idx = b + 1;
-                if ((g.idx & 7u) == 0) {
-                    g.cur = g.nxt;
-                    g.nxt = sym64[(g.idx >> 3) + 1];
+                sid = s.order[w];
+                const uint64_t b = s.off[sid];
+                mg_len = static_cast<uint32_t>(s.off[sid + 1] - b);
+                mg_ptr = sym64 + (b >> 3);
+                mg_cur = *mg_ptr++;
+                mg_nxt = *mg_ptr++;
+                mg_pos = static_cast<uint32_t>(b & 7u);
+                colv = (static_cast<uint32_t>(mg_cur >> (mg_pos * 8u)) & 0xffu) * RS;
+                if ((++mg_pos & 7u) == 0) {
+                    mg_cur = mg_nxt;
+                    mg_nxt = *mg_ptr++;
                 }
-                g.act = 1;
                 started = true;
-                one = g.len == 1;
+                one = mg_len == 1;
             }
-            mgr[lane] = g;
+            mgr[lane].sid = sid;
         }
         const uint32_t startm = __ballot_sync(0xffffffffu, started);
         const uint32_t onem = __ballot_sync(0xffffffffu, one);
@@ -312,19 +354,34 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         }
         __syncwarp();
     };
+    const uint32_t mbar_s = static_cast<uint32_t>(__cvta_generic_to_shared(&mbar[0]));
+    if (tid == 0) {
+        mbar_init(mbar_s, NW);
+        mbar_init(mbar_s + 8u, NW);
+    }
     if (warp == MW) refill((1u << Q) - 1u, ctl[0], true);
     __syncthreads();
 
-    // Time loop.  par = parity of the step = index of the score buffer that is read and of the
-    // control block that is consumed (a uniform register: addresses stay reg + ureg + imm).
-    uint32_t par = 0;
+    // Time loop.  tau = CTA step; par = tau & 1 = index of the score buffers that are read.
+    // The two float4 groups are two PHASES of a step with their own split barriers: a group's
+    // stores are followed by an arrive, and the matching wait sits one phase later (just before
+    // that group's scores are gathered again), so the warps of a CTA drift up to a phase apart
+    // instead of meeting at a __syncthreads every step -- the shared-memory crossbar stays busy
+    // across step boundaries.  Control blocks live in a ring of 4 for the same reason.
+    uint32_t tau = 0;
+#ifdef SV_LS_DEBUG
+    long long dbg_wa = 0, dbg_wb = 0;
+    const long long dbg_start = clock64();
+#endif
+    LsPair io;
+    if constexpr (OVL) ls_gather<0>(eo, 0u, io, 0, SH::at(0) >= 2);
     for (;;) {
+        const uint32_t par = tau & 1u;
         const uint32_t pofs = par * BS;
         unsigned char* vn = smem_raw + (par ^ 1u) * BS;
-        // first gathers of the step (group 0, rank 0, slots 0-1) go out before anything else
-        LsPair io;
-        ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2);
-        const LsCtl& c = ctl[par];
+        if constexpr (!OVL) ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2); // one barrier per step: no overlap
+        SV_TRACE(0);
+        const LsCtl& c = ctl[tau & 3u];
         if (c.any_act == 0) break;
         const uint32_t init_mask = c.init_mask, fin_mask = c.fin_mask;
         uint32_t col[Q];
@@ -341,25 +398,18 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 
         // ---- managers first (off the tail of the step): control block of the NEXT step ----
         if (warp == MW) {
-            LsCtl& nx = ctl[par ^ 1u];
+            LsCtl& nx = ctl[(tau + 1u) & 3u];
             bool cont = false, last = false;
             uint32_t colv = 0;
-            if (lane < Q) {
-                LsMgr& g = mgr[lane];
-                const uint32_t t = g.t, len = g.len;
-                if (g.act != 0 && t + 1u < len) {
-                    cont = true;
-                    unsigned long long idx = g.idx;
-                    colv = (static_cast<uint32_t>(g.cur >> ((idx & 7u) * 8u)) & 0xffu) * RS;
-                    ++idx;
-                    if ((idx & 7u) == 0) {
-                        g.cur = g.nxt;
-                        g.nxt = sym64[(idx >> 3) + 1];
-                    }
-                    g.idx = idx;
-                    last = t + 2u == len;
-                    g.t = t + 1u;
+            if (lane < Q && mg_t + 1u < mg_len) { // pure register arithmetic: no memory round trip
+                cont = true;
+                colv = (static_cast<uint32_t>(mg_cur >> ((mg_pos & 7u) * 8u)) & 0xffu) * RS;
+                if ((++mg_pos & 7u) == 0) {
+                    mg_cur = mg_nxt;     // arrived 8 steps ago
+                    mg_nxt = *mg_ptr++;  // consumed 8 steps from now: never waited for
                 }
+                last = mg_t + 2u == mg_len;
+                ++mg_t;
             }
             const uint32_t contm = __ballot_sync(0xffffffffu, cont);
             const uint32_t lastm = __ballot_sync(0xffffffffu, last);
@@ -371,6 +421,22 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
             }
         }
 
+        // ---- rare: first step of a sequence, v_0 = E[o_0] + start overwrites the relaxed scores
+        //      (same thread, program order) -- kept out of the hot path as a real branch ----
+        auto init_fix = [&](int q0, int q1) {
+#pragma unroll 1
+            for (int r = 0; r < nranks; ++r) {
+                const int p = r * TPG + tid;
+                const float st = m.start_p[p];
+#pragma unroll 1
+                for (int q = q0; q < q1; ++q) {
+                    if (!((init_mask >> q) & 1u)) continue;
+                    const float ev = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + p];
+                    reinterpret_cast<float*>(vn + (q >> 2) * GS + p * 16)[q & 3] = ev + st;
+                }
+            }
+        };
+
         // ---- light rows, one float4 group of 4 sequences at a time: slices (g, r) in order
         //      (0,0) (0,1) .. (0,4) (1,0) ..; E[o_q][own rows] of a group = 8 tensor-memory loads,
         //      those of group 1 are issued before the last slice of group 0 ----
@@ -381,9 +447,7 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         auto slice_step = [&](auto gc, auto rc) {
             constexpr int g = decltype(gc)::value;
             constexpr int r = decltype(rc)::value;
-            constexpr int i = g * SH::R + r; // slice index
-            constexpr bool has_next = i + 1 < NQ4 * SH::R;
-            constexpr int ng = (i + 1) / SH::R, nr = (i + 1) % SH::R;
+            constexpr bool last_r = r == SH::R - 1;
             if constexpr (r == 0) {
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
@@ -391,41 +455,64 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     asm volatile("" : "+r"(et[g][j][0]), "+r"(et[g][j][1]), "+r"(et[g][j][2]), "+r"(et[g][j][3]),
                                  "+r"(et[g][j][4]));
             }
-            if constexpr (r == SH::R - 1 && g + 1 < NQ4) {
+            if constexpr (last_r && g + 1 < NQ4) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) tmem_ld5(col[4 * (g + 1 < NQ4 ? g + 1 : 0) + j], et[g + 1 < NQ4 ? g + 1 : 0][j]);
+            }
+            if constexpr (OVL && r == SH::R - 2) {
+                // Split-barrier wait for the buffer the LAST slice of this phase prefetches from.  Placed
+                // one slice early, right behind this slice's own (already issued) gathers: the poll is a
+                // shared-memory-pipe round trip of hundreds of cycles under load and overlaps with them.
+                if constexpr (g == 0) {
+                    SV_DBG_T0();
+                    SV_TRACE(2);
+                    if (tau != 0) mbar_wait(mbar_s + 8u, (tau - 1u) & 1u); // group 1 scores of step tau-1 complete
+                    SV_TRACE(3);
+                    SV_DBG_ACC(dbg_wb);
+                } else {
+                    SV_DBG_T0();
+                    SV_TRACE(5);
+                    mbar_wait(mbar_s, tau & 1u); // group 0 scores of this step complete
+                    SV_TRACE(6);
+                    SV_DBG_ACC(dbg_wa);
+                }
             }
             float e[4], acc[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) e[j] = __uint_as_float(et[g][j][r]);
-            ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), (has_next ? ng : 0) * GS, (has_next ? SH::base(nr) : -1),
-                         (SH::at(nr) >= 2), NSL>(static_cast<int>((degs >> (4 * r)) & 15u), ew, eo, pofs, e, acc, io);
+            const int d = static_cast<int>((degs >> (4 * r)) & 15u);
+            if constexpr (!last_r) { // next slice: next rank of the same group
+                ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), g * GS, SH::base(last_r ? 0 : r + 1),
+                             (SH::at(last_r ? 0 : r + 1) >= 2), NSL>(d, ew, eo, pofs, pofs, e, acc, io);
+            } else if constexpr (g + 1 < NQ4) { // next slice: rank 0 of group 1, same step
+                ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), GS, 0, (SH::at(0) >= 2), NSL>(d, ew, eo, pofs, pofs, e, acc,
+                                                                                             io);
+            } else if constexpr (OVL) { // next slice: rank 0 of group 0 of the NEXT step (other buffer)
+                ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), 0, 0, (SH::at(0) >= 2), NSL>(d, ew, eo, pofs, pofs ^ BS, e,
+                                                                                            acc, io);
+            } else {
+                ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), 0, -1, false, NSL>(d, ew, eo, pofs, pofs, e, acc, io);
+            }
             if (r < nranks) sts128<g * GS + r * TPG * 16>(ownn, acc);
         };
         auto group_step = [&](auto gc) {
+            [[maybe_unused]] constexpr int g = decltype(gc)::value;
             slice_step(gc, std::integral_constant<int, 0>{});
             slice_step(gc, std::integral_constant<int, 1>{});
             slice_step(gc, std::integral_constant<int, 2>{});
             slice_step(gc, std::integral_constant<int, 3>{});
             slice_step(gc, std::integral_constant<int, 4>{});
+            if constexpr (OVL) {
+                if (init_mask != 0) init_fix(4 * g, 4 * g + 4);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(mbar_s + 8u * g);
+                SV_TRACE(g == 0 ? 4 : 7);
+            }
         };
         group_step(std::integral_constant<int, 0>{});
         if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
-
-        // ---- rare: first step of a sequence, v_0 = E[o_0] + start overwrites the relaxed scores
-        //      (same thread, program order) -- kept out of the hot path as a real branch ----
-        if (init_mask != 0) {
-#pragma unroll 1
-            for (int r = 0; r < nranks; ++r) {
-                const int p = r * TPG + tid;
-                const float st = m.start_p[p];
-#pragma unroll 1
-                for (int q = 0; q < Q; ++q) {
-                    if (!((init_mask >> q) & 1u)) continue;
-                    const float ev = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + p];
-                    reinterpret_cast<float*>(vn + (q >> 2) * GS + p * 16)[q & 3] = ev + st;
-                }
-            }
+        if constexpr (!OVL) {
+            if (init_mask != 0) init_fix(0, Q);
         }
 
         // ---- heavy rows: every thread relaxes a slice, block-wide min ----
@@ -442,7 +529,7 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                             he[j] = m.emis_p[static_cast<size_t>(c.col[4 * g + j] / RS) * n_pad + ph];
                         LsPair hio;
                         ls_gather<g * GS>(eo, pofs, hio, NL + h * HS, HS >= 2);
-                        ls_run_slots<g * GS, NL + h * HS, 0, HS, 0, -1, false, NSL>(m.heavy_slots[h], ew, eo, pofs, he, acc, hio);
+                        ls_run_slots<g * GS, NL + h * HS, 0, HS, 0, -1, false, NSL>(m.heavy_slots[h], ew, eo, pofs, pofs, he, acc, hio);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
 #pragma unroll
@@ -478,10 +565,11 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 }
             }
         }
-        __syncthreads();
+        if constexpr (!OVL) __syncthreads();
 
         // ---- rare path: write out finished sequences, hand out new ones ----
         if (fin_mask != 0) {
+            if constexpr (OVL) mbar_wait(mbar_s + 8u, tau & 1u); // (group 0 was waited for in the last slice)
             for (int q = 0; q < Q; ++q) {
                 if (!((fin_mask >> q) & 1u)) continue;
                 const uint32_t sid = mgr[q].sid;
@@ -533,12 +621,19 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     __syncthreads();
                 }
             }
-            if (warp == MW) refill(fin_mask, ctl[par ^ 1u], false);
+            __syncthreads(); // every thread is done with mgr[].sid
+            if (warp == MW) refill(fin_mask, ctl[(tau + 1u) & 3u], false);
             __syncthreads();
         }
-        par ^= 1u;
+        ++tau;
     }
 
+#ifdef SV_LS_DEBUG
+    if (lane == 0 && blockIdx.x < 148) {
+        unsigned long long* d = g_ls_dbg + (blockIdx.x * 16 + warp) * 4;
+        d[0] = dbg_wa; d[1] = dbg_wb; d[2] = clock64() - dbg_start; d[3] = tau;
+    }
+#endif
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) tmem_free(tbase, static_cast<uint32_t>(m.tmem_cols));
@@ -581,6 +676,14 @@ const void* ls_variant_fn(int index) {
 
 } // namespace
 
+#ifdef SV_LS_DEBUG
+extern "C" int sv_debug_ls_dump(unsigned long long* out) {
+    return cudaMemcpyFromSymbol(out, g_ls_dbg, sizeof(g_ls_dbg));
+}
+extern "C" int sv_debug_ls_trace(unsigned long long* out) {
+    return cudaMemcpyFromSymbol(out, g_ls_trace, sizeof(g_ls_trace));
+}
+#endif
 int sv_ls_num_variants() { return kNumLsVariants; }
 const SvLsVariant& sv_ls_variant(int index) { return kLsVariants[index]; }
 
