@@ -73,39 +73,6 @@ __device__ __forceinline__ void sts128(uint32_t addr, const float (&a)[4]) {
                  "f"(a[3])
                  : "memory");
 }
-// ---- split-phase CTA barriers (one per float4 group): arrive after the group's stores, wait
-//      only before the group's buffer is gathered again -- one whole phase later ----
-__device__ __forceinline__ void mbar_init(uint32_t addr, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t addr) {
-    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(addr) : "memory");
-}
-#ifdef SV_LS_DEBUG
-__device__ unsigned long long g_ls_dbg[148 * 16 * 4];
-__device__ unsigned long long g_ls_trace[16 * 8 * 8];
-#define SV_TRACE(ev)                                                                                   \
-    do {                                                                                               \
-        if (blockIdx.x == 5 && lane == 0 && tau >= 1000 && tau < 1008)                                  \
-            g_ls_trace[(warp * 8 + (tau - 1000)) * 8 + (ev)] = clock64();                              \
-    } while (0)
-#define SV_DBG_T0() const long long dbg_t0 = clock64()
-#define SV_DBG_ACC(x) (x) += clock64() - dbg_t0
-#else
-#define SV_DBG_T0()
-#define SV_DBG_ACC(x)
-#define SV_TRACE(ev)
-#endif
-__device__ __forceinline__ void mbar_wait(uint32_t addr, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                     : "=r"(done)
-                     : "r"(addr), "r"(parity)
-                     : "memory");
-    } while (done == 0);
-}
-
 // Per-step control block published by the manager lanes.
 struct alignas(16) LsCtl {
     uint32_t col[8];    // TMEM column offset of each sequence's current symbol: symbol * RSTRIDE
@@ -248,11 +215,6 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     constexpr int Q = 4 * NQ4;
     constexpr int NW = TPG / 32;
     constexpr int MW = NW - 1; // manager warp: the one K0 gives the fewest slots
-#ifdef SV_LS_NO_OVL
-    constexpr bool OVL = false;
-#else
-    constexpr bool OVL = NQ4 == 2 && NH == 0; // split-phase barriers (no block-reduced heavy rows)
-#endif
     constexpr int NL = SH::total();
     constexpr int NSL = NL + NH * HS;
     constexpr int RS = SV_LS_RSTRIDE;
@@ -265,7 +227,6 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* red = reinterpret_cast<float*>(smem_raw + 2 * BS); // [NH][NW][Q]
     __shared__ LsCtl ctl[4];
-    __shared__ __align__(8) unsigned long long mbar[2];
     __shared__ LsMgr mgr[8];
     __shared__ uint32_t s_taddr;
     __shared__ float s_bv[NW];
@@ -307,14 +268,26 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     for (int r = 0; r < SV_ES_RMAX; ++r) degs |= static_cast<uint32_t>(m.deg[warp * SV_ES_RMAX + r]) << (4 * r);
     const uint32_t own_s = sbase + static_cast<uint32_t>(tid) * 16u; // own row of rank 0, group 0, buffer 0
 
-    // Hands new sequences to the manager lanes in `mask` and patches the control block of the
-    // coming step (fresh: overwrite it).  Called by all lanes of warp 0.
+    // Control blocks are published TWO steps ahead (ring of 4): block tau+1 has been visible since
+    // the barrier of step tau-1, so every warp can fetch its flags and the emission scores of the
+    // next step before the barrier of step tau instead of after it.
+    //
+    // refill: hands new sequences to the manager lanes in `mask` and patches the control blocks of
+    // the two coming steps d0, d1 (fresh: overwrite them).  Called by all lanes of the manager warp.
     unsigned long long mg_cur = 0, mg_nxt = 0;       // current / next 8 packed symbols
     const unsigned long long* mg_ptr = sym64;        // word that follows mg_nxt
-    uint32_t mg_pos = 0, mg_t = 0, mg_len = 0;       // byte phase of the next symbol, local step, length (0 = idle)
-    auto refill = [&](uint32_t mask, LsCtl& dst, bool fresh) {
-        bool started = false, one = false;
-        uint32_t colv = 0;
+    uint32_t mg_pos = 0, mg_t = 0, mg_len = 0;       // byte phase of the next symbol, last published local step, length (0 = idle)
+    auto next_symbol = [&]() -> uint32_t {           // pure register arithmetic; the refreshing load is
+        const uint32_t sym = static_cast<uint32_t>(mg_cur >> ((mg_pos & 7u) * 8u)) & 0xffu;
+        if ((++mg_pos & 7u) == 0) {                  // consumed 8 steps after it is issued: never waited for
+            mg_cur = mg_nxt;
+            mg_nxt = *mg_ptr++;
+        }
+        return sym;
+    };
+    auto refill = [&](uint32_t mask, LsCtl& d0, LsCtl& d1, bool fresh) {
+        bool started = false, one = false, second = false, two = false;
+        uint32_t col0 = 0, col1 = 0;
         if (lane < Q && ((mask >> lane) & 1u)) {
             mg_len = 0;
             mg_t = 0;
@@ -328,86 +301,77 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 mg_cur = *mg_ptr++;
                 mg_nxt = *mg_ptr++;
                 mg_pos = static_cast<uint32_t>(b & 7u);
-                colv = (static_cast<uint32_t>(mg_cur >> (mg_pos * 8u)) & 0xffu) * RS;
-                if ((++mg_pos & 7u) == 0) {
-                    mg_cur = mg_nxt;
-                    mg_nxt = *mg_ptr++;
-                }
+                col0 = next_symbol() * RS;
                 started = true;
                 one = mg_len == 1;
+                if (mg_len > 1) {
+                    col1 = next_symbol() * RS;
+                    second = true;
+                    two = mg_len == 2;
+                    mg_t = 1;
+                }
             }
             mgr[lane].sid = sid;
         }
         const uint32_t startm = __ballot_sync(0xffffffffu, started);
         const uint32_t onem = __ballot_sync(0xffffffffu, one);
-        if (lane < Q && (fresh || ((mask >> lane) & 1u))) dst.col[lane] = colv;
+        const uint32_t secm = __ballot_sync(0xffffffffu, second);
+        const uint32_t twom = __ballot_sync(0xffffffffu, two);
+        if (lane < Q && (fresh || ((mask >> lane) & 1u))) {
+            d0.col[lane] = col0;
+            d1.col[lane] = col1;
+        }
         if (lane == 0) {
             if (fresh) {
-                dst.init_mask = startm;
-                dst.fin_mask = onem;
-                dst.any_act = startm;
+                d0.init_mask = startm; d0.fin_mask = onem; d0.any_act = startm;
+                d1.init_mask = 0;      d1.fin_mask = twom; d1.any_act = secm;
             } else {
-                dst.init_mask |= startm;
-                dst.fin_mask |= onem;
-                dst.any_act |= startm;
+                d0.init_mask |= startm; d0.fin_mask |= onem; d0.any_act |= startm;
+                d1.fin_mask |= twom;    d1.any_act |= secm;
             }
         }
         __syncwarp();
     };
-    const uint32_t mbar_s = static_cast<uint32_t>(__cvta_generic_to_shared(&mbar[0]));
-    if (tid == 0) {
-        mbar_init(mbar_s, NW);
-        mbar_init(mbar_s + 8u, NW);
-    }
-    if (warp == MW) refill((1u << Q) - 1u, ctl[0], true);
+    if (warp == MW) refill((1u << Q) - 1u, ctl[0], ctl[1], true);
     __syncthreads();
 
+    // Flags of the coming step and E[o_q][own rows] of its first group are fetched BEFORE the
+    // barrier that ends the current step (here: before the loop).
+    uint32_t et[NQ4][4][5];
+    uint4 fl; // x = init_mask, y = fin_mask, z = any_act of the coming step
+    auto prefetch_step = [&](const LsCtl& nc) {
+        fl = *reinterpret_cast<const uint4*>(&nc.init_mask);
+        const uint4 c0 = *reinterpret_cast<const uint4*>(&nc.col[0]);
+        tmem_ld5(tE + c0.x, et[0][0]);
+        tmem_ld5(tE + c0.y, et[0][1]);
+        tmem_ld5(tE + c0.z, et[0][2]);
+        tmem_ld5(tE + c0.w, et[0][3]);
+    };
+    prefetch_step(ctl[0]);
+
     // Time loop.  tau = CTA step; par = tau & 1 = index of the score buffers that are read.
-    // The two float4 groups are two PHASES of a step with their own split barriers: a group's
-    // stores are followed by an arrive, and the matching wait sits one phase later (just before
-    // that group's scores are gathered again), so the warps of a CTA drift up to a phase apart
-    // instead of meeting at a __syncthreads every step -- the shared-memory crossbar stays busy
-    // across step boundaries.  Control blocks live in a ring of 4 for the same reason.
     uint32_t tau = 0;
-#ifdef SV_LS_DEBUG
-    long long dbg_wa = 0, dbg_wb = 0;
-    const long long dbg_start = clock64();
-#endif
-    LsPair io;
-    if constexpr (OVL) ls_gather<0>(eo, 0u, io, 0, SH::at(0) >= 2);
     for (;;) {
+        const uint32_t init_mask = fl.x, fin_mask = fl.y;
+        if (fl.z == 0) break;
         const uint32_t par = tau & 1u;
         const uint32_t pofs = par * BS;
         unsigned char* vn = smem_raw + (par ^ 1u) * BS;
-        if constexpr (!OVL) ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2); // one barrier per step: no overlap
-        SV_TRACE(0);
+        // first gathers of the step (group 0, rank 0, slots 0-1) go out before anything else
+        LsPair io;
+        ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2);
         const LsCtl& c = ctl[tau & 3u];
-        if (c.any_act == 0) break;
-        const uint32_t init_mask = c.init_mask, fin_mask = c.fin_mask;
-        uint32_t col[Q];
-        {
-            const uint4 c0 = *reinterpret_cast<const uint4*>(&c.col[0]);
-            col[0] = c0.x; col[1] = c0.y; col[2] = c0.z; col[3] = c0.w;
-            if constexpr (NQ4 == 2) {
-                const uint4 c1 = *reinterpret_cast<const uint4*>(&c.col[4]);
-                col[4] = c1.x; col[5] = c1.y; col[6] = c1.z; col[7] = c1.w;
-            }
-#pragma unroll
-            for (int q = 0; q < Q; ++q) col[q] += tE;
-        }
+        [[maybe_unused]] uint4 cg1 = make_uint4(0u, 0u, 0u, 0u); // TMEM columns of group 1 (consumed five slices later)
+        if constexpr (NQ4 == 2) cg1 = *reinterpret_cast<const uint4*>(&c.col[4]);
 
-        // ---- managers first (off the tail of the step): control block of the NEXT step ----
+        // ---- managers first (off the tail of the step): control block of step tau + 2 ----
         if (warp == MW) {
-            LsCtl& nx = ctl[(tau + 1u) & 3u];
+            LsCtl& nx = ctl[(tau + 2u) & 3u];
             bool cont = false, last = false;
             uint32_t colv = 0;
-            if (lane < Q && mg_t + 1u < mg_len) { // pure register arithmetic: no memory round trip
+            if (lane < Q && mg_t + 1u < mg_len) {
                 cont = true;
-                colv = (static_cast<uint32_t>(mg_cur >> ((mg_pos & 7u) * 8u)) & 0xffu) * RS;
-                if ((++mg_pos & 7u) == 0) {
-                    mg_cur = mg_nxt;     // arrived 8 steps ago
-                    mg_nxt = *mg_ptr++;  // consumed 8 steps from now: never waited for
-                }
+                colv = next_symbol() * RS;
                 last = mg_t + 2u == mg_len;
                 ++mg_t;
             }
@@ -438,11 +402,9 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         };
 
         // ---- light rows, one float4 group of 4 sequences at a time: slices (g, r) in order
-        //      (0,0) (0,1) .. (0,4) (1,0) ..; E[o_q][own rows] of a group = 8 tensor-memory loads,
-        //      those of group 1 are issued before the last slice of group 0 ----
-        uint32_t et[NQ4][4][5];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) tmem_ld5(col[j], et[0][j]);
+        //      (0,0) (0,1) .. (0,4) (1,0) ..; E[o_q][own rows] of a group = 8 tensor-memory loads:
+        //      group 0's were issued before the previous barrier, group 1's go out before the last
+        //      slice of group 0 ----
         const uint32_t ownn = own_s + (pofs ^ BS); // own row, rank 0, group 0 of the buffer being written
         auto slice_step = [&](auto gc, auto rc) {
             constexpr int g = decltype(gc)::value;
@@ -456,26 +418,11 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                                  "+r"(et[g][j][4]));
             }
             if constexpr (last_r && g + 1 < NQ4) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) tmem_ld5(col[4 * (g + 1 < NQ4 ? g + 1 : 0) + j], et[g + 1 < NQ4 ? g + 1 : 0][j]);
-            }
-            if constexpr (OVL && r == SH::R - 2) {
-                // Split-barrier wait for the buffer the LAST slice of this phase prefetches from.  Placed
-                // one slice early, right behind this slice's own (already issued) gathers: the poll is a
-                // shared-memory-pipe round trip of hundreds of cycles under load and overlaps with them.
-                if constexpr (g == 0) {
-                    SV_DBG_T0();
-                    SV_TRACE(2);
-                    if (tau != 0) mbar_wait(mbar_s + 8u, (tau - 1u) & 1u); // group 1 scores of step tau-1 complete
-                    SV_TRACE(3);
-                    SV_DBG_ACC(dbg_wb);
-                } else {
-                    SV_DBG_T0();
-                    SV_TRACE(5);
-                    mbar_wait(mbar_s, tau & 1u); // group 0 scores of this step complete
-                    SV_TRACE(6);
-                    SV_DBG_ACC(dbg_wa);
-                }
+                constexpr int g1 = g + 1 < NQ4 ? g + 1 : 0;
+                tmem_ld5(tE + cg1.x, et[g1][0]);
+                tmem_ld5(tE + cg1.y, et[g1][1]);
+                tmem_ld5(tE + cg1.z, et[g1][2]);
+                tmem_ld5(tE + cg1.w, et[g1][3]);
             }
             float e[4], acc[4];
 #pragma unroll
@@ -484,36 +431,24 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
             if constexpr (!last_r) { // next slice: next rank of the same group
                 ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), g * GS, SH::base(last_r ? 0 : r + 1),
                              (SH::at(last_r ? 0 : r + 1) >= 2), NSL>(d, ew, eo, pofs, pofs, e, acc, io);
-            } else if constexpr (g + 1 < NQ4) { // next slice: rank 0 of group 1, same step
+            } else if constexpr (g + 1 < NQ4) { // next slice: rank 0 of group 1
                 ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), GS, 0, (SH::at(0) >= 2), NSL>(d, ew, eo, pofs, pofs, e, acc,
                                                                                              io);
-            } else if constexpr (OVL) { // next slice: rank 0 of group 0 of the NEXT step (other buffer)
-                ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), 0, 0, (SH::at(0) >= 2), NSL>(d, ew, eo, pofs, pofs ^ BS, e,
-                                                                                            acc, io);
             } else {
                 ls_run_slots<g * GS, SH::base(r), 0, SH::at(r), 0, -1, false, NSL>(d, ew, eo, pofs, pofs, e, acc, io);
             }
             if (r < nranks) sts128<g * GS + r * TPG * 16>(ownn, acc);
         };
         auto group_step = [&](auto gc) {
-            [[maybe_unused]] constexpr int g = decltype(gc)::value;
             slice_step(gc, std::integral_constant<int, 0>{});
             slice_step(gc, std::integral_constant<int, 1>{});
             slice_step(gc, std::integral_constant<int, 2>{});
             slice_step(gc, std::integral_constant<int, 3>{});
             slice_step(gc, std::integral_constant<int, 4>{});
-            if constexpr (OVL) {
-                if (init_mask != 0) init_fix(4 * g, 4 * g + 4);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(mbar_s + 8u * g);
-                SV_TRACE(g == 0 ? 4 : 7);
-            }
         };
         group_step(std::integral_constant<int, 0>{});
         if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
-        if constexpr (!OVL) {
-            if (init_mask != 0) init_fix(0, Q);
-        }
+        if (init_mask != 0) init_fix(0, Q);
 
         // ---- heavy rows: every thread relaxes a slice, block-wide min ----
         if constexpr (NH > 0) {
@@ -565,11 +500,13 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 }
             }
         }
-        if constexpr (!OVL) __syncthreads();
+        // flags + first emission scores of step tau + 1 (published during step tau - 1): in flight
+        // across the barrier
+        prefetch_step(ctl[(tau + 1u) & 3u]);
+        __syncthreads();
 
         // ---- rare path: write out finished sequences, hand out new ones ----
         if (fin_mask != 0) {
-            if constexpr (OVL) mbar_wait(mbar_s + 8u, tau & 1u); // (group 0 was waited for in the last slice)
             for (int q = 0; q < Q; ++q) {
                 if (!((fin_mask >> q) & 1u)) continue;
                 const uint32_t sid = mgr[q].sid;
@@ -622,18 +559,15 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 }
             }
             __syncthreads(); // every thread is done with mgr[].sid
-            if (warp == MW) refill(fin_mask, ctl[(tau + 1u) & 3u], false);
+            if (warp == MW) refill(fin_mask, ctl[(tau + 1u) & 3u], ctl[(tau + 2u) & 3u], false);
             __syncthreads();
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); // retire the stale fetch, then redo it
+            prefetch_step(ctl[(tau + 1u) & 3u]);
         }
         ++tau;
     }
 
-#ifdef SV_LS_DEBUG
-    if (lane == 0 && blockIdx.x < 148) {
-        unsigned long long* d = g_ls_dbg + (blockIdx.x * 16 + warp) * 4;
-        d[0] = dbg_wa; d[1] = dbg_wb; d[2] = clock64() - dbg_start; d[3] = tau;
-    }
-#endif
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); // the last prefetch is never consumed
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) tmem_free(tbase, static_cast<uint32_t>(m.tmem_cols));
@@ -676,14 +610,6 @@ const void* ls_variant_fn(int index) {
 
 } // namespace
 
-#ifdef SV_LS_DEBUG
-extern "C" int sv_debug_ls_dump(unsigned long long* out) {
-    return cudaMemcpyFromSymbol(out, g_ls_dbg, sizeof(g_ls_dbg));
-}
-extern "C" int sv_debug_ls_trace(unsigned long long* out) {
-    return cudaMemcpyFromSymbol(out, g_ls_trace, sizeof(g_ls_trace));
-}
-#endif
 int sv_ls_num_variants() { return kNumLsVariants; }
 const SvLsVariant& sv_ls_variant(int index) { return kLsVariants[index]; }
 
