@@ -188,6 +188,7 @@ int upload_ls(sv_model* m) {
     d.emits = static_cast<int>(m->emits);
     d.ranks = p.ranks;
     d.tmem_cols = p.tmem_cols;
+    d.nonneg = p.nonneg ? 1 : 0;
     d.edge_w = reinterpret_cast<const float*>(base + o_w);
     d.edge_off = reinterpret_cast<const uint32_t*>(base + o_off);
     d.deg = reinterpret_cast<const uint8_t*>(base + o_deg);

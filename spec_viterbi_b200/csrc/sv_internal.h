@@ -130,6 +130,7 @@ struct SvLsPlan {
     int n_lpad = 0;   // light positions = ranks * threads (holes included)
     int n_pad = 0;    // positions per score buffer (n_lpad + heavy, rounded up to 8)
     int n_heavy = 0, nslots = 0, ranks = 0, tmem_cols = 0;
+    bool nonneg = false; // every finite score is >= 0 (or -0): float order == signed-int order
     uint64_t gather_wavefronts = 0, gather_ideal = 0, smem_bytes = 0, split_states = 0;
     uint64_t colour_cost_before = 0, colour_cost_after = 0; // excess bank-group loads (K0 search)
     std::vector<float> edge_w;       // [nslots][threads]
@@ -144,6 +145,7 @@ struct SvLsPlan {
 
 struct SvLsDev {
     int n = 0, n_int = 0, n_lpad = 0, n_pad = 0, n_heavy = 0, emits = 0, ranks = 0, tmem_cols = 0;
+    int nonneg = 0; // scores are >= 0: warp minima may use the integer REDUX unit
     const float* edge_w = nullptr;
     const uint32_t* edge_off = nullptr;
     const uint8_t* deg = nullptr;

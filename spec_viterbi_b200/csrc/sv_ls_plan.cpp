@@ -669,6 +669,16 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->smem_bytes = smem;
     plan->split_states = n_int - n;
     plan->deg = deg;
+    // Sums of scores that are all >= 0 (or -0) stay >= 0, so their float order is the signed-int
+    // order of their bit patterns and warp-wide minima can run on the integer REDUX unit.
+    {
+        auto ok = [](float x) { return !(x < 0.0f) && x == x; };
+        bool nn = true;
+        for (const float x : csr.w) nn &= ok(x);
+        for (const float x : emis) nn &= ok(x);
+        for (const float x : start) nn &= ok(x);
+        plan->nonneg = nn;
+    }
     return true;
 }
 

@@ -465,11 +465,17 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                         LsPair hio;
                         ls_gather<g * GS>(eo, pofs, hio, NL + h * HS, HS >= 2);
                         ls_run_slots<g * GS, NL + h * HS, 0, HS, 0, -1, false, NSL>(m.heavy_slots[h], ew, eo, pofs, pofs, he, acc, hio);
+                        if (m.nonneg) { // one REDUX per value instead of five shuffle + min stages
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
+                            for (int j = 0; j < 4; ++j)
+                                acc[j] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(acc[j])));
+                        } else {
 #pragma unroll
-                            for (int d = 16; d > 0; d >>= 1)
-                                acc[j] = fminf(acc[j], __shfl_xor_sync(0xffffffffu, acc[j], d));
+                            for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                                for (int d = 16; d > 0; d >>= 1)
+                                    acc[j] = fminf(acc[j], __shfl_xor_sync(0xffffffffu, acc[j], d));
+                            }
                         }
                         if (lane == 0) {
 #pragma unroll
