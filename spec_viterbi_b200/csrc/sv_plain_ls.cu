@@ -255,6 +255,16 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 
+    // emission scores of the heavy rows, indexed by the control block's column value (symbol * RS)
+    constexpr int kHeStride = 256 * RS;
+    __shared__ float s_he[NH > 0 ? NH * kHeStride : 1];
+    const bool has_heavy = NH > 0 && m.n_heavy > 0;
+    if constexpr (NH > 0) {
+        for (int i = tid; i < NH * m.emits; i += TPG) {
+            const int h = i / m.emits, o = i % m.emits;
+            s_he[h * kHeStride + o * RS] = h < m.n_heavy ? m.emis_p[static_cast<size_t>(o) * n_pad + m.n_lpad + h] : 0.f;
+        }
+    }
     const uint32_t sbase = static_cast<uint32_t>(__cvta_generic_to_shared(smem_raw));
     float ew[NSL];
     uint32_t eo[NSL];
@@ -357,9 +367,12 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         const uint32_t par = tau & 1u;
         const uint32_t pofs = par * BS;
         unsigned char* vn = smem_raw + (par ^ 1u) * BS;
-        // first gathers of the step (group 0, rank 0, slots 0-1) go out before anything else
+        // first gathers of the step (group 0: first heavy row if any, else rank 0) go out before anything else
         LsPair io;
-        ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2);
+        if (has_heavy)
+            ls_gather<0>(eo, pofs, io, NH > 0 ? NL : 0, HS >= 2);
+        else
+            ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2);
         const LsCtl& c = ctl[tau & 3u];
         [[maybe_unused]] uint4 cg1 = make_uint4(0u, 0u, 0u, 0u); // TMEM columns of group 1 (consumed five slices later)
         if constexpr (NQ4 == 2) cg1 = *reinterpret_cast<const uint4*>(&c.col[4]);
@@ -446,50 +459,53 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
             slice_step(gc, std::integral_constant<int, 3>{});
             slice_step(gc, std::integral_constant<int, 4>{});
         };
-        group_step(std::integral_constant<int, 0>{});
-        if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
-        if (init_mask != 0) init_fix(0, Q);
-
-        // ---- heavy rows: every thread relaxes a slice, block-wide min ----
+        // ---- heavy rows (dense rows of profile HMMs): every thread relaxes a slice of the row and
+        //      the warp minima go to shared memory FIRST in the step; after group 0 a barrier
+        //      publishes them and warp h finishes row h while the other warps run group 1, so the
+        //      finishing chain is off the critical path ----
         if constexpr (NH > 0) {
-            if (m.n_heavy > 0) {
-                auto heavy_step = [&](auto hc, auto gc) {
-                    constexpr int h = decltype(hc)::value;
-                    constexpr int g = decltype(gc)::value;
-                    if (h < m.n_heavy) {
-                        const int ph = m.n_lpad + h;
-                        float he[4], acc[4];
+            if (has_heavy) {
+                auto heavy_step = [&](auto kc) {
+                    constexpr int k = decltype(kc)::value; // chain index: h-major over (h, g)
+                    constexpr int h = k / NQ4, g = k % NQ4;
+                    constexpr bool lastk = k + 1 == NH * NQ4;
+                    constexpr int nh = lastk ? 0 : (k + 1) / NQ4, ng = lastk ? 0 : (k + 1) % NQ4;
+                    float he[4], acc[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) he[j] = s_he[h * kHeStride + c.col[4 * g + j]];
+                    const int d = h < m.n_heavy ? m.heavy_slots[h] : 0;
+                    if constexpr (lastk) // next slice: light rows, group 0, rank 0
+                        ls_run_slots<g * GS, NL + h * HS, 0, HS, 0, 0, (SH::at(0) >= 2), NSL>(d, ew, eo, pofs, pofs, he, acc, io);
+                    else
+                        ls_run_slots<g * GS, NL + h * HS, 0, HS, ng * GS, NL + nh * HS, (HS >= 2), NSL>(d, ew, eo, pofs, pofs, he,
+                                                                                                  acc, io);
+                    if (m.nonneg) { // one REDUX per value instead of five shuffle + min stages
 #pragma unroll
                         for (int j = 0; j < 4; ++j)
-                            he[j] = m.emis_p[static_cast<size_t>(c.col[4 * g + j] / RS) * n_pad + ph];
-                        LsPair hio;
-                        ls_gather<g * GS>(eo, pofs, hio, NL + h * HS, HS >= 2);
-                        ls_run_slots<g * GS, NL + h * HS, 0, HS, 0, -1, false, NSL>(m.heavy_slots[h], ew, eo, pofs, pofs, he, acc, hio);
-                        if (m.nonneg) { // one REDUX per value instead of five shuffle + min stages
+                            acc[j] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(acc[j])));
+                    } else {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                acc[j] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(acc[j])));
-                        } else {
+                        for (int j = 0; j < 4; ++j) {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-#pragma unroll
-                                for (int d = 16; d > 0; d >>= 1)
-                                    acc[j] = fminf(acc[j], __shfl_xor_sync(0xffffffffu, acc[j], d));
-                            }
-                        }
-                        if (lane == 0) {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) red[(h * NW + warp) * Q + 4 * g + j] = acc[j];
+                            for (int dd = 16; dd > 0; dd >>= 1)
+                                acc[j] = fminf(acc[j], __shfl_xor_sync(0xffffffffu, acc[j], dd));
                         }
                     }
+                    if (lane == 0) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) red[(h * NW + warp) * Q + 4 * g + j] = acc[j];
+                    }
                 };
-                heavy_step(std::integral_constant<int, 0>{}, std::integral_constant<int, 0>{});
-                if constexpr (NQ4 == 2) heavy_step(std::integral_constant<int, 0>{}, std::integral_constant<int, 1>{});
-                if constexpr (NH > 1) {
-                    heavy_step(std::integral_constant<int, 1>{}, std::integral_constant<int, 0>{});
-                    if constexpr (NQ4 == 2)
-                        heavy_step(std::integral_constant<int, 1>{}, std::integral_constant<int, 1>{});
-                }
+                heavy_step(std::integral_constant<int, 0>{});
+                if constexpr (NH * NQ4 > 1) heavy_step(std::integral_constant<int, 1>{});
+                if constexpr (NH * NQ4 > 2) heavy_step(std::integral_constant<int, 2>{});
+                if constexpr (NH * NQ4 > 3) heavy_step(std::integral_constant<int, 3>{});
+                static_assert(NH * NQ4 <= 4, "heavy chain");
+            }
+        }
+        group_step(std::integral_constant<int, 0>{});
+        if constexpr (NH > 0) {
+            if (has_heavy) {
                 __syncthreads();
                 if (warp < m.n_heavy) {
                     // lane l: sequence q = l / LPQ, partials of warps (l % LPQ) + j * LPQ
@@ -498,7 +514,7 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     float x = pos_inf();
                     for (int w = lane % LPQ; w < NW; w += LPQ) x = fminf(x, red[(h * NW + w) * Q + q]);
 #pragma unroll
-                    for (int d = LPQ / 2; d > 0; d >>= 1) x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
+                    for (int dd = LPQ / 2; dd > 0; dd >>= 1) x = fminf(x, __shfl_xor_sync(0xffffffffu, x, dd));
                     if ((init_mask >> q) & 1u)
                         x = m.emis_p[static_cast<size_t>(c.col[q] / RS) * n_pad + ph] + m.start_p[ph];
                     if (lane % LPQ == 0)
@@ -506,6 +522,9 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 }
             }
         }
+        if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
+        if (init_mask != 0) init_fix(0, Q);
+
         // flags + first emission scores of step tau + 1 (published during step tau - 1): in flight
         // across the barrier
         prefetch_step(ctl[(tau + 1u) & 3u]);
