@@ -141,7 +141,9 @@ typedef struct sv_spec sv_spec;
 enum {
     SV_SPEC_AUTO = 0,
     SV_SPEC_DENSE_GEMM = 1, /* K3: register-blocked dense (min,+) GEMM, 2*N^3 ops / handler */
-    SV_SPEC_SPARSE_LHS = 2  /* K3': sparse level-1 matrix times dense handler, 2*nnz*N ops */
+    SV_SPEC_SPARSE_LHS = 2, /* K3': sparse level-1 matrix times dense handler, 2*nnz*N ops */
+    SV_SPEC_PAIR_ROWS = 3   /* K3'': level 2 only, sparse x sparse rows streamed into the dense table;
+                               AUTO picks it for level 2 when the model has few dense rows */
 };
 
 /* spec_with(hmm): level-1 tables, and for level > 1 the dense handler of every symbol

@@ -309,6 +309,12 @@ class Spec:
     def set_range(self, b: int, e: int) -> None:
         L.check(self._lib.sv_spec_set_range(self._h, b, e))
 
+    def table(self):
+        """-> (device pointer of the handler table, first tuple, end tuple)."""
+        tb, te = C.c_uint64(), C.c_uint64()
+        ptr = self._lib.sv_spec_table(self._h, C.byref(tb), C.byref(te))
+        return int(ptr or 0), tb.value, te.value
+
     def handler(self, tuple_index: int) -> np.ndarray:
         n = self.model.hmm.states_num
         out = np.empty((n, n), np.float32)

@@ -200,6 +200,9 @@ struct sv_model {
     SvLsPlan ls;
     SvLsDev lsdev;
     void* d_ls_blob = nullptr;
+    // level-2 pair precompute (sv_spec.cu): dense copies of the heavy rows + CSC, built on first use
+    void* d_pair_blob = nullptr;
+    int pair_state = 0; // 0 = not built, 1 = ready, -1 = model not eligible (too many heavy rows)
     int kernel_pref = SV_KERNEL_AUTO;
     int last_launches = 0;
     int last_kernel = 0;

@@ -12,6 +12,8 @@
 #include "sv_internal.h"
 
 #include <algorithm>
+#include <cstring>
+#include <limits>
 #include <new>
 #include <vector>
 
@@ -91,6 +93,193 @@ sparse_lhs_kernel(SvGenericDev m, const float* __restrict__ prev, uint64_t prev_
 #pragma unroll
         for (int c = 0; c < 4; ++c)
             if (k0 + c < n) O[k0 + c] = acc[c];
+    }
+}
+
+// ------------------------------------------------------ K3'': level-2 pair rows, sparse x sparse ----
+// Level 2 only: BOTH factors of H(a,b) = M_b (x) M_a have the sparsity of T', so one output row
+//   out[t][i][k] = min_{j in in(i)} fl( fl(E[b][i] + T'[i][j]) + fl(E[a][j] + T'[j][k]) )
+// needs no dense operand at all: the kernel is a pure streaming WRITE of the dense table
+// (E^2 * N^2 * 4 bytes) with a handful of terms per row.  Rows of T' with more than kPairHeavy
+// entries ("heavy": the dense rows of profile HMMs) are kept as dense vectors Wd[h][.]:
+//   * light row i: dense terms (heavy j) are evaluated per column, the few (k, value) pairs that
+//     the light j contribute are patched in after a CTA barrier;
+//   * heavy row i: column k walks its CSC list {j : k in in(j)} and looks T'[i][j] up in Wd.
+// Same association as K3' => same bits.  grid: x = row i, y = tuple (relative); 256 threads.
+constexpr int kPairHeavy = 32;    // rows with more in-edges are "heavy"
+constexpr int kPairMaxHeavy = 64; // more heavy rows than this: use K3'
+constexpr int kPairLongCol = 64;  // CSC columns longer than this are reduced by the whole CTA
+constexpr int kPairMaxPairs = kPairHeavy * kPairHeavy;
+
+struct SvPairDev {
+    int n = 0, emits = 0, n_longcol = 0;
+    const uint32_t* rowptr = nullptr; // CSR of T' (row = destination)
+    const uint32_t* col = nullptr;
+    const float* w = nullptr;
+    const float* emis = nullptr;      // [emits][n]
+    const int32_t* hidx = nullptr;    // [n] index of the row's dense copy, -1 = light row
+    const float* wd = nullptr;        // [heavy][n] dense copies, +inf where absent
+    const uint32_t* cscptr = nullptr; // CSC of T' (column = source)
+    const uint32_t* cscrow = nullptr;
+    const float* cscw = nullptr;
+    const uint32_t* longcol = nullptr; // columns with more than kPairLongCol entries
+    const uint32_t* hrow = nullptr;    // [heavy] row of each dense copy
+    int n_heavy = 0;
+};
+
+constexpr int kPairChunk = 16; // consecutive tuples per CTA: the row's structure is set up once
+
+__global__ void __launch_bounds__(256)
+pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uint64_t tuple_count, int heavy_pass) {
+    // light pass: x = row, y = chunk of kPairChunk tuples (heavy rows exit); heavy pass: x = heavy row
+    // index, y = one tuple (their per-tuple work is ~100x a light row's: spread it over the grid)
+    const int n = d.n, tid = threadIdx.x;
+    const int i = heavy_pass ? static_cast<int>(d.hrow[blockIdx.x]) : static_cast<int>(blockIdx.x);
+    const int chunk = heavy_pass ? 1 : kPairChunk;
+    const uint64_t rel0 = static_cast<uint64_t>(blockIdx.y) * chunk;
+    const int ntup = static_cast<int>(min(static_cast<uint64_t>(chunk), tuple_count - rel0));
+    const int hi = d.hidx[i];
+    __shared__ float s_red[8];
+    if ((hi >= 0) != (heavy_pass != 0)) return;
+    if (hi >= 0) { // ---- heavy row: per column, over the column's CSC list ----
+        const float* __restrict__ Wi = d.wd + static_cast<size_t>(hi) * n;
+        for (int s = 0; s < ntup; ++s) {
+            const uint64_t tuple = tuple_first + rel0 + s;
+            const int b = static_cast<int>(tuple % d.emits), a = static_cast<int>(tuple / d.emits);
+            float* __restrict__ O = out + (rel0 + s) * static_cast<size_t>(n) * n + static_cast<size_t>(i) * n;
+            const float eb = d.emis[static_cast<size_t>(b) * n + i];
+            const float* __restrict__ Ea = d.emis + static_cast<size_t>(a) * n;
+            for (int k = tid; k < n; k += 256) {
+                const uint32_t p0 = d.cscptr[k], p1 = d.cscptr[k + 1];
+                float acc = pos_inf();
+                if (p1 - p0 <= static_cast<uint32_t>(kPairLongCol)) {
+                    for (uint32_t p = p0; p < p1; ++p) {
+                        const uint32_t j = d.cscrow[p];
+                        acc = fminf(acc, (eb + Wi[j]) + (Ea[j] + d.cscw[p]));
+                    }
+                }
+                O[k] = acc;
+            }
+            for (int c = 0; c < d.n_longcol; ++c) { // long columns: CTA-wide reduction, thread 0 overwrites
+                const uint32_t k = d.longcol[c];
+                float acc = pos_inf();
+                for (uint32_t p = d.cscptr[k] + tid; p < d.cscptr[k + 1]; p += 256) {
+                    const uint32_t j = d.cscrow[p];
+                    acc = fminf(acc, (eb + Wi[j]) + (Ea[j] + d.cscw[p]));
+                }
+                acc = warp_min(acc);
+                __syncthreads(); // orders the O[k] stores above / the previous round's s_red reads
+                if ((tid & 31) == 0) s_red[tid >> 5] = acc;
+                __syncthreads();
+                if (tid == 0) {
+                    float x = s_red[0];
+#pragma unroll
+                    for (int q = 1; q < 8; ++q) x = fminf(x, s_red[q]);
+                    O[k] = x;
+                }
+            }
+        }
+        return;
+    }
+    // ---- light row: structure once, values per tuple ----
+    __shared__ float s_w[kPairHeavy];       // T'[i][j_q]
+    __shared__ uint32_t s_j[kPairHeavy];    // j_q
+    __shared__ int s_h[kPairHeavy];         // dense copy of row j_q, -1 = light
+    __shared__ uint32_t s_off[kPairHeavy + 1];
+    __shared__ uint32_t s_pk[kPairMaxPairs]; // pairs contributed by the light j: column,
+    __shared__ float s_pw[kPairMaxPairs];    //   T'[j][k],
+    __shared__ uint8_t s_pq[kPairMaxPairs];  //   and which q they belong to
+    __shared__ int s_nheavy;
+    __shared__ uint8_t s_hq[kPairHeavy];     // the q with heavy j
+    const uint32_t r0 = d.rowptr[i];
+    const int di = static_cast<int>(d.rowptr[i + 1] - r0);
+    if (tid < di) {
+        const uint32_t j = d.col[r0 + tid];
+        s_w[tid] = d.w[r0 + tid];
+        s_j[tid] = j;
+        s_h[tid] = d.hidx[j];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t o = 0;
+        int nhv = 0;
+        for (int q = 0; q < di; ++q) {
+            s_off[q] = o;
+            if (s_h[q] < 0)
+                o += d.rowptr[s_j[q] + 1] - d.rowptr[s_j[q]];
+            else
+                s_hq[nhv++] = static_cast<uint8_t>(q);
+        }
+        s_off[di] = o;
+        s_nheavy = nhv;
+    }
+    __syncthreads();
+    const int npairs = static_cast<int>(s_off[di]);
+    const int nhv = s_nheavy;
+    if (tid < di && s_h[tid] < 0) {
+        const uint32_t q0 = d.rowptr[s_j[tid]], q1 = d.rowptr[s_j[tid] + 1];
+        for (uint32_t p = q0; p < q1; ++p) {
+            s_pk[s_off[tid] + (p - q0)] = d.col[p];
+            s_pw[s_off[tid] + (p - q0)] = d.w[p];
+            s_pq[s_off[tid] + (p - q0)] = static_cast<uint8_t>(tid);
+        }
+    }
+    __syncthreads();
+    for (int s = 0; s < ntup; ++s) {
+        const uint64_t tuple = tuple_first + rel0 + s;
+        const int b = static_cast<int>(tuple % d.emits), a = static_cast<int>(tuple / d.emits);
+        float* __restrict__ O = out + (rel0 + s) * static_cast<size_t>(n) * n + static_cast<size_t>(i) * n;
+        const float eb = d.emis[static_cast<size_t>(b) * n + i];
+        const float* __restrict__ Ea = d.emis + static_cast<size_t>(a) * n;
+        // dense terms (heavy j): min_q fl( fl(E_b[i] + T'[i][j_q]) + fl(E_a[j_q] + T'[j_q][k]) ); the per-tuple
+        // invariants of the first two heavy j live in registers
+        float hu0 = pos_inf(), hu1 = pos_inf(), hea0 = 0.f, hea1 = 0.f;
+        const float* __restrict__ hp0 = d.wd;
+        const float* __restrict__ hp1 = d.wd;
+        if (nhv > 0) {
+            const int q = s_hq[0];
+            hu0 = eb + s_w[q];
+            hea0 = Ea[s_j[q]];
+            hp0 = d.wd + static_cast<size_t>(s_h[q]) * n;
+        }
+        if (nhv > 1) {
+            const int q = s_hq[1];
+            hu1 = eb + s_w[q];
+            hea1 = Ea[s_j[q]];
+            hp1 = d.wd + static_cast<size_t>(s_h[q]) * n;
+        }
+        auto dense_at = [&](int k) {
+            float acc = pos_inf();
+            if (nhv > 0) acc = hu0 + (hea0 + hp0[k]);
+            if (nhv > 1) acc = fminf(acc, hu1 + (hea1 + hp1[k]));
+            for (int x = 2; x < nhv; ++x) {
+                const int q = s_hq[x];
+                acc = fminf(acc, (eb + s_w[q]) + (Ea[s_j[q]] + d.wd[static_cast<size_t>(s_h[q]) * n + k]));
+            }
+            return acc;
+        };
+        // the row as 16-byte stores where its (odd-length) placement allows, scalar head and tail
+        const int kb = static_cast<int>((4u - ((reinterpret_cast<uintptr_t>(O) >> 2) & 3u)) & 3u);
+        const int nb = (n - kb) / 4;
+        if (tid < kb) O[tid] = dense_at(tid);
+        for (int g = tid; g < nb; g += 256) {
+            const int k = kb + 4 * g;
+            *reinterpret_cast<float4*>(O + k) = make_float4(dense_at(k), dense_at(k + 1), dense_at(k + 2), dense_at(k + 3));
+        }
+        for (int k = kb + 4 * nb + tid; k < n; k += 256) O[k] = dense_at(k);
+        if (npairs > 0) {
+            __syncthreads(); // the row's stores are ordered before the patches
+            for (int t = tid; t < npairs; t += 256) {
+                const uint32_t k = s_pk[t];
+                float v = dense_at(static_cast<int>(k));
+                for (int t2 = 0; t2 < npairs; ++t2)
+                    if (s_pk[t2] == k) {
+                        const int q = s_pq[t2];
+                        v = fminf(v, (eb + s_w[q]) + (Ea[s_j[q]] + s_pw[t2]));
+                    }
+                O[k] = v; // entries with equal k write equal values
+            }
+        }
     }
 }
 
@@ -366,6 +555,108 @@ int build_sparse(sv_model* m, uint64_t lvl, uint64_t tb, uint64_t te, float* dst
     return rc;
 }
 
+// Device images for K3'' (built on first use, cached in the model).  Returns false if the model
+// has too many heavy rows for the dense copies (then K3' is used).
+bool pair_prepare(sv_model* m, SvPairDev* out) {
+    const size_t n = m->n, nnz = m->csr.col.size();
+    if (m->pair_state < 0) return false;
+    std::vector<int32_t> hidx(n, -1);
+    std::vector<uint32_t> heavy;
+    for (size_t i = 0; i < n; ++i)
+        if (m->csr.rowptr[i + 1] - m->csr.rowptr[i] > static_cast<uint32_t>(kPairHeavy)) {
+            hidx[i] = static_cast<int32_t>(heavy.size());
+            heavy.push_back(static_cast<uint32_t>(i));
+        }
+    if (heavy.size() > static_cast<size_t>(kPairMaxHeavy)) {
+        m->pair_state = -1;
+        return false;
+    }
+    const size_t nh = std::max<size_t>(heavy.size(), 1);
+    auto align = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t o_hidx = 0;
+    const size_t o_wd = align(o_hidx + n * 4);
+    const size_t o_cptr = align(o_wd + nh * n * 4);
+    const size_t o_crow = align(o_cptr + (n + 1) * 4);
+    const size_t o_cw = align(o_crow + std::max<size_t>(nnz, 1) * 4);
+    const size_t o_long = align(o_cw + std::max<size_t>(nnz, 1) * 4);
+    const size_t o_hrow = align(o_long + n * 4); // (at most n long columns)
+    if (m->pair_state == 0) {
+        std::vector<float> wd(nh * n, std::numeric_limits<float>::infinity());
+        for (size_t h = 0; h < heavy.size(); ++h)
+            for (uint32_t p = m->csr.rowptr[heavy[h]]; p < m->csr.rowptr[heavy[h] + 1]; ++p)
+                wd[h * n + m->csr.col[p]] = m->csr.w[p];
+        std::vector<uint32_t> cptr(n + 1, 0), crow(nnz), fillp;
+        std::vector<float> cw(nnz);
+        for (size_t p = 0; p < nnz; ++p) cptr[m->csr.col[p] + 1] += 1;
+        for (size_t k = 0; k < n; ++k) cptr[k + 1] += cptr[k];
+        fillp.assign(cptr.begin(), cptr.end() - 1);
+        for (size_t i = 0; i < n; ++i)
+            for (uint32_t p = m->csr.rowptr[i]; p < m->csr.rowptr[i + 1]; ++p) {
+                const uint32_t q = fillp[m->csr.col[p]]++;
+                crow[q] = static_cast<uint32_t>(i);
+                cw[q] = m->csr.w[p];
+            }
+        std::vector<uint32_t> longcol;
+        for (size_t k = 0; k < n; ++k)
+            if (cptr[k + 1] - cptr[k] > static_cast<uint32_t>(kPairLongCol)) longcol.push_back(static_cast<uint32_t>(k));
+        const size_t bytes = o_hrow + nh * 4 + 256;
+        std::vector<unsigned char> host(bytes, 0);
+        std::memcpy(host.data() + o_hidx, hidx.data(), n * 4);
+        std::memcpy(host.data() + o_wd, wd.data(), wd.size() * 4);
+        std::memcpy(host.data() + o_cptr, cptr.data(), cptr.size() * 4);
+        if (nnz) std::memcpy(host.data() + o_crow, crow.data(), nnz * 4);
+        if (nnz) std::memcpy(host.data() + o_cw, cw.data(), nnz * 4);
+        if (!longcol.empty()) std::memcpy(host.data() + o_long, longcol.data(), longcol.size() * 4);
+        if (!heavy.empty()) std::memcpy(host.data() + o_hrow, heavy.data(), heavy.size() * 4);
+        if (cudaMalloc(&m->d_pair_blob, bytes) != cudaSuccess ||
+            cudaMemcpy(m->d_pair_blob, host.data(), bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+            cudaGetLastError();
+            if (m->d_pair_blob) cudaFree(m->d_pair_blob);
+            m->d_pair_blob = nullptr;
+            m->pair_state = -1;
+            return false;
+        }
+        m->pair_state = 1 + static_cast<int>(longcol.size());
+    }
+    auto* base = static_cast<unsigned char*>(m->d_pair_blob);
+    out->n = static_cast<int>(n);
+    out->emits = static_cast<int>(m->emits);
+    out->n_longcol = m->pair_state - 1;
+    out->rowptr = m->gen.rowptr;
+    out->col = m->gen.col;
+    out->w = m->gen.w;
+    out->emis = m->gen.emis;
+    out->hidx = reinterpret_cast<const int32_t*>(base + o_hidx);
+    out->wd = reinterpret_cast<const float*>(base + o_wd);
+    out->cscptr = reinterpret_cast<const uint32_t*>(base + o_cptr);
+    out->cscrow = reinterpret_cast<const uint32_t*>(base + o_crow);
+    out->cscw = reinterpret_cast<const float*>(base + o_cw);
+    out->longcol = reinterpret_cast<const uint32_t*>(base + o_long);
+    out->hrow = reinterpret_cast<const uint32_t*>(base + o_hrow);
+    out->n_heavy = static_cast<int>(heavy.size());
+    return true;
+}
+
+// Level 2 with K3'': no dense prefix table, one streaming pass over the output.
+int build_pair_level2(sv_model* m, const SvPairDev& pd, uint64_t tb, uint64_t te, float* dst, cudaStream_t st) {
+    const size_t n = m->n;
+    int rc = SV_OK;
+    const uint64_t ymax = 32768ull;
+    for (uint64_t t0 = tb; t0 < te && rc == SV_OK; t0 += ymax) {
+        const uint64_t cnt = std::min(ymax, te - t0);
+        dim3 grid(static_cast<unsigned>(n), static_cast<unsigned>((cnt + kPairChunk - 1) / kPairChunk));
+        if (pd.n_heavy > 0) { // first: the few long-running CTAs
+            dim3 hgrid(static_cast<unsigned>(pd.n_heavy), static_cast<unsigned>(cnt));
+            pair_rows_kernel<<<hgrid, 256, 0, st>>>(pd, dst + (t0 - tb) * n * n, t0, cnt, 1);
+        }
+        pair_rows_kernel<<<grid, 256, 0, st>>>(pd, dst + (t0 - tb) * n * n, t0, cnt, 0);
+        if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "pair_rows launch failed");
+    }
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (rc == SV_OK && e != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, cudaGetErrorString(e));
+    return rc;
+}
+
 int build_dense_level2(sv_model* m, uint64_t tb, uint64_t te, float* dst, cudaStream_t st) {
     const size_t n = m->n;
     const size_t npad = (n + GM - 1) / GM * GM;
@@ -414,12 +705,15 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
     if (tuple_begin == 0 && tuple_end == 0) tuple_end = ntuples;
     if (tuple_begin > tuple_end || tuple_end > ntuples)
         return sv_fail(SV_ERR_ARG, "sv_spec_create: bad tuple range");
-    if (method == SV_SPEC_AUTO) method = SV_SPEC_SPARSE_LHS;
-    if (method != SV_SPEC_SPARSE_LHS && method != SV_SPEC_DENSE_GEMM)
-        return sv_fail(SV_ERR_ARG, "sv_spec_create: unknown method");
     if (method == SV_SPEC_DENSE_GEMM && level != 2 && level != 1)
         return sv_fail(SV_ERR_UNSUPPORTED, "dense (min,+) GEMM precompute is implemented for level 2");
     SV_CUDA(cudaSetDevice(m->device));
+    SvPairDev pairdev;
+    if (method == SV_SPEC_AUTO) method = (level == 2 && pair_prepare(m, &pairdev)) ? SV_SPEC_PAIR_ROWS : SV_SPEC_SPARSE_LHS;
+    if (method != SV_SPEC_SPARSE_LHS && method != SV_SPEC_DENSE_GEMM && method != SV_SPEC_PAIR_ROWS)
+        return sv_fail(SV_ERR_ARG, "sv_spec_create: unknown method");
+    if (method == SV_SPEC_PAIR_ROWS && (level != 2 || !pair_prepare(m, &pairdev)))
+        return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_create: the pair-rows kernel builds level 2 of models with few dense rows");
     sv_spec* s = new (std::nothrow) sv_spec;
     if (s == nullptr) return sv_fail(SV_ERR_MEMORY, "sv_spec_create: out of host memory");
     s->m = m;
@@ -444,9 +738,9 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
         }
         int rc = SV_OK;
         if (tuple_end > tuple_begin) {
-            rc = method == SV_SPEC_DENSE_GEMM
-                     ? build_dense_level2(m, tuple_begin, tuple_end, s->d_table, st)
-                     : build_sparse(m, level, tuple_begin, tuple_end, s->d_table, st);
+            rc = method == SV_SPEC_DENSE_GEMM  ? build_dense_level2(m, tuple_begin, tuple_end, s->d_table, st)
+                 : method == SV_SPEC_PAIR_ROWS ? build_pair_level2(m, pairdev, tuple_begin, tuple_end, s->d_table, st)
+                                               : build_sparse(m, level, tuple_begin, tuple_end, s->d_table, st);
         }
         if (rc != SV_OK) {
             sv_spec_destroy(s);

@@ -19,11 +19,12 @@ def test_reference_known_answers(i, level, api, load_model, load_seqs, golden):
     assert same_bits(v, golden[f"tiny{i}_spec{level}"])
 
 
-@pytest.mark.parametrize("method", ["sparse", "dense"])
+@pytest.mark.parametrize("method", ["sparse", "dense", "pair", "auto"])
 @pytest.mark.parametrize("name", ["100", "200"])
 def test_level2_reference_fixture(name, method, api, load_model, load_seqs, golden):
     from spec_viterbi_b200 import _lib
-    impl = api.B200_spec_impl(2, method=_lib.SPEC_DENSE_GEMM if method == "dense" else _lib.SPEC_SPARSE_LHS)
+    impl = api.B200_spec_impl(2, method={"dense": _lib.SPEC_DENSE_GEMM, "sparse": _lib.SPEC_SPARSE_LHS,
+                                         "pair": _lib.SPEC_PAIR_ROWS, "auto": _lib.SPEC_AUTO}[method])
     impl.spec_with(load_model(name))
     out = impl.run_Viterbi_spec_batch(load_seqs("emit_3_3500_20"))
     for k in range(3):
@@ -32,17 +33,35 @@ def test_level2_reference_fixture(name, method, api, load_model, load_seqs, gold
 
 @pytest.mark.parametrize("name", ["100", "300"])
 def test_handlers_bit_exact(name, api, oracle, load_model):
-    """Every compared pair handler equals the oracle's M_b (x) M_a, for both precompute kernels."""
+    """Every compared pair handler equals the oracle's M_b (x) M_a, for all three precompute kernels."""
     from spec_viterbi_b200 import _lib
     hmm = load_model(name)
     m = api.Model(hmm)
     osp = oracle.spec(hmm, 2)
     sparse = api.Spec(m, 2, _lib.SPEC_SPARSE_LHS)
     dense = api.Spec(m, 2, _lib.SPEC_DENSE_GEMM)
+    pair = api.Spec(m, 2, _lib.SPEC_PAIR_ROWS)
     for t in (0, 1, 19, 20, 57, 211, 399):
         exp = osp.handler(t)
         assert same_bits(sparse.handler(t), exp), t
         assert same_bits(dense.handler(t), exp), t
+        assert same_bits(pair.handler(t), exp), t
+
+
+def test_pair_rows_equals_sparse_lhs_on_large_models(api, load_model):
+    """K3'' against K3' (itself pinned to the oracle above) on the largest profile HMM (dense rows,
+    one dense column) and on a random sparse model with colliding (k, value) pairs."""
+    from spec_viterbi_b200 import generators, _lib
+    for hmm in (load_model("2405"), generators.random_hmm(states_num=700, seed=5)):
+        m = api.Model(hmm)
+        E = hmm.emit_num
+        for t0 in (0, 7 * E + 3, E * E - 2):
+            a = api.Spec(m, 2, _lib.SPEC_SPARSE_LHS, t0, t0 + 2)
+            b = api.Spec(m, 2, _lib.SPEC_PAIR_ROWS, t0, t0 + 2)
+            for t in (t0, t0 + 1):
+                assert same_bits(a.handler(t), b.handler(t)), t
+            a.close()
+            b.close()
 
 
 def test_random_model_levels(api, oracle):
@@ -50,7 +69,8 @@ def test_random_model_levels(api, oracle):
     hmm = generators.random_hmm(states_num=130, seed=9)
     rng = np.random.default_rng(1)
     seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 50, 301)]
-    for level, method in ((1, _lib.SPEC_AUTO), (2, _lib.SPEC_SPARSE_LHS), (2, _lib.SPEC_DENSE_GEMM)):
+    for level, method in ((1, _lib.SPEC_AUTO), (2, _lib.SPEC_SPARSE_LHS), (2, _lib.SPEC_DENSE_GEMM),
+                          (2, _lib.SPEC_PAIR_ROWS)):
         impl = api.B200_spec_impl(level, method=method)
         impl.spec_with(hmm)
         out = impl.run_Viterbi_spec_batch(seqs)
