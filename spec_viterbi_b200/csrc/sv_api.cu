@@ -403,6 +403,23 @@ int ensure_device(sv_seqs* s, size_t bytes) {
     return SV_OK;
 }
 
+// Device-side validation of a directly uploaded u8 symbol stream (symbol < emit_num): the host
+// never touches the caller's buffer (a scalar scan of 29 MB costs more than its PCIe copy).
+__global__ void sv_validate_u8_kernel(const uint8_t* __restrict__ sym, uint64_t total, unsigned emits,
+                                      unsigned* __restrict__ flag) {
+    const uint64_t words = total / 16;
+    const uint4* __restrict__ w = reinterpret_cast<const uint4*>(sym);
+    const unsigned lim = emits * 0x01010101u;
+    unsigned bad = 0;
+    for (uint64_t k = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; k < words;
+         k += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint4 v = w[k];
+        bad |= __vcmpgeu4(v.x, lim) | __vcmpgeu4(v.y, lim) | __vcmpgeu4(v.z, lim) | __vcmpgeu4(v.w, lim);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < total - words * 16) bad |= sym[words * 16 + threadIdx.x] >= emits;
+    if (bad) atomicOr(flag, 1u);
+}
+
 // (Re)fills a sequence batch: validates, packs symbols to u8/u16, builds the longest-first
 // work order and uploads on `st` (asynchronous; the pinned staging buffer is owned by `s`, so
 // the caller must not refill `s` before the stream has consumed it).  u8 input that needs no
@@ -432,12 +449,14 @@ int seqs_assign(sv_seqs* s, const sv_model* m, const SrcT* symbols, const uint64
     const size_t o_sym = blob_reserve<uint8_t>(&dbytes, total * sym_bytes + 16);
     const size_t o_off = blob_reserve<uint64_t>(&dbytes, nseq + 1);
     const size_t o_ord = blob_reserve<uint32_t>(&dbytes, nseq);
+    const size_t o_flag = blob_reserve<uint32_t>(&dbytes, 4);
     dbytes += 256;
     // host staging: [offsets][order][symbols unless direct]
     size_t hbytes = 0;
     const size_t h_off = blob_reserve<uint64_t>(&hbytes, nseq + 1);
     const size_t h_ord = blob_reserve<uint32_t>(&hbytes, nseq);
     const size_t h_sym = blob_reserve<uint8_t>(&hbytes, direct ? 16 : total * sym_bytes + 16);
+    const size_t h_flag = blob_reserve<uint32_t>(&hbytes, 4);
     int rc = ensure_pinned(s, hbytes);
     if (rc != SV_OK) return rc;
     if ((rc = ensure_device(s, dbytes)) != SV_OK) return rc;
@@ -447,9 +466,7 @@ int seqs_assign(sv_seqs* s, const sv_model* m, const SrcT* symbols, const uint64
     const SrcT* src = symbols + first;
     unsigned long long worst = 0;
     if (direct) {
-        unsigned mx = 0;
-        for (uint64_t k = 0; k < total; ++k) mx = std::max<unsigned>(mx, static_cast<unsigned>(src[k]));
-        worst = mx;
+        // validated on the device after the copy (below)
     } else if (sym_bytes == 1) {
         uint8_t* dst = host + h_sym;
         for (uint64_t k = 0; k < total; ++k) {
@@ -483,6 +500,15 @@ int seqs_assign(sv_seqs* s, const sv_model* m, const SrcT* symbols, const uint64
     if (direct) {
         SV_CUDA(cudaMemcpyAsync(base + o_sym, src, total, cudaMemcpyHostToDevice, st));
         SV_CUDA(cudaMemsetAsync(base + o_sym + total, 0, 16, st));
+        if (m->emits < 256 && total > 0) {
+            unsigned* d_flag = reinterpret_cast<unsigned*>(base + o_flag);
+            unsigned* h_flagp = reinterpret_cast<unsigned*>(host + h_flag);
+            SV_CUDA(cudaMemsetAsync(d_flag, 0, sizeof(unsigned), st));
+            sv_validate_u8_kernel<<<296, 256, 0, st>>>(base + o_sym, total, static_cast<unsigned>(m->emits), d_flag);
+            SV_CUDA(cudaMemcpyAsync(h_flagp, d_flag, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+            SV_CUDA(cudaStreamSynchronize(st)); // an invalid symbol must never reach a step kernel
+            if (*h_flagp != 0) return sv_fail(SV_ERR_ARG, "sequence upload: symbol >= emit_num");
+        }
     } else {
         SV_CUDA(cudaMemcpyAsync(base + o_sym, host + h_sym, total * sym_bytes + 16,
                                 cudaMemcpyHostToDevice, st));

@@ -135,3 +135,11 @@ def test_argument_errors(api, load_model):
         m.viterbi(np.zeros(0, np.uint64))          # empty sequence
     with pytest.raises(SvError):
         m.viterbi(np.array([0, 99], np.uint64))    # symbol >= emit_num
+    # packed u8 input is validated on the device (no host scan): bad symbol in the word body and in the tail
+    for pos in (5, 40):
+        syms = np.zeros(41, np.uint8)
+        syms[pos] = 200
+        with pytest.raises(SvError):
+            m.viterbi_batch(syms, np.array([0, 20, 41], np.uint64))
+    out, _, _ = m.viterbi_batch(np.zeros(41, np.uint8), np.array([0, 20, 41], np.uint64))  # still usable
+    assert out.shape[0] == 2
