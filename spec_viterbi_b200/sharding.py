@@ -80,6 +80,8 @@ def all_gather_table(table, ntuples: int, group=None) -> None:
     """In-place all-gather of a [ntuples, n, n] handler table whose rank-r slice
     [shard_tuples(ntuples, world, r)] has been computed locally."""
     import torch.distributed as dist
+    if not dist.is_available() or not dist.is_initialized():
+        return  # single process: the local range is the whole table
     world = dist.get_world_size(group)
     if world == 1:
         return
