@@ -344,6 +344,11 @@ def run_b200(args):
                     "relaxations_per_launch": relax, "relax_per_clk_per_sm": relax / kernel_s / (sm_count * mhz * 1e6),
                     "peak_source": f"{sm_count} SMs x 128 lanes x {mhz:.0f} MHz (NVML median during the run) / 1.5 issue "
                                    f"slots per (min,+) MAC; MEASURED_PEAKS.json ({peak_kind}) holds only HBM/bf16 peaks",
+                    # the resource that actually binds K2: 4 B gathered per relaxation + 4 B stored per
+                    # state update over the shared-memory crossbar (128 B/clk/SM)
+                    "smem_crossbar": {"achieved_GBs": (4.0 * relax + 4.0 * nseq * T * n) / kernel_s / 1e9,
+                                      "peak_GBs": sm_count * 128 * mhz * 1e6 / 1e9,
+                                      "frac": (4.0 * relax + 4.0 * nseq * T * n) / kernel_s / (sm_count * 128 * mhz * 1e6)},
                     "hbm_algorithmic_gbs": (syms.nbytes + d_out.numel() * 4) / kernel_s / 1e9,
                     "hbm_peak_gbs": peaks.get("hbm_gbs")}
         line = {
