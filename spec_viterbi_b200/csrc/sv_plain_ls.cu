@@ -348,14 +348,25 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     // Flags of the coming step and E[o_q][own rows] of its first group are fetched BEFORE the
     // barrier that ends the current step (here: before the loop).
     uint32_t et[NQ4][4][5];
-    uint4 fl; // x = init_mask, y = fin_mask, z = any_act of the coming step
+    uint4 fl;       // x = init_mask, y = fin_mask, z = any_act of the coming step
+    uint4 nfl, nc0; // ... in flight: flags and the first group's TMEM columns
+    // Two stages, because under load a shared-memory read takes hundreds of cycles and the in-order
+    // pipeline stalls at its first use: the control block is READ two small slices before the end
+    // of the step, the tensor-memory fetch that needs it is ISSUED after the last slice.
+    auto prefetch_ctl = [&](const LsCtl& nc) {
+        nfl = *reinterpret_cast<const uint4*>(&nc.init_mask);
+        nc0 = *reinterpret_cast<const uint4*>(&nc.col[0]);
+    };
+    auto prefetch_tmem = [&]() {
+        fl = nfl;
+        tmem_ld5(tE + nc0.x, et[0][0]);
+        tmem_ld5(tE + nc0.y, et[0][1]);
+        tmem_ld5(tE + nc0.z, et[0][2]);
+        tmem_ld5(tE + nc0.w, et[0][3]);
+    };
     auto prefetch_step = [&](const LsCtl& nc) {
-        fl = *reinterpret_cast<const uint4*>(&nc.init_mask);
-        const uint4 c0 = *reinterpret_cast<const uint4*>(&nc.col[0]);
-        tmem_ld5(tE + c0.x, et[0][0]);
-        tmem_ld5(tE + c0.y, et[0][1]);
-        tmem_ld5(tE + c0.z, et[0][2]);
-        tmem_ld5(tE + c0.w, et[0][3]);
+        prefetch_ctl(nc);
+        prefetch_tmem();
     };
     prefetch_step(ctl[0]);
 
@@ -374,8 +385,7 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         else
             ls_gather<0>(eo, pofs, io, 0, SH::at(0) >= 2);
         const LsCtl& c = ctl[tau & 3u];
-        [[maybe_unused]] uint4 cg1 = make_uint4(0u, 0u, 0u, 0u); // TMEM columns of group 1 (consumed five slices later)
-        if constexpr (NQ4 == 2) cg1 = *reinterpret_cast<const uint4*>(&c.col[4]);
+        [[maybe_unused]] uint4 cg1 = make_uint4(0u, 0u, 0u, 0u); // TMEM columns of group 1 (read in slice (0,3))
 
         // ---- managers first (off the tail of the step): control block of step tau + 2 ----
         if (warp == MW) {
@@ -436,6 +446,12 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 tmem_ld5(tE + cg1.y, et[g1][1]);
                 tmem_ld5(tE + cg1.z, et[g1][2]);
                 tmem_ld5(tE + cg1.w, et[g1][3]);
+            }
+            if constexpr (r == SH::R - 2) { // control reads, two small slices before they are needed
+                if constexpr (g + 1 < NQ4)
+                    cg1 = *reinterpret_cast<const uint4*>(&c.col[4 * (g + 1 < NQ4 ? g + 1 : 0)]);
+                else
+                    prefetch_ctl(ctl[(tau + 1u) & 3u]);
             }
             float e[4], acc[4];
 #pragma unroll
@@ -525,9 +541,9 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
         if (init_mask != 0) init_fix(0, Q);
 
-        // flags + first emission scores of step tau + 1 (published during step tau - 1): in flight
-        // across the barrier
-        prefetch_step(ctl[(tau + 1u) & 3u]);
+        // first emission scores of step tau + 1 (control block published during step tau - 1, read in
+        // slice (last group, 3)): in flight across the barrier
+        prefetch_tmem();
         __syncthreads();
 
         // ---- rare path: write out finished sequences, hand out new ones ----
