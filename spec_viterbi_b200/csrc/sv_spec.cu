@@ -258,27 +258,53 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
             }
             return acc;
         };
-        // the row as 16-byte stores where its (odd-length) placement allows, scalar head and tail
+        // the row as 16-byte stores where its (odd-length) placement allows, scalar head and tail; the
+        // streaming loop is specialised on the number of dense terms (0, 1, 2, more)
         const int kb = static_cast<int>((4u - ((reinterpret_cast<uintptr_t>(O) >> 2) & 3u)) & 3u);
         const int nb = (n - kb) / 4;
-        if (tid < kb) O[tid] = dense_at(tid);
-        for (int g = tid; g < nb; g += 256) {
-            const int k = kb + 4 * g;
-            *reinterpret_cast<float4*>(O + k) = make_float4(dense_at(k), dense_at(k + 1), dense_at(k + 2), dense_at(k + 3));
-        }
-        for (int k = kb + 4 * nb + tid; k < n; k += 256) O[k] = dense_at(k);
-        if (npairs > 0) {
-            __syncthreads(); // the row's stores are ordered before the patches
-            for (int t = tid; t < npairs; t += 256) {
-                const uint32_t k = s_pk[t];
-                float v = dense_at(static_cast<int>(k));
-                for (int t2 = 0; t2 < npairs; ++t2)
-                    if (s_pk[t2] == k) {
-                        const int q = s_pq[t2];
-                        v = fminf(v, (eb + s_w[q]) + (Ea[s_j[q]] + s_pw[t2]));
-                    }
-                O[k] = v; // entries with equal k write equal values
+        auto stream = [&](auto f) {
+            if (tid < kb) O[tid] = f(tid);
+            for (int g = tid; g < nb; g += 256) {
+                const int k = kb + 4 * g;
+                *reinterpret_cast<float4*>(O + k) = make_float4(f(k), f(k + 1), f(k + 2), f(k + 3));
             }
+            for (int k = kb + 4 * nb + tid; k < n; k += 256) O[k] = f(k);
+        };
+        if (nhv == 0)
+            stream([&](int) { return pos_inf(); });
+        else if (nhv == 1)
+            stream([&](int k) { return hu0 + (hea0 + hp0[k]); });
+        else if (nhv == 2)
+            stream([&](int k) { return fminf(hu0 + (hea0 + hp0[k]), hu1 + (hea1 + hp1[k])); });
+        else
+            stream(dense_at);
+        // patches: the (k, value) pairs of the light j.  A patch must land after the streamed store of
+        // its column: with few pairs every thread applies the patches of the columns IT streamed
+        // (program order, no barrier); with many, a barrier and one thread per pair.
+        auto patched = [&](uint32_t k) {
+            float v = dense_at(static_cast<int>(k));
+            for (int t2 = 0; t2 < npairs; ++t2)
+                if (s_pk[t2] == k) {
+                    const int q = s_pq[t2];
+                    v = fminf(v, (eb + s_w[q]) + (Ea[s_j[q]] + s_pw[t2]));
+                }
+            return v;
+        };
+        if (npairs > 0 && npairs <= 32) {
+            for (int t = 0; t < npairs; ++t) {
+                const int k = static_cast<int>(s_pk[t]);
+                int owner;
+                if (k < kb)
+                    owner = k;
+                else if (k < kb + 4 * nb)
+                    owner = ((k - kb) >> 2) & 255;
+                else
+                    owner = (k - kb - 4 * nb) & 255;
+                if (owner == tid) O[k] = patched(static_cast<uint32_t>(k));
+            }
+        } else if (npairs > 32) {
+            __syncthreads(); // the row's stores are ordered before the patches
+            for (int t = tid; t < npairs; t += 256) O[s_pk[t]] = patched(s_pk[t]); // equal k: equal values
         }
     }
 }

@@ -52,7 +52,9 @@ def test_pair_rows_equals_sparse_lhs_on_large_models(api, load_model):
     """K3'' against K3' (itself pinned to the oracle above) on the largest profile HMM (dense rows,
     one dense column) and on a random sparse model with colliding (k, value) pairs."""
     from spec_viterbi_b200 import generators, _lib
-    for hmm in (load_model("2405"), generators.random_hmm(states_num=700, seed=5)):
+    for hmm in (load_model("2405"), generators.random_hmm(states_num=700, seed=5),
+                generators.random_hmm(states_num=300, trans_per_state=9, seed=6),     # > 32 pairs per row: barrier path
+                generators.random_hmm(states_num=60, trans_per_state=40, seed=7)):   # every row heavy: CSC walk
         m = api.Model(hmm)
         E = hmm.emit_num
         for t0 in (0, 7 * E + 3, E * E - 2):
