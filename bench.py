@@ -53,6 +53,32 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
 
 
+def ncu_traffic(kernel_substr: str, workload: str):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary
+    (profiles/*_ncu_summary.txt, written by tools/ncu_summary.py); None if there is none for this workload."""
+    if workload != "synthetic2405":
+        return None, None
+    best = None
+    for f in sorted((ROOT / "profiles").glob("*_ls_*ncu_summary.txt")):
+        if "profile2405" in f.name:
+            continue
+        rd = wr = None
+        ok = False
+        for ln in f.read_text().splitlines():
+            parts = ln.split("\t")
+            if parts[0] == "Kernel Name":
+                ok = kernel_substr in parts[-1]
+            if len(parts) == 3 and ok:
+                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(parts[1])
+                if parts[0] == "dram__bytes_read.sum" and scale:
+                    rd = float(parts[2]) * scale
+                if parts[0] == "dram__bytes_write.sum" and scale:
+                    wr = float(parts[2]) * scale
+        if rd is not None and wr is not None:
+            best = (rd + wr, f.name)
+    return best if best else (None, None)
+
+
 def make_workload(name: str, rank: int):
     from spec_viterbi_b200 import api, generators
     w = WORKLOADS[name]
@@ -338,8 +364,9 @@ def run_b200(args):
         # measured during the run
         achieved = 2.0 * relax / kernel_s / 1e12
         peak = 2.0 * sm_count * 128 * mhz * 1e6 / 1.5 / 1e12
+        traffic, traffic_src = ncu_traffic("sv_ls_kernel", args.workload) if info.kernel == _lib.KERNEL_LS else (None, None)
         roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": None,
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                     "kernel": {_lib.KERNEL_ES: "sv_es_kernel", _lib.KERNEL_LS: "sv_ls_kernel"}.get(info.kernel, "sv_plain_generic_kernel"),
                     "relaxations_per_launch": relax, "relax_per_clk_per_sm": relax / kernel_s / (sm_count * mhz * 1e6),
                     "peak_source": f"{sm_count} SMs x 128 lanes x {mhz:.0f} MHz (NVML median during the run) / 1.5 issue "

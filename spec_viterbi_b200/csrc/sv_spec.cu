@@ -260,7 +260,9 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
         };
         // the row as 16-byte stores where its (odd-length) placement allows, scalar head and tail; the
         // streaming loop is specialised on the number of dense terms (0, 1, 2, more)
-        const int kb = static_cast<int>((4u - ((reinterpret_cast<uintptr_t>(O) >> 2) & 3u)) & 3u);
+        // (the vector body starts on a 128-byte line, so that every warp store writes whole lines: partially
+        //  written lines cost a read-modify-write in the memory system)
+        const int kb = min(n, static_cast<int>((32u - ((reinterpret_cast<uintptr_t>(O) >> 2) & 31u)) & 31u));
         const int nb = (n - kb) / 4;
         auto stream = [&](auto f) {
             if (tid < kb) O[tid] = f(tid);
