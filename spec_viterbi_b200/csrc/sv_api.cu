@@ -144,6 +144,14 @@ int upload_es(sv_model* m) {
     d.n_int = p.n_int;
     d.n_light = p.n_light;
     d.n_heavy = p.n_heavy;
+    {
+        auto ok = [](float x) { return !(x < 0.0f) && x == x; };
+        bool nn = true;
+        for (const float x : m->csr.w) nn &= ok(x);
+        for (const float x : m->emis) nn &= ok(x);
+        for (const float x : m->start) nn &= ok(x);
+        d.nonneg = nn ? 1 : 0;
+    }
     d.emits = static_cast<int>(m->emits);
     d.nslots = p.nslots;
     d.edge_w = reinterpret_cast<const float*>(base + o_w);

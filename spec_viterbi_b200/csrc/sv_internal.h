@@ -88,6 +88,7 @@ struct SvEsPlan {
 
 struct SvEsDev {
     int n = 0, n_int = 0, n_light = 0, n_heavy = 0, emits = 0, nslots = 0;
+    int nonneg = 0; // scores are >= 0: warp minima may use the integer REDUX unit
     const float* edge_w = nullptr;
     const uint32_t* edge_off = nullptr;
     const uint8_t* deg = nullptr;

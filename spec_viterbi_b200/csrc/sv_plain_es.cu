@@ -262,9 +262,13 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                                                                      he, acc);
 #pragma unroll
                     for (int q = 0; q < Q; ++q) {
+                        if (m.nonneg) { // float order == signed-int order: one REDUX instead of five shuffle stages
+                            acc[q] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(acc[q])));
+                        } else {
 #pragma unroll
-                        for (int d = 16; d > 0; d >>= 1)
-                            acc[q] = fminf(acc[q], __shfl_xor_sync(0xffffffffu, acc[q], d));
+                            for (int d = 16; d > 0; d >>= 1)
+                                acc[q] = fminf(acc[q], __shfl_xor_sync(0xffffffffu, acc[q], d));
+                        }
                         if (lane == 0) red[(h * NW + warp) * Q + q] = acc[q];
                     }
                 }
@@ -281,9 +285,13 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 #pragma unroll
                     for (int q = 0; q < Q; ++q) {
                         float x = lane < NW ? red[(h * NW + lane) * Q + q] : pos_inf();
+                        if (m.nonneg) {
+                            x = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(x)));
+                        } else {
 #pragma unroll
-                        for (int d = 16; d > 0; d >>= 1)
-                            x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
+                            for (int d = 16; d > 0; d >>= 1)
+                                x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
+                        }
                         acc[q] = x;
                         if (init[q]) acc[q] = erow[q][ph] + m.start_p[ph];
                     }
