@@ -19,6 +19,7 @@ SOURCES = [
     "csrc/sv_plain_generic.cu",
     "csrc/sv_plain_es.cu",
     "csrc/sv_plain_ls.cu",
+    "csrc/sv_plain_ls2.cu",
     "csrc/sv_spec.cu",
     "csrc/sv_probe.cu",
     "csrc/sv_es_plan.cpp",
@@ -26,7 +27,7 @@ SOURCES = [
     "csrc/sv_io.cpp",
     "host/data_reader.cpp",
 ]
-HEADERS = ["csrc/sv_internal.h", "host/data_reader.h", "host/HMM.h", "../include/spec_viterbi_b200.h"]
+HEADERS = ["csrc/sv_internal.h", "csrc/sv_ls_device.cuh", "host/data_reader.h", "host/HMM.h", "../include/spec_viterbi_b200.h"]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17",

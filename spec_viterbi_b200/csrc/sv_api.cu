@@ -364,7 +364,7 @@ extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
     }
     if (m->ls.valid) {
         info->ls_threads = m->ls.var.threads;
-        info->ls_seqs_per_cta = 4 * m->ls.var.nq4;
+        info->ls_seqs_per_cta = 4 * m->ls.var.nq4 * m->ls.var.halves;
         info->ls_ranks = m->ls.ranks;
         info->ls_heavy_rows = m->ls.n_heavy;
         info->ls_tmem_cols = m->ls.tmem_cols;
@@ -653,7 +653,7 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
     m->last_nseq = seqs->nseq;
     m->last_kernel = kernel;
     if (kernel == SV_KERNEL_LS) {
-        const int q = 4 * m->ls.var.nq4;
+        const int q = 4 * m->ls.var.nq4 * m->ls.var.halves;
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
         const int grid = static_cast<int>(std::min<int64_t>(want, m->sm_count));
         rc = sv_ls_launch(m->ls.variant_index, m->lsdev, seqs->dev, d_out, d_best, d_best_state,

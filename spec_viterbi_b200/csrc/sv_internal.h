@@ -113,14 +113,17 @@ int sv_es_prepare(int index, size_t smem); // sets the dynamic smem attribute
 // emission table lives in TENSOR MEMORY (tcgen05.ld lookup), which frees the shared memory
 // for the score vectors.  K0 colours the states so that the 8 lanes of every LDS.128 phase hit
 // 8 distinct 16-byte bank groups.
-constexpr int SV_LS_RSTRIDE = SV_ES_RMAX; // TMEM columns per symbol (one per rank)
+constexpr int SV_LS_RSTRIDE = SV_ES_RMAX; // TMEM columns per symbol (one per rank) of the 5-rank variants
+constexpr int SV_LS_RMAX = 10;            // rank capacity of any lockstep variant
 
 struct SvLsVariant {
-    int threads;                 // threads per CTA
-    int nq4;                     // float4 groups of sequences: Q = 4 * nq4
-    int shape[SV_ES_RMAX];       // max register slots per rank
+    int threads;                 // threads that share one set of rows (a CTA, or one HALF of a CTA)
+    int nq4;                     // float4 groups of sequences per set: Q = 4 * nq4
+    int shape[SV_LS_RMAX];       // max register slots per rank
     int nh;                      // heavy rows supported
     int hs;                      // register slots per heavy row per thread
+    int ranks;                   // rows per thread (5 or 10)
+    int halves;                  // independent thread sets per CTA (1, or 2 with their own barriers)
 };
 
 struct SvLsPlan {
@@ -149,7 +152,7 @@ struct SvLsDev {
     int nonneg = 0; // scores are >= 0: warp minima may use the integer REDUX unit
     const float* edge_w = nullptr;
     const uint32_t* edge_off = nullptr;
-    const uint8_t* deg = nullptr;
+    const uint8_t* deg = nullptr;    // [warps][variant ranks]
     uint8_t heavy_slots[SV_ES_NHMAX] = {0, 0};
     const float* emis_p = nullptr;
     const float* start_p = nullptr;

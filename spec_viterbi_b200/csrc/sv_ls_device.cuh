@@ -1,0 +1,188 @@
+// Device helpers shared by the lockstep step kernels (sv_plain_ls.cu: one thread set per CTA;
+// sv_plain_ls2.cu: two independent halves per CTA).  Internal to the library.
+#pragma once
+#include "sv_internal.h"
+
+#include <type_traits>
+
+namespace {
+
+__device__ __forceinline__ float pos_inf() { return __int_as_float(0x7f800000); }
+
+template <int... S> struct LShape {
+    static constexpr int R = sizeof...(S);
+    __host__ __device__ static constexpr int at(int r) {
+        constexpr int v[] = {S...};
+        return v[r];
+    }
+    __host__ __device__ static constexpr int base(int r) {
+        int b = 0;
+        for (int k = 0; k < r; ++k) b += at(k);
+        return b;
+    }
+    __host__ __device__ static constexpr int total() { return base(R); }
+};
+
+// ---- tensor memory ----
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {
+    const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(smem_slot));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst), "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_free(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_st1(uint32_t taddr, float v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(__float_as_uint(v))
+                 : "memory");
+}
+// E[o][own rows of ranks 0..4] of one sequence: 5 consecutive TMEM columns at a run-time address.
+__device__ __forceinline__ void tmem_ld5(uint32_t taddr, uint32_t (&r)[5]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr)
+                 : "memory");
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r[4]) : "r"(taddr + 4u) : "memory");
+}
+// v'[own row] of 4 sequences: 32-bit shared address + immediate (no generic-pointer arithmetic)
+template <int IMM>
+__device__ __forceinline__ void sts128(uint32_t addr, const float (&a)[4]) {
+    asm volatile("st.shared.v4.f32 [%0+%1], {%2,%3,%4,%5};" ::"r"(addr), "n"(IMM), "f"(a[0]), "f"(a[1]), "f"(a[2]),
+                 "f"(a[3])
+                 : "memory");
+}
+// Per-step control block published by the manager lanes.
+struct alignas(16) LsCtl {
+    uint32_t col[8];    // TMEM column offset of each sequence's current symbol: symbol * RSTRIDE
+    uint32_t init_mask; // sequences whose step is v_0 = E[o_0] + start
+    uint32_t fin_mask;  // sequences for which this step is the last one
+    uint32_t any_act;   // sequences that take part in this step (0 = CTA is done)
+    uint32_t pad;
+};
+
+// Sequence-manager state of one sequence slot lives in REGISTERS of lane q of the manager warp:
+// under load a shared-memory round trip takes hundreds of cycles (the crossbar queue is deep), and
+// a manager that chases its state through shared memory falls a thousand cycles behind the other
+// warps every step.  Only the sequence id (needed on the rare write-out path) is kept in memory.
+struct LsMgr {
+    uint32_t sid;
+};
+
+// fl(fl(E + T') + v) -- the two adds are never re-associated (GraphBLAS_impl.cpp:65,69)
+__device__ __forceinline__ float relax1(float e, float w, float v) { return (e + w) + v; }
+
+// One pair of slots for 4 sequences: acc = min(acc, x0, x1) is a single 3-input FMNMX3.
+template <bool FIRST>
+__device__ __forceinline__ void pair4(float w0, float w1, const float4 a, const float4 b, const float* e,
+                                      float* acc) {
+    const float x0 = fminf(relax1(e[0], w0, a.x), relax1(e[0], w1, b.x));
+    const float x1 = fminf(relax1(e[1], w0, a.y), relax1(e[1], w1, b.y));
+    const float x2 = fminf(relax1(e[2], w0, a.z), relax1(e[2], w1, b.z));
+    const float x3 = fminf(relax1(e[3], w0, a.w), relax1(e[3], w1, b.w));
+    if (FIRST) {
+        acc[0] = x0; acc[1] = x1; acc[2] = x2; acc[3] = x3;
+    } else {
+        acc[0] = fminf(acc[0], x0); acc[1] = fminf(acc[1], x1);
+        acc[2] = fminf(acc[2], x2); acc[3] = fminf(acc[3], x3);
+    }
+}
+template <bool FIRST>
+__device__ __forceinline__ void single4(float w0, const float4 a, const float* e, float* acc) {
+    const float x0 = relax1(e[0], w0, a.x), x1 = relax1(e[1], w0, a.y);
+    const float x2 = relax1(e[2], w0, a.z), x3 = relax1(e[3], w0, a.w);
+    if (FIRST) {
+        acc[0] = x0; acc[1] = x1; acc[2] = x2; acc[3] = x3;
+    } else {
+        acc[0] = fminf(acc[0], x0); acc[1] = fminf(acc[1], x1);
+        acc[2] = fminf(acc[2], x2); acc[3] = fminf(acc[3], x3);
+    }
+}
+
+// Gather of one slot: volatile, so the software pipeline below is emitted in the order written
+// (the relaxations float freely around the loads).  addr = absolute shared address of v[src] in
+// buffer 0 + parity offset (a uniform register); the float4-group offset is an immediate.
+template <int IMM>
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4+%5];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(addr), "n"(IMM)
+                 : "memory");
+    return v;
+}
+
+// Gathered scores of one slot pair (4 sequences).
+struct LsPair {
+    float4 a, b;
+};
+
+// k / both are compile-time constants after unrolling (register indices stay static).  `eo(k)` returns
+// the shared address (or offset) of slot k: a plain register array element, or one half of a register
+// that packs two 16-bit offsets.
+template <int GOFF, typename EO>
+__device__ __forceinline__ void ls_gather(const EO& eo, uint32_t pofs, LsPair& d, int k, bool both) {
+    d.a = lds128<GOFF>(eo(k) + pofs);
+    if (both) d.b = lds128<GOFF>(eo(k + 1) + pofs);
+}
+
+// D slots (compile-time) of the register slice [BASE, BASE + D) for the 4 sequences of the float4
+// group at byte offset GOFF, as straight-line code, slot PAIRS at a time with register double
+// buffering: the gathers of pair p + 1 are issued before the relaxations of pair p, and before the
+// last pair the FIRST pair of the next slice (NBASE >= 0: next rank, or rank 0 of the next group,
+// at group offset NGOFF) is issued, so that only the first gather of a time step is exposed.
+// `io` holds this slice's first pair on entry and the next slice's first pair on exit.
+template <int GOFF, int BASE, int D, int NGOFF, int NBASE, bool NBOTH, int NSLOTS, typename EO>
+__device__ __forceinline__ void ls_fixed(const float (&ew)[NSLOTS], const EO& eo, uint32_t pofs,
+                                         uint32_t npofs, const float (&e)[4], float (&acc)[4], LsPair& io) {
+    if constexpr (D == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[q] = pos_inf();
+        if constexpr (NBASE >= 0) ls_gather<NGOFF>(eo, npofs, io, NBASE, NBOTH);
+    } else {
+        constexpr int NP = (D + 1) / 2;
+        LsPair buf[NP + 1];
+        buf[0] = io;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+            if (p + 1 < NP)
+                ls_gather<GOFF>(eo, pofs, buf[p + 1], BASE + 2 * p + 2, 2 * p + 3 < D);
+            else if (NBASE >= 0)
+                ls_gather<NGOFF>(eo, npofs, buf[p + 1], NBASE, NBOTH);
+            const int k = BASE + 2 * p;
+            if (2 * p + 1 < D) {
+                if (p == 0)
+                    pair4<true>(ew[k], ew[k + 1], buf[p].a, buf[p].b, e, acc);
+                else
+                    pair4<false>(ew[k], ew[k + 1], buf[p].a, buf[p].b, e, acc);
+            } else {
+                if (p == 0)
+                    single4<true>(ew[k], buf[p].a, e, acc);
+                else
+                    single4<false>(ew[k], buf[p].a, e, acc);
+            }
+        }
+        if constexpr (NBASE >= 0) io = buf[NP];
+    }
+}
+
+// Runs slots [0, d) of the register slice [BASE, BASE + SMAX).  d is warp-uniform and lies in
+// [LO, HI]: a binary tree of uniform branches into straight-line code (a jump table costs a
+// constant-bank load and an indirect branch per slice).
+template <int GOFF, int BASE, int LO, int HI, int NGOFF, int NBASE, bool NBOTH, int NSLOTS, typename EO>
+__device__ __forceinline__ void ls_run_slots(int d, const float (&ew)[NSLOTS], const EO& eo,
+                                             uint32_t pofs, uint32_t npofs, const float (&e)[4], float (&acc)[4],
+                                             LsPair& io) {
+    static_assert(HI <= 8, "at most 8 slots per rank");
+    if constexpr (LO == HI) {
+        ls_fixed<GOFF, BASE, LO, NGOFF, NBASE, NBOTH, NSLOTS>(ew, eo, pofs, npofs, e, acc, io);
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (d <= MID)
+            ls_run_slots<GOFF, BASE, LO, MID, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, npofs, e, acc, io);
+        else
+            ls_run_slots<GOFF, BASE, MID + 1, HI, NGOFF, NBASE, NBOTH, NSLOTS>(d, ew, eo, pofs, npofs, e, acc, io);
+    }
+}
+
+} // namespace

@@ -421,10 +421,11 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     const int TPG = var.threads, NW = TPG / 32, Q = 4 * var.nq4;
     const size_t n = csr.n;
     const size_t cap = var.shape[0];
-    const size_t max_light = static_cast<size_t>(SV_ES_RMAX) * TPG;
+    const int R = var.ranks;
+    const size_t max_light = static_cast<size_t>(R) * TPG;
     if (n > max_light + var.nh) return false;
     // tensor memory: one column per (warp group, symbol, rank)
-    const size_t tcols_need = static_cast<size_t>(NW / 4) * emits * SV_LS_RSTRIDE;
+    const size_t tcols_need = static_cast<size_t>(NW / 4) * emits * R;
     if (tcols_need > 512 || emits > 256) return false;
     int tcols = 32;
     while (static_cast<size_t>(tcols) < tcols_need) tcols *= 2;
@@ -474,9 +475,9 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
 
     // ---- shared memory: 2 buffers x nq4 groups x n_pad float4, heavy reduction scratch ----
     // (static layout: every float4 group is sized for the largest model the variant takes)
-    const size_t npad_max = static_cast<size_t>(SV_ES_RMAX) * TPG + 8;
+    const size_t npad_max = static_cast<size_t>(R) * TPG + 8;
     if (static_cast<size_t>(n_pad) > npad_max) return false;
-    const size_t smem = static_cast<size_t>(2) * var.nq4 * npad_max * 16 +
+    const size_t smem = static_cast<size_t>(2) * var.nq4 * var.halves * npad_max * 16 +
                         static_cast<size_t>(var.nh) * NW * Q * 4;
     if (smem + 1024 > smem_limit) return false;
 
@@ -525,7 +526,7 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
         for (size_t h = 0; h < n_heavy; ++h) col.pos_of[heavy_rows[h]] = static_cast<uint32_t>(n_lpad + h);
     }
     col.cellD.assign(n_lpad / 32, 0);
-    std::vector<uint8_t> deg(static_cast<size_t>(NW) * SV_ES_RMAX, 0);
+    std::vector<uint8_t> deg(static_cast<size_t>(NW) * R, 0);
     for (int r = 0; r < nranks; ++r) {
         for (int w = 0; w < NW; ++w) {
             size_t d = 0;
@@ -534,7 +535,7 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
                 if (row >= 0) d = std::max(d, g.in[row].size());
             }
             if (d > static_cast<size_t>(var.shape[r])) return false;
-            deg[static_cast<size_t>(w) * SV_ES_RMAX + r] = static_cast<uint8_t>(d);
+            deg[static_cast<size_t>(w) * R + r] = static_cast<uint8_t>(d);
             col.cellD[(static_cast<size_t>(r) * TPG + w * 32) / 32] = static_cast<uint8_t>(d);
         }
     }
@@ -551,10 +552,10 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->colour_cost_after = static_cast<uint64_t>(col.cost);
 
     // ---- slot assignment per octet, register images ----
-    int base[SV_ES_RMAX + 1];
+    int base[SV_LS_RMAX + 1];
     base[0] = 0;
-    for (int r = 0; r < SV_ES_RMAX; ++r) base[r + 1] = base[r] + var.shape[r];
-    const int NL = base[SV_ES_RMAX];
+    for (int r = 0; r < R; ++r) base[r + 1] = base[r] + var.shape[r];
+    const int NL = base[R];
     const int NSL = NL + var.nh * var.hs;
     plan->edge_w.assign(static_cast<size_t>(NSL) * TPG, kInf);
     plan->edge_off.assign(static_cast<size_t>(NSL) * TPG, 0);
@@ -562,7 +563,7 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     Rng rng(977u + n);
     for (int r = 0; r < nranks; ++r) {
         for (int w = 0; w < NW; ++w) {
-            const int D = deg[static_cast<size_t>(w) * SV_ES_RMAX + r];
+            const int D = deg[static_cast<size_t>(w) * R + r];
             for (int o = 0; o < 4; ++o) {
                 const int p0 = r * TPG + w * 32 + o * 8;
                 std::vector<std::vector<OEdge>> rows(8);
@@ -690,11 +691,14 @@ void sv_ls_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->valid = false;
     int want_nq4 = 0;
     if (const char* env = std::getenv("SV_LS_NQ4")) want_nq4 = std::atoi(env);
+    int max_halves = 1; // two-halves variants are opt-in (SV_LS_HALVES=2)
+    if (const char* env = std::getenv("SV_LS_HALVES")) max_halves = std::atoi(env);
     uint64_t sa_iters = std::min<uint64_t>(8000000ull, 3300ull * csr.n);
     if (const char* env = std::getenv("SV_LS_SA_ITERS")) sa_iters = std::strtoull(env, nullptr, 10);
     // variants are listed in order of preference; the first that fits wins
     for (int v = 0; v < sv_ls_num_variants(); ++v) {
         if (want_nq4 != 0 && sv_ls_variant(v).nq4 != want_nq4) continue;
+        if (sv_ls_variant(v).halves > max_halves) continue;
         SvLsPlan cand;
         if (ls_try_variant(csr, emis, start, emits, smem_limit, v, sa_iters, &cand)) {
             *plan = std::move(cand);
@@ -755,7 +759,7 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
     if (!plan.valid) return SV_OK;
     const int TPG = plan.var.threads, NW = TPG / 32;
     stats[1] = TPG;
-    stats[2] = 4 * plan.var.nq4;
+    stats[2] = 4 * plan.var.nq4 * plan.var.halves;
     stats[3] = plan.ranks;
     stats[4] = plan.n_heavy;
     stats[5] = plan.split_states;
@@ -766,10 +770,11 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
     stats[10] = plan.smem_bytes;
     stats[11] = plan.tmem_cols;
     if (seq == nullptr || len == 0 || out == nullptr) return SV_OK;
-    int base[SV_ES_RMAX + 1];
+    const int R = plan.var.ranks;
+    int base[SV_LS_RMAX + 1];
     base[0] = 0;
-    for (int r = 0; r < SV_ES_RMAX; ++r) base[r + 1] = base[r] + plan.var.shape[r];
-    const int NL = base[SV_ES_RMAX];
+    for (int r = 0; r < R; ++r) base[r + 1] = base[r] + plan.var.shape[r];
+    const int NL = base[R];
     const int n_pad = plan.n_pad;
     std::vector<float> cur(n_pad, kInf), nxt(n_pad, kInf);
     for (uint64_t t = 0; t < len; ++t) {
@@ -779,7 +784,7 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
             const int r = p / TPG, tid = p % TPG, w = tid / 32;
             const float e = em[p];
             float acc = kInf;
-            const int D = plan.deg[static_cast<size_t>(w) * SV_ES_RMAX + r];
+            const int D = plan.deg[static_cast<size_t>(w) * R + r];
             for (int k = 0; k < D; ++k) {
                 const size_t slot = static_cast<size_t>(base[r] + k) * TPG + tid;
                 acc = std::fmin(acc, (e + plan.edge_w[slot]) + cur[plan.edge_off[slot] / 16]);
