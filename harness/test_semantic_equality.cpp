@@ -7,7 +7,9 @@
 // usage: test_semantic_equality <models dir> <sequence file> [max states for level 2 = 400]
 #include "harness_common.h"
 
+#include <cstdio>
 #include <dirent.h>
+#include <unistd.h>
 
 #include <iostream>
 #include <memory>
@@ -60,6 +62,19 @@ int main(int argc, char** argv) {
                 std::cout << "MISMATCH " << f << " sequence " << s << "\n";
                 ++failures;
             }
+        }
+        // smallest model: the level-2 tables survive a save / attach round trip (not in the reference)
+        if (&f == &files.front() && spec.size() > 1) {
+            const std::string tmp = "/tmp/sv_tables_" + std::to_string(::getpid()) + ".svht";
+            spec[1]->save_tables(tmp);
+            B200_spec_impl again(2);
+            again.spec_with_saved(hmm, tmp);
+            std::remove(tmp.c_str());
+            for (const auto& sq : sequences)
+                if (!harness::bit_equal(spec[1]->run_Viterbi_spec(sq), again.run_Viterbi_spec(sq))) {
+                    std::cout << "MISMATCH after save/load " << f << "\n";
+                    ++failures;
+                }
         }
         std::cout << hmm.states_num << " states: ok (" << spec.size() << " spec levels)" << std::endl;
     }

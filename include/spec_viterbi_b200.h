@@ -163,6 +163,16 @@ float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_t* tuple_en
 /* Copies one dense handler (states*states floats, row = destination state) to the host. */
 int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out);
 
+/* Handler-table persistence (level >= 2).  The reference rebuilds every table in each spec_with
+ * call (GraphBLAS_spec_impl.cpp:45-48); these two keep a built table across processes.
+ * sv_spec_save writes the valid tuple range of the table (64-byte header + dense handlers);
+ * sv_spec_load attaches a saved table to `m` without recomputing it -- it fails with SV_ERR_ARG
+ * if the file was built from a different model (dimensions and a fingerprint of T' and the
+ * emissions are checked).  d_table: optional caller-owned device buffer for the loaded range
+ * (as in sv_spec_create), NULL = allocate. */
+int sv_spec_save(const sv_spec* s, const char* path);
+int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out);
+
 int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out);
 int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
                       float* out, float* best, int32_t* best_state);

@@ -68,6 +68,8 @@ SIGNATURES = {
     "sv_spec_set_range": (C.c_int, [vp, C.c_uint64, C.c_uint64]),
     "sv_spec_table": (vp, [vp, u64p, u64p]),
     "sv_spec_get_handler": (C.c_int, [vp, C.c_uint64, f32p]),
+    "sv_spec_save": (C.c_int, [vp, C.c_char_p]),
+    "sv_spec_load": (C.c_int, [vp, C.c_char_p, vp, C.POINTER(vp)]),
     "sv_spec_run": (C.c_int, [vp, u64p, C.c_uint64, f32p]),
     "sv_spec_run_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, f32p, f32p, i32p]),
     "sv_spec_run_batch_u8": (C.c_int, [vp, u8p, u64p, C.c_uint64, f32p, f32p, i32p]),

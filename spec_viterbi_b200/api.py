@@ -291,6 +291,21 @@ class Spec:
         L.check(self._lib.sv_spec_create(model.handle, level, method, tuple_begin, tuple_end,
                                          d_table or None, stream or None, C.byref(self._h)))
 
+    @classmethod
+    def load(cls, model: Model, path, d_table: int = 0) -> "Spec":
+        """Attaches a handler table written by `save` (sv_spec_load); no recomputation."""
+        self = cls.__new__(cls)
+        self._lib = L.lib()
+        self.model = model
+        self._h = C.c_void_p()
+        L.check(self._lib.sv_spec_load(model.handle, str(path).encode(), d_table or None, C.byref(self._h)))
+        self.level = int(self._lib.sv_spec_level(self._h))
+        return self
+
+    def save(self, path) -> None:
+        """Writes the valid tuple range of the handler table to `path` (sv_spec_save)."""
+        L.check(self._lib.sv_spec_save(self._h, str(path).encode()))
+
     @property
     def handle(self):
         return self._h

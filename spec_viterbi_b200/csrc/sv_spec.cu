@@ -12,9 +12,11 @@
 #include "sv_internal.h"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstring>
 #include <limits>
 #include <new>
+#include <string>
 #include <vector>
 
 struct sv_spec {
@@ -814,6 +816,179 @@ extern "C" int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float
     SV_CUDA(cudaSetDevice(s->m->device));
     SV_CUDA(cudaMemcpy(out, s->d_table + (tuple_index - s->table_first) * mat, mat * sizeof(float),
                        cudaMemcpyDeviceToHost));
+    return SV_OK;
+}
+
+// ---------------------------------------------------------------- persistence ----
+// Handler tables on disk (the reference rebuilds every table in each spec_with call,
+// GraphBLAS_spec_impl.cpp:45-48).  File = 64-byte header + the dense handlers of [t_begin, t_end) in tuple
+// order, row = destination state.  The header carries a fingerprint of the model the table was built
+// from, so a table is never attached to a different model.
+namespace {
+
+constexpr char kTableMagic[8] = {'S', 'V', 'H', 'T', '0', '0', '0', '1'};
+constexpr size_t kIoChunk = 64ull << 20; // bytes per pinned staging buffer (two of them, double buffered)
+
+struct TableHeader {
+    char magic[8];
+    uint64_t states, emits, level, t_begin, t_end, fingerprint, reserved;
+};
+static_assert(sizeof(TableHeader) == 64, "table header layout");
+
+uint64_t fnv1a(uint64_t h, const void* p, size_t bytes) {
+    const unsigned char* b = static_cast<const unsigned char*>(p);
+    for (size_t k = 0; k < bytes; ++k) h = (h ^ b[k]) * 1099511628211ull;
+    return h;
+}
+
+// Every bit that enters a handler: T' (CSR, FIRST-wins duplicates already applied), emissions, dims.
+uint64_t model_fingerprint(const sv_model* m) {
+    uint64_t h = 1469598103934665603ull;
+    const uint64_t dims[3] = {m->n, m->emits, m->nnz};
+    h = fnv1a(h, dims, sizeof(dims));
+    h = fnv1a(h, m->csr.rowptr.data(), m->csr.rowptr.size() * sizeof(uint32_t));
+    h = fnv1a(h, m->csr.col.data(), m->csr.col.size() * sizeof(uint32_t));
+    h = fnv1a(h, m->csr.w.data(), m->csr.w.size() * sizeof(float));
+    h = fnv1a(h, m->emis.data(), m->emis.size() * sizeof(float));
+    return h;
+}
+
+struct PinnedPair {
+    void* p[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    cudaStream_t st = nullptr;
+    ~PinnedPair() {
+        for (int k = 0; k < 2; ++k) {
+            if (p[k]) cudaFreeHost(p[k]);
+            if (ev[k]) cudaEventDestroy(ev[k]);
+        }
+        if (st) cudaStreamDestroy(st);
+    }
+    bool init() {
+        if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return false;
+        for (int k = 0; k < 2; ++k)
+            if (cudaMallocHost(&p[k], kIoChunk) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming) != cudaSuccess)
+                return false;
+        return true;
+    }
+};
+
+} // namespace
+
+extern "C" int sv_spec_save(const sv_spec* s, const char* path) {
+    if (s == nullptr || path == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_save: NULL");
+    if (s->level < 2) return sv_fail(SV_ERR_ARG, "sv_spec_save: level 1 has no handler table (K2 forms E+T' on the fly)");
+    const sv_model* m = s->m;
+    SV_CUDA(cudaSetDevice(m->device));
+    SV_CUDA(cudaDeviceSynchronize()); // the table may still be under construction on a caller's stream
+    PinnedPair io;
+    if (!io.init()) {
+        cudaGetLastError();
+        return sv_fail(SV_ERR_MEMORY, "sv_spec_save: no pinned staging memory");
+    }
+    FILE* f = std::fopen(path, "wb");
+    if (f == nullptr) return sv_fail(SV_ERR_IO, std::string("sv_spec_save: cannot open ") + path);
+    TableHeader h{};
+    std::memcpy(h.magic, kTableMagic, 8);
+    h.states = m->n; h.emits = m->emits; h.level = s->level;
+    h.t_begin = s->t_begin; h.t_end = s->t_end; h.fingerprint = model_fingerprint(m);
+    bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1;
+    const size_t mat = static_cast<size_t>(m->n) * m->n * sizeof(float);
+    const char* src = reinterpret_cast<const char*>(s->d_table) + (s->t_begin - s->table_first) * mat;
+    const size_t total = (s->t_end - s->t_begin) * mat;
+    // D2H of chunk k+1 overlaps the fwrite of chunk k
+    size_t issued = 0, written = 0;
+    int k = 0;
+    auto issue = [&](int b) {
+        const size_t len = std::min(kIoChunk, total - issued);
+        cudaMemcpyAsync(io.p[b], src + issued, len, cudaMemcpyDeviceToHost, io.st);
+        cudaEventRecord(io.ev[b], io.st);
+        issued += len;
+    };
+    if (total > 0) issue(0);
+    while (ok && written < total) {
+        const int b = k & 1;
+        if (issued < total) issue(b ^ 1);
+        if (cudaEventSynchronize(io.ev[b]) != cudaSuccess) { ok = false; break; }
+        const size_t len = std::min(kIoChunk, total - written);
+        ok = std::fwrite(io.p[b], 1, len, f) == len;
+        written += len;
+        ++k;
+    }
+    cudaStreamSynchronize(io.st);
+    ok = (std::fclose(f) == 0) && ok;
+    if (cudaGetLastError() != cudaSuccess) ok = false;
+    if (!ok) {
+        std::remove(path);
+        return sv_fail(SV_ERR_IO, std::string("sv_spec_save: write failed: ") + path);
+    }
+    return SV_OK;
+}
+
+extern "C" int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out) {
+    if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_load: out is NULL");
+    *out = nullptr;
+    if (m == nullptr || path == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_load: NULL");
+    FILE* f = std::fopen(path, "rb");
+    if (f == nullptr) return sv_fail(SV_ERR_IO, std::string("sv_spec_load: cannot open ") + path);
+    TableHeader h{};
+    auto fail = [&](int code, const std::string& msg) {
+        std::fclose(f);
+        return sv_fail(code, "sv_spec_load: " + msg + ": " + path);
+    };
+    if (std::fread(&h, sizeof(h), 1, f) != 1 || std::memcmp(h.magic, kTableMagic, 8) != 0)
+        return fail(SV_ERR_IO, "not a handler-table file");
+    if (h.states != m->n || h.emits != m->emits || h.fingerprint != model_fingerprint(m))
+        return fail(SV_ERR_ARG, "table was built from a different model");
+    const uint64_t ntuples = h.level >= 2 ? ipow(m->emits, h.level) : ~0ull;
+    if (ntuples == ~0ull || h.t_begin > h.t_end || h.t_end > ntuples) return fail(SV_ERR_IO, "corrupt header");
+    const size_t mat = static_cast<size_t>(m->n) * m->n * sizeof(float);
+    const size_t total = (h.t_end - h.t_begin) * mat;
+    if (cudaSetDevice(m->device) != cudaSuccess) return fail(SV_ERR_CUDA, "cudaSetDevice");
+    PinnedPair io;
+    if (!io.init()) {
+        cudaGetLastError();
+        return fail(SV_ERR_MEMORY, "no pinned staging memory");
+    }
+    sv_spec* s = new (std::nothrow) sv_spec;
+    if (s == nullptr) return fail(SV_ERR_MEMORY, "out of host memory");
+    s->m = m;
+    s->level = h.level;
+    s->ntuples = ntuples;
+    s->method = SV_SPEC_SPARSE_LHS;
+    s->table_first = s->t_begin = h.t_begin;
+    s->t_end = h.t_end;
+    if (d_table != nullptr) {
+        s->d_table = d_table;
+    } else if (total > 0) {
+        if (cudaMalloc(&s->d_table, total) != cudaSuccess) {
+            cudaGetLastError();
+            delete s;
+            return fail(SV_ERR_MEMORY, "handler table does not fit device memory");
+        }
+        s->owns_table = true;
+    }
+    // fread of chunk k+1 overlaps the H2D of chunk k
+    char* dst = reinterpret_cast<char*>(s->d_table);
+    size_t done = 0;
+    bool ok = true;
+    for (int k = 0; ok && done < total; ++k) {
+        const int b = k & 1;
+        if (k >= 2 && cudaEventSynchronize(io.ev[b]) != cudaSuccess) { ok = false; break; }
+        const size_t len = std::min(kIoChunk, total - done);
+        if (std::fread(io.p[b], 1, len, f) != len) { ok = false; break; }
+        cudaMemcpyAsync(dst + done, io.p[b], len, cudaMemcpyHostToDevice, io.st);
+        cudaEventRecord(io.ev[b], io.st);
+        done += len;
+    }
+    if (cudaStreamSynchronize(io.st) != cudaSuccess || cudaGetLastError() != cudaSuccess) ok = false;
+    if (!ok) {
+        sv_spec_destroy(s);
+        return fail(SV_ERR_IO, "short or unreadable file");
+    }
+    std::fclose(f);
+    *out = s;
     return SV_OK;
 }
 

@@ -158,6 +158,24 @@ class B200_spec_impl : public Viterbi_spec_impl {
         return res;
     }
 
+    // Not in the reference (it recomputes in every spec_with): keep the handler tables of level >= 2
+    // across processes.  spec_with_saved attaches a table written by save_tables; it throws if the file
+    // was built from a different model.
+    void save_tables(const std::string& path) const {
+        if (spec == nullptr) throw std::runtime_error("B200_spec_impl: spec_with(hmm) must be called first");
+        b200_detail::check(sv_spec_save(spec, path.c_str()), "sv_spec_save");
+    }
+    void spec_with_saved(const HMM& hmm, const std::string& path) {
+        drop();
+        model = b200_detail::make_model(hmm, device);
+        states = hmm.states_num;
+        b200_detail::check(sv_spec_load(model, path.c_str(), nullptr, &spec), "sv_spec_load");
+        if (sv_spec_level(spec) != level) {
+            drop();
+            throw std::runtime_error("B200_spec_impl: saved tables are of another level");
+        }
+    }
+
     [[nodiscard]] std::vector<HMM::Mod_prob_vec_t> run_Viterbi_spec_batch(const HMM::Emit_seq_vec_t& seqs) const {
         if (spec == nullptr) throw std::runtime_error("B200_spec_impl: spec_with(hmm) must be called first");
         std::vector<std::uint64_t> symbols, offsets;

@@ -89,6 +89,28 @@ def test_random_models(n, seed, kernel, api, oracle):
         assert (best[k] == bv or (np.isposinf(bv) and np.isposinf(best[k]))) and arg[k] == bi
 
 
+@pytest.mark.parametrize("n,seed", [(150, 7), (2405, 2405)])
+def test_two_halves_lockstep_variant(n, seed, api, oracle, monkeypatch):
+    """Opt-in variant of K2 (sv_plain_ls2.cu): two independent 256-thread halves per CTA, 10 rows per
+    thread; same bits as the oracle, including the refill path (more sequences than slots)."""
+    from spec_viterbi_b200 import generators, _lib
+    monkeypatch.setenv("SV_LS_HALVES", "2")
+    hmm = generators.random_hmm(states_num=n, trans_per_state=3, num_non_zero_start_probs=2, seed=seed)
+    rng = np.random.default_rng(seed)
+    lens = [1, 2, 3, 17, 64, 200, 5, 1, 129] + [int(x) for x in rng.integers(1, 120, 1400)]
+    seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in lens]
+    m = _model(api, hmm, "ls")
+    info = m.info()
+    assert info.ls_threads == 256 and info.ls_smem_bytes == 164352  # 2 halves x 2 buffers x 2568 x 16 B
+    syms, offs = api.pack_sequences(seqs)
+    out, best, arg = m.viterbi_batch(syms, offs)
+    exp = oracle.plain_batch(hmm, syms, offs, threads=8)
+    assert same_bits(out, exp)
+    for k in range(0, len(seqs), 37):
+        bv, bi = best_state(exp[k])
+        assert (best[k] == bv or (np.isposinf(bv) and np.isposinf(best[k]))) and arg[k] == bi
+
+
 def test_high_in_degree_and_duplicates(api, oracle):
     """Dense destination rows, duplicate COO entries (FIRST wins) and duplicate start entries."""
     rng = np.random.default_rng(5)

@@ -109,3 +109,40 @@ def test_spec_vs_plain_cross_path(api, load_model, load_seqs):
     assert np.all(np.abs(plain - spec) <= 1.0)
     assert np.max(np.abs(plain - spec) / plain) < 5e-5
     assert np.array_equal(plain.argmin(1), spec.argmin(1))
+
+
+def test_handler_table_save_load(api, oracle, tmp_path):
+    """a saved level-2 table attaches to the same model without recomputation and
+    gives the same bits; it is refused for a different model; tuple shards round-trip too."""
+    from spec_viterbi_b200 import generators, _lib
+    hmm = generators.random_hmm(states_num=150, trans_per_state=3, num_non_zero_start_probs=2, seed=9)
+    seqs = [np.random.default_rng(k).integers(0, 20, L).astype(np.uint64) for k, L in enumerate((1, 2, 7, 64, 201))]
+    syms, offs = api.pack_sequences(seqs)
+    m = api.Model(hmm)
+    built = api.Spec(m, 2)
+    exp, _, _ = built.run_batch(syms, offs)
+    osp = oracle.spec(hmm, 2)
+    assert same_bits(exp[4], osp.run(seqs[4]))
+    path = tmp_path / "level2.svht"
+    built.save(path)
+    assert path.stat().st_size == 64 + 400 * 150 * 150 * 4
+    loaded = api.Spec.load(m, path)
+    assert loaded.level == 2 and loaded.table()[1:] == (0, 400)
+    assert same_bits(loaded.handler(123), built.handler(123))
+    got, _, _ = loaded.run_batch(syms, offs)
+    assert same_bits(got, exp)
+    # a shard of the tuple range
+    shard = api.Spec(m, 2, tuple_begin=100, tuple_end=160)
+    shard.save(tmp_path / "shard.svht")
+    back = api.Spec.load(m, tmp_path / "shard.svht")
+    assert back.table()[1:] == (100, 160) and same_bits(back.handler(159), built.handler(159))
+    # another model (one weight differs) must not accept the table
+    other = generators.random_hmm(states_num=150, trans_per_state=3, num_non_zero_start_probs=2, seed=10)
+    with pytest.raises(_lib.SvError):
+        api.Spec.load(api.Model(other), path)
+    # not a table file / level 1 has nothing to save
+    (tmp_path / "junk").write_bytes(b"x" * 100)
+    with pytest.raises(_lib.SvError):
+        api.Spec.load(m, tmp_path / "junk")
+    with pytest.raises(_lib.SvError):
+        api.Spec(m, 1).save(tmp_path / "l1")
