@@ -130,6 +130,8 @@ struct SvPairDev {
 };
 
 constexpr int kPairChunk = 16; // consecutive tuples per CTA: the row's structure is set up once
+constexpr int kPairFast = 64;  // pairs per row whose per-tuple values are tabulated in shared memory
+constexpr int kPairBitWords = 1024; // column bitmap of the fast path: up to 32 * 1024 - 64 states
 
 __global__ void __launch_bounds__(256)
 pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uint64_t tuple_count, int heavy_pass) {
@@ -227,6 +229,103 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
         }
     }
     __syncthreads();
+    // ---- fast path (few pairs, at most two dense terms): everything a tuple needs from global memory --
+    //      E_b[i], E_a[j_q] -- is tabulated for the whole chunk up front, so that the tuple loop is a pure
+    //      store stream with no dependent load at the head of every tuple (that latency, paid kPairChunk
+    //      times per CTA and again inside every patch, held the first version at a third of the HBM
+    //      write rate).  Patches are merged into the streamed stores through a column bitmap. ----
+    if (npairs <= kPairFast && nhv <= 2 && n <= 32 * kPairBitWords - 64) {
+        __shared__ float s_val[kPairChunk][kPairFast]; // per tuple: min over the pairs of the u-th patched column
+        __shared__ float s_hu[kPairChunk][2], s_hea[kPairChunk][2];
+        __shared__ uint32_t s_bits[kPairBitWords];     // columns that receive a patch
+        __shared__ uint8_t s_pref[kPairBitWords];      // patched columns below 32 * w
+        __shared__ uint8_t s_first[kPairFast], s_u[kPairFast];
+        const int nwords = (n >> 5) + 2;
+        for (int w = tid; w < nwords; w += 256) s_bits[w] = 0u;
+        if (tid < npairs) { // first occurrence of its column?
+            bool first = true;
+            for (int t2 = 0; t2 < tid; ++t2) first = first && s_pk[t2] != s_pk[tid];
+            s_first[tid] = first;
+        }
+        __syncthreads();
+        if (tid < npairs) {
+            atomicOr(&s_bits[s_pk[tid] >> 5], 1u << (s_pk[tid] & 31u));
+            int u = 0; // rank of this pair's column among the patched columns
+            for (int t2 = 0; t2 < npairs; ++t2) u += (s_first[t2] && s_pk[t2] < s_pk[tid]) ? 1 : 0;
+            s_u[tid] = static_cast<uint8_t>(u);
+        }
+        for (int w = tid; w < nwords; w += 256) {
+            int c = 0;
+            for (int t2 = 0; t2 < npairs; ++t2) c += (s_first[t2] && s_pk[t2] < 32u * w) ? 1 : 0;
+            s_pref[w] = static_cast<uint8_t>(c);
+        }
+        __syncthreads();
+        for (int idx = tid; idx < ntup * npairs; idx += 256) {
+            const int s = idx / npairs, t = idx - s * npairs;
+            if (!s_first[t]) continue;
+            const uint64_t tuple = tuple_first + rel0 + s;
+            const size_t b = tuple % d.emits, a = tuple / d.emits;
+            const float eb = d.emis[b * n + i];
+            float v = pos_inf();
+            for (int t2 = t; t2 < npairs; ++t2)
+                if (s_pk[t2] == s_pk[t]) {
+                    const int q = s_pq[t2];
+                    v = fminf(v, (eb + s_w[q]) + (d.emis[a * n + s_j[q]] + s_pw[t2]));
+                }
+            s_val[s][s_u[t]] = v;
+        }
+        if (tid < 2 * ntup && (tid & 1) < nhv) {
+            const int s = tid >> 1, x = tid & 1, q = s_hq[x];
+            const uint64_t tuple = tuple_first + rel0 + s;
+            const size_t b = tuple % d.emits, a = tuple / d.emits;
+            s_hu[s][x] = d.emis[b * n + i] + s_w[q];
+            s_hea[s][x] = d.emis[a * n + s_j[q]];
+        }
+        __syncthreads();
+        const float* __restrict__ hp0 = nhv > 0 ? d.wd + static_cast<size_t>(s_h[s_hq[0]]) * n : d.wd;
+        const float* __restrict__ hp1 = nhv > 1 ? d.wd + static_cast<size_t>(s_h[s_hq[1]]) * n : d.wd;
+        for (int s = 0; s < ntup; ++s) {
+            float* __restrict__ O = out + (rel0 + s) * static_cast<size_t>(n) * n + static_cast<size_t>(i) * n;
+            const float hu0 = s_hu[s][0], hea0 = s_hea[s][0], hu1 = s_hu[s][1], hea1 = s_hea[s][1];
+            const float* __restrict__ val = s_val[s];
+            const int kb = min(n, static_cast<int>((32u - ((reinterpret_cast<uintptr_t>(O) >> 2) & 31u)) & 31u));
+            const int nb = (n - kb) / 4;
+            auto rank_of = [&](int k) { return s_pref[k >> 5] + __popc(s_bits[k >> 5] & ((1u << (k & 31)) - 1u)); };
+            auto fix1 = [&](int k, float v) {
+                if ((s_bits[k >> 5] >> (k & 31)) & 1u) v = fminf(v, val[rank_of(k)]);
+                return v;
+            };
+            auto stream = [&](auto f) {
+                if (tid < kb) O[tid] = fix1(tid, f(tid));
+                // column k = kb + 4 * (tid + 256 * it): the bit offset inside a bitmap word is the same in
+                // every iteration, the word index advances by 32
+                const int k0 = kb + 4 * tid, sh = k0 & 31;
+                const uint32_t* __restrict__ bw = s_bits + (k0 >> 5);
+                float4* __restrict__ dst = reinterpret_cast<float4*>(O + k0);
+                int k = k0;
+                for (int g = tid; g < nb; g += 256, k += 1024, bw += 32, dst += 256) {
+                    float v[4] = {f(k), f(k + 1), f(k + 2), f(k + 3)};
+                    const uint32_t bits = __funnelshift_r(bw[0], bw[1], sh) & 15u;
+                    if (bits) { // the patched columns of a row are ranked left to right
+                        int u = rank_of(k);
+                        if (bits & 1u) v[0] = fminf(v[0], val[u++]);
+                        if (bits & 2u) v[1] = fminf(v[1], val[u++]);
+                        if (bits & 4u) v[2] = fminf(v[2], val[u++]);
+                        if (bits & 8u) v[3] = fminf(v[3], val[u]);
+                    }
+                    *dst = make_float4(v[0], v[1], v[2], v[3]);
+                }
+                for (int kk = kb + 4 * nb + tid; kk < n; kk += 256) O[kk] = fix1(kk, f(kk));
+            };
+            if (nhv == 0)
+                stream([&](int) { return pos_inf(); });
+            else if (nhv == 1)
+                stream([&](int k) { return hu0 + (hea0 + hp0[k]); });
+            else
+                stream([&](int k) { return fminf(hu0 + (hea0 + hp0[k]), hu1 + (hea1 + hp1[k])); });
+        }
+        return;
+    }
     for (int s = 0; s < ntup; ++s) {
         const uint64_t tuple = tuple_first + rel0 + s;
         const int b = static_cast<int>(tuple % d.emits), a = static_cast<int>(tuple / d.emits);
