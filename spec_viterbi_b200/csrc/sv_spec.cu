@@ -17,6 +17,7 @@
 #include <limits>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 struct sv_spec {
@@ -127,9 +128,13 @@ struct SvPairDev {
     const uint32_t* longcol = nullptr; // columns with more than kPairLongCol entries
     const uint32_t* hrow = nullptr;    // [heavy] row of each dense copy
     int n_heavy = 0;
+    int stage_row = 0; // light pass: (n + 8) floats of dynamic shared memory hold the row's first dense source
 };
 
-constexpr int kPairChunk = 16; // consecutive tuples per CTA: the row's structure is set up once
+#ifndef SV_PAIR_CHUNK
+#define SV_PAIR_CHUNK 40
+#endif
+constexpr int kPairChunk = SV_PAIR_CHUNK; // consecutive tuples per CTA: the row's structure is set up once
 constexpr int kPairFast = 64;  // pairs per row whose per-tuple values are tabulated in shared memory
 constexpr int kPairBitWords = 1024; // column bitmap of the fast path: up to 32 * 1024 - 64 states
 
@@ -281,9 +286,17 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
             s_hu[s][x] = d.emis[b * n + i] + s_w[q];
             s_hea[s][x] = d.emis[a * n + s_j[q]];
         }
-        __syncthreads();
         const float* __restrict__ hp0 = nhv > 0 ? d.wd + static_cast<size_t>(s_h[s_hq[0]]) * n : d.wd;
         const float* __restrict__ hp1 = nhv > 1 ? d.wd + static_cast<size_t>(s_h[s_hq[1]]) * n : d.wd;
+        // one dense source (every light row of a profile HMM): its dense copy is staged in shared memory
+        // once per chunk, so that the stream reads it with two aligned LDS.128 per 16-byte store instead
+        // of four scalar global loads with 64-bit addresses (the stream is issue-bound)
+        extern __shared__ __align__(16) unsigned char s_dyn[];
+        float* s_row = reinterpret_cast<float*>(s_dyn);
+        const bool staged = d.stage_row != 0 && nhv == 1;
+        if (staged)
+            for (int x = tid; x < n + 8; x += 256) s_row[x] = x < n ? hp0[x] : pos_inf();
+        __syncthreads();
         for (int s = 0; s < ntup; ++s) {
             float* __restrict__ O = out + (rel0 + s) * static_cast<size_t>(n) * n + static_cast<size_t>(i) * n;
             const float hu0 = s_hu[s][0], hea0 = s_hea[s][0], hu1 = s_hu[s][1], hea1 = s_hea[s][1];
@@ -317,9 +330,53 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
                 }
                 for (int kk = kb + 4 * nb + tid; kk < n; kk += 256) O[kk] = fix1(kk, f(kk));
             };
+            // same, the dense term read from the staged row: columns k..k+3 straddle two aligned float4;
+            // the shift r = k & 3 is the same for every group of the tuple (compile-time in the body)
+            auto stream_staged = [&](auto rc) {
+                constexpr int r = decltype(rc)::value;
+                auto f = [&](int k) { return hu0 + (hea0 + s_row[k]); };
+                if (tid < kb) O[tid] = fix1(tid, f(tid));
+                const int k0 = kb + 4 * tid, sh = k0 & 31;
+                const uint32_t* __restrict__ bw = s_bits + (k0 >> 5);
+                const float4* __restrict__ rp = reinterpret_cast<const float4*>(s_row) + (k0 >> 2);
+                float4* __restrict__ dst = reinterpret_cast<float4*>(O + k0);
+                int k = k0;
+                for (int g = tid; g < nb; g += 256, k += 1024, bw += 32, dst += 256, rp += 256) {
+                    const float4 a = rp[0];
+                    float x[4];
+                    if constexpr (r == 0) {
+                        x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+                    } else {
+                        const float4 b = rp[1];
+                        if constexpr (r == 1) { x[0] = a.y; x[1] = a.z; x[2] = a.w; x[3] = b.x; }
+                        if constexpr (r == 2) { x[0] = a.z; x[1] = a.w; x[2] = b.x; x[3] = b.y; }
+                        if constexpr (r == 3) { x[0] = a.w; x[1] = b.x; x[2] = b.y; x[3] = b.z; }
+                    }
+                    float v[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) v[c] = hu0 + (hea0 + x[c]);
+                    const uint32_t bits = __funnelshift_r(bw[0], bw[1], sh) & 15u;
+                    if (bits) {
+                        int u = rank_of(k);
+                        if (bits & 1u) v[0] = fminf(v[0], val[u++]);
+                        if (bits & 2u) v[1] = fminf(v[1], val[u++]);
+                        if (bits & 4u) v[2] = fminf(v[2], val[u++]);
+                        if (bits & 8u) v[3] = fminf(v[3], val[u]);
+                    }
+                    *dst = make_float4(v[0], v[1], v[2], v[3]);
+                }
+                for (int kk = kb + 4 * nb + tid; kk < n; kk += 256) O[kk] = fix1(kk, f(kk));
+            };
             if (nhv == 0)
                 stream([&](int) { return pos_inf(); });
-            else if (nhv == 1)
+            else if (staged) {
+                switch (kb & 3) {
+                case 0: stream_staged(std::integral_constant<int, 0>{}); break;
+                case 1: stream_staged(std::integral_constant<int, 1>{}); break;
+                case 2: stream_staged(std::integral_constant<int, 2>{}); break;
+                default: stream_staged(std::integral_constant<int, 3>{}); break;
+                }
+            } else if (nhv == 1)
                 stream([&](int k) { return hu0 + (hea0 + hp0[k]); });
             else
                 stream([&](int k) { return fminf(hu0 + (hea0 + hp0[k]), hu1 + (hea1 + hp1[k])); });
@@ -778,7 +835,10 @@ int build_pair_level2(sv_model* m, const SvPairDev& pd, uint64_t tb, uint64_t te
             dim3 hgrid(static_cast<unsigned>(pd.n_heavy), static_cast<unsigned>(cnt));
             pair_rows_kernel<<<hgrid, 256, 0, st>>>(pd, dst + (t0 - tb) * n * n, t0, cnt, 1);
         }
-        pair_rows_kernel<<<grid, 256, 0, st>>>(pd, dst + (t0 - tb) * n * n, t0, cnt, 0);
+        SvPairDev pl = pd; // light pass: stage the dense source of a row when it fits beside 4 resident CTAs
+        const size_t stage_bytes = (n + 8) * sizeof(float);
+        pl.stage_row = pd.n_heavy > 0 && stage_bytes <= 28 * 1024;
+        pair_rows_kernel<<<grid, 256, pl.stage_row ? stage_bytes : 0, st>>>(pl, dst + (t0 - tb) * n * n, t0, cnt, 0);
         if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "pair_rows launch failed");
     }
     cudaError_t e = cudaStreamSynchronize(st);
