@@ -297,12 +297,15 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
         if (staged)
             for (int x = tid; x < n + 8; x += 256) s_row[x] = x < n ? hp0[x] : pos_inf();
         __syncthreads();
-        for (int s = 0; s < ntup; ++s) {
-            float* __restrict__ O = out + (rel0 + s) * static_cast<size_t>(n) * n + static_cast<size_t>(i) * n;
+        // (the per-tuple preamble is kept short -- the row pointer advances by n * n, nothing is re-derived
+        //  from the tuple index: at ~20 instructions per 512-byte store the preamble was 40 % of all issue slots)
+        float* __restrict__ O = out + rel0 * static_cast<size_t>(n) * n + static_cast<size_t>(i) * n;
+        const size_t nn = static_cast<size_t>(n) * n;
+        for (int s = 0; s < ntup; ++s, O += nn) {
             const float hu0 = s_hu[s][0], hea0 = s_hea[s][0], hu1 = s_hu[s][1], hea1 = s_hea[s][1];
             const float* __restrict__ val = s_val[s];
-            const int kb = min(n, static_cast<int>((32u - ((reinterpret_cast<uintptr_t>(O) >> 2) & 31u)) & 31u));
-            const int nb = (n - kb) / 4;
+            const int kb = min(n, static_cast<int>((32u - (static_cast<uint32_t>(reinterpret_cast<uintptr_t>(O) >> 2) & 31u)) & 31u));
+            const int nb = static_cast<int>(static_cast<uint32_t>(n - kb) >> 2);
             auto rank_of = [&](int k) { return s_pref[k >> 5] + __popc(s_bits[k >> 5] & ((1u << (k & 31)) - 1u)); };
             auto fix1 = [&](int k, float v) {
                 if ((s_bits[k >> 5] >> (k & 31)) & 1u) v = fminf(v, val[rank_of(k)]);
@@ -314,9 +317,10 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
                 // every iteration, the word index advances by 32
                 const int k0 = kb + 4 * tid, sh = k0 & 31;
                 const uint32_t* __restrict__ bw = s_bits + (k0 >> 5);
+                const uint32_t* const bw_end = s_bits + ((kb + 4 * nb) >> 5) + ((((kb + 4 * nb) & 31) > sh) ? 1 : 0);
                 float4* __restrict__ dst = reinterpret_cast<float4*>(O + k0);
-                int k = k0;
-                for (int g = tid; g < nb; g += 256, k += 1024, bw += 32, dst += 256) {
+                for (; bw < bw_end; bw += 32, dst += 256) { // the word pointer is the only loop counter
+                    const int k = (static_cast<int>(bw - s_bits) << 5) + sh;
                     float v[4] = {f(k), f(k + 1), f(k + 2), f(k + 3)};
                     const uint32_t bits = __funnelshift_r(bw[0], bw[1], sh) & 15u;
                     if (bits) { // the patched columns of a row are ranked left to right
@@ -338,10 +342,11 @@ pair_rows_kernel(SvPairDev d, float* __restrict__ out, uint64_t tuple_first, uin
                 if (tid < kb) O[tid] = fix1(tid, f(tid));
                 const int k0 = kb + 4 * tid, sh = k0 & 31;
                 const uint32_t* __restrict__ bw = s_bits + (k0 >> 5);
+                const uint32_t* const bw_end = s_bits + ((kb + 4 * nb) >> 5) + ((((kb + 4 * nb) & 31) > sh) ? 1 : 0);
                 const float4* __restrict__ rp = reinterpret_cast<const float4*>(s_row) + (k0 >> 2);
                 float4* __restrict__ dst = reinterpret_cast<float4*>(O + k0);
-                int k = k0;
-                for (int g = tid; g < nb; g += 256, k += 1024, bw += 32, dst += 256, rp += 256) {
+                for (; bw < bw_end; bw += 32, dst += 256, rp += 256) {
+                    const int k = (static_cast<int>(bw - s_bits) << 5) + sh;
                     const float4 a = rp[0];
                     float x[4];
                     if constexpr (r == 0) {
