@@ -105,8 +105,11 @@ sparse_lhs_kernel(SvGenericDev m, const float* __restrict__ prev, uint64_t prev_
 // needs no dense operand at all: the kernel is a pure streaming WRITE of the dense table
 // (E^2 * N^2 * 4 bytes) with a handful of terms per row.  Rows of T' with more than kPairHeavy
 // entries ("heavy": the dense rows of profile HMMs) are kept as dense vectors Wd[h][.]:
-//   * light row i: dense terms (heavy j) are evaluated per column, the few (k, value) pairs that
-//     the light j contribute are patched in after a CTA barrier;
+//   * light row i: dense terms (heavy j) are evaluated per column; the few (k, value) pairs that the
+//     light j contribute are merged into the streamed 16-byte stores through a column bitmap with
+//     prefix popcounts (fast path: <= 64 pairs, <= 2 dense terms; the tuple-dependent scalars of a whole
+//     chunk of tuples are tabulated in shared memory first, so the stream has no dependent load), or
+//     patched in after a CTA barrier (general path);
 //   * heavy row i: column k walks its CSC list {j : k in in(j)} and looks T'[i][j] up in Wd.
 // Same association as K3' => same bits.  grid: x = row i, y = tuple (relative); 256 threads.
 constexpr int kPairHeavy = 32;    // rows with more in-edges are "heavy"
