@@ -112,6 +112,10 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     return v;
 }
 
+#ifndef SV_LS_DEPTH
+#define SV_LS_DEPTH 1 // slot pairs in flight beside the one being relaxed
+#endif
+
 // Gathered scores of one slot pair (4 sequences).
 struct LsPair {
     float4 a, b;
@@ -143,12 +147,22 @@ __device__ __forceinline__ void ls_fixed(const float (&ew)[NSLOTS], const EO& eo
         constexpr int NP = (D + 1) / 2;
         LsPair buf[NP + 1];
         buf[0] = io;
+        // future pairs F = [pair 1, .., pair NP-1, first pair of the next slice]; before pair p is relaxed
+        // F[0 .. p + DEPTH - 1] have been issued (DEPTH = SV_LS_DEPTH pairs in flight beside the one in use)
+        auto issue = [&](int f) { // f = index into F, compile-time after unrolling
+            if (f + 1 < NP)
+                ls_gather<GOFF>(eo, pofs, buf[f + 1], BASE + 2 * f + 2, 2 * f + 3 < D);
+            else if (f + 1 == NP && NBASE >= 0)
+                ls_gather<NGOFF>(eo, npofs, buf[f + 1], NBASE, NBOTH);
+        };
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
-            if (p + 1 < NP)
-                ls_gather<GOFF>(eo, pofs, buf[p + 1], BASE + 2 * p + 2, 2 * p + 3 < D);
-            else if (NBASE >= 0)
-                ls_gather<NGOFF>(eo, npofs, buf[p + 1], NBASE, NBOTH);
+            if (p == 0) {
+#pragma unroll
+                for (int f = 0; f < SV_LS_DEPTH; ++f) issue(f);
+            } else {
+                issue(p + SV_LS_DEPTH - 1);
+            }
             const int k = BASE + 2 * p;
             if (2 * p + 1 < D) {
                 if (p == 0)
