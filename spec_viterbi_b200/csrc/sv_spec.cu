@@ -32,6 +32,11 @@ struct sv_spec {
     // run-phase scratch
     float* d_v[2] = {nullptr, nullptr};
     uint64_t v_capacity = 0;
+    // K4 runs groups of sequences on side streams so that the partial last wave of one group's
+    // launch is filled by the next group's (sequences are independent)
+    static constexpr int kRunStreams = 4;
+    cudaStream_t aux[kRunStreams - 1] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[kRunStreams - 1] = {nullptr, nullptr, nullptr};
 };
 
 namespace {
@@ -595,9 +600,9 @@ __global__ void spec_init_kernel(SvGenericDev m, RunSeqs s, float* __restrict__ 
 __global__ void __launch_bounds__(256)
 handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
                     const float* __restrict__ table, uint64_t table_first,
-                    const float* __restrict__ vin, float* __restrict__ vout, int rows_per_cta) {
+                    const float* __restrict__ vin, float* __restrict__ vout, int rows_per_cta, int seq_base) {
     extern __shared__ float sv[];
-    const int q = blockIdx.y;
+    const int q = seq_base + blockIdx.y;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
     const uint64_t nchunks = (len - 1) / level;
@@ -952,6 +957,11 @@ extern "C" void sv_spec_destroy(sv_spec* s) {
     if (s == nullptr) return;
     cudaSetDevice(s->m->device);
     if (s->owns_table && s->d_table) cudaFree(s->d_table);
+    for (int g = 0; g < sv_spec::kRunStreams - 1; ++g) {
+        if (s->aux[g]) cudaStreamDestroy(s->aux[g]);
+        if (s->ev_join[g]) cudaEventDestroy(s->ev_join[g]);
+    }
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->d_v[0]) cudaFree(s->d_v[0]);
     if (s->d_v[1]) cudaFree(s->d_v[1]);
     delete s;
@@ -1196,14 +1206,35 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         const uint64_t slots = static_cast<uint64_t>(std::max(1, m->sm_count)) * 8ull;
         while (rows_per_cta > 8 && ((n + rows_per_cta - 1) / rows_per_cta) * nseq < 6ull * slots) rows_per_cta /= 2;
     }
+    // sequence groups on up to kRunStreams streams (group 0 stays on the caller's stream)
+    const int ngroups = static_cast<int>(std::min<uint64_t>(sv_spec::kRunStreams, nseq));
+    if (ngroups > 1 && s->ev_fork == nullptr) {
+        SV_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+        for (int g = 0; g < sv_spec::kRunStreams - 1; ++g) {
+            SV_CUDA(cudaStreamCreateWithFlags(&s->aux[g], cudaStreamNonBlocking));
+            SV_CUDA(cudaEventCreateWithFlags(&s->ev_join[g], cudaEventDisableTiming));
+        }
+    }
+    if (ngroups > 1 && max_chunks > 0) {
+        SV_CUDA(cudaEventRecord(s->ev_fork, st));
+        for (int g = 1; g < ngroups; ++g) SV_CUDA(cudaStreamWaitEvent(s->aux[g - 1], s->ev_fork, 0));
+    }
     for (uint64_t c = 0; c < max_chunks; ++c) {
-        dim3 grid(static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta),
-                  static_cast<unsigned>(nseq));
-        handler_gemv_kernel<<<grid, 256, n * sizeof(float), st>>>(
-            static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c,
-            s->d_table, s->table_first, s->d_v[cur], s->d_v[cur ^ 1], rows_per_cta);
+        for (int g = 0; g < ngroups; ++g) {
+            const uint64_t q0 = nseq * g / ngroups, q1 = nseq * (g + 1) / ngroups;
+            dim3 grid(static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta), static_cast<unsigned>(q1 - q0));
+            handler_gemv_kernel<<<grid, 256, n * sizeof(float), g == 0 ? st : s->aux[g - 1]>>>(
+                static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c,
+                s->d_table, s->table_first, s->d_v[cur], s->d_v[cur ^ 1], rows_per_cta, static_cast<int>(q0));
+            ++launches;
+        }
         cur ^= 1;
-        ++launches;
+    }
+    if (ngroups > 1 && max_chunks > 0) {
+        for (int g = 1; g < ngroups; ++g) {
+            SV_CUDA(cudaEventRecord(s->ev_join[g - 1], s->aux[g - 1]));
+            SV_CUDA(cudaStreamWaitEvent(st, s->ev_join[g - 1], 0));
+        }
     }
     for (uint64_t tl = 0; tl + 1 < s->level; ++tl) {
         tail_step_kernel<<<static_cast<unsigned>(nseq), 1024, n * sizeof(float), st>>>(
