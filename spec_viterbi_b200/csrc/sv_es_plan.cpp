@@ -164,7 +164,7 @@ bool try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
 
     // ---- shared memory budget ----
     const size_t vb = (n_int * Q * 4 + 15) & ~size_t(15);
-    const size_t smem = 2 * vb + static_cast<size_t>(var.nh) * NW * Q * 4 + emits * n_int * 4;
+    const size_t smem = 2 * vb + 2 * static_cast<size_t>(var.nh) * NW * Q * 4 + emits * n_int * 4; // red is double buffered
     if (smem + 512 > smem_limit) return false; // headroom for the kernel's static shared variables
 
     // ---- placement: sorted light rows -> chunks of 32 -> (rank, warp) cells, snake order ----

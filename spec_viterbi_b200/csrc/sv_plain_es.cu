@@ -86,27 +86,35 @@ __device__ __forceinline__ void relax(float w, uint32_t off, const unsigned char
     }
 }
 
-// Runs slots [0, d) of a register slice of SMAX slots starting at BASE (d <= SMAX,
-// warp-uniform).  Fall-through switch: every register index is a compile-time constant.
+// Runs slots [0, d) of a register slice of SMAX slots starting at BASE (d <= SMAX, warp-uniform):
+// a binary tree of uniform branches into straight-line code for exactly d slots (every register
+// index is a compile-time constant; a switch costs a constant-bank load and an indirect branch
+// per slice, and this kernel is latency-bound).
+template <int Q, int BASE, int D, int NSLOTS>
+__device__ __forceinline__ void run_fixed(const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS],
+                                          const unsigned char* vcur, const float (&e)[Q], float (&acc)[Q]) {
+#pragma unroll
+    for (int k = 0; k < D; ++k) relax<Q>(ew[BASE + k], eo[BASE + k], vcur, e, acc);
+}
+template <int Q, int BASE, int LO, int HI, int NSLOTS>
+__device__ __forceinline__ void run_tree(int d, const float (&ew)[NSLOTS], const uint32_t (&eo)[NSLOTS],
+                                         const unsigned char* vcur, const float (&e)[Q], float (&acc)[Q]) {
+    if constexpr (LO == HI) {
+        run_fixed<Q, BASE, LO, NSLOTS>(ew, eo, vcur, e, acc);
+    } else {
+        constexpr int MID = (LO + HI) / 2;
+        if (d <= MID)
+            run_tree<Q, BASE, LO, MID, NSLOTS>(d, ew, eo, vcur, e, acc);
+        else
+            run_tree<Q, BASE, MID + 1, HI, NSLOTS>(d, ew, eo, vcur, e, acc);
+    }
+}
 template <int Q, int BASE, int SMAX, int NSLOTS>
 __device__ __forceinline__ void run_slots(int d, const float (&ew)[NSLOTS],
                                           const uint32_t (&eo)[NSLOTS],
                                           const unsigned char* vcur, const float (&e)[Q],
                                           float (&acc)[Q]) {
-#define SV_SLOT(K)                                                                 \
-    if constexpr ((K) < SMAX) relax<Q>(ew[BASE + (K)], eo[BASE + (K)], vcur, e, acc);
-    switch (d) {
-    case 8: SV_SLOT(7) [[fallthrough]];
-    case 7: SV_SLOT(6) [[fallthrough]];
-    case 6: SV_SLOT(5) [[fallthrough]];
-    case 5: SV_SLOT(4) [[fallthrough]];
-    case 4: SV_SLOT(3) [[fallthrough]];
-    case 3: SV_SLOT(2) [[fallthrough]];
-    case 2: SV_SLOT(1) [[fallthrough]];
-    case 1: SV_SLOT(0) [[fallthrough]];
-    default: break;
-    }
-#undef SV_SLOT
+    run_tree<Q, BASE, 0, SMAX, NSLOTS>(d, ew, eo, vcur, e, acc);
 }
 
 template <int TPG, int Q, typename SH, int NH, int HS, typename SymT>
@@ -124,13 +132,14 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
     const uint32_t vbytes = static_cast<uint32_t>(n_int) * Q * 4u; // one v buffer
     unsigned char* vbuf0 = smem_raw;
     unsigned char* vbuf1 = smem_raw + ((vbytes + 15u) & ~15u);
-    float* red = reinterpret_cast<float*>(vbuf1 + ((vbytes + 15u) & ~15u)); // [NH][NW][Q]
-    const float* Es = red + (NH > 0 ? NH * NW * Q : 0);                    // [emits][n_int]
+    float* red = reinterpret_cast<float*>(vbuf1 + ((vbytes + 15u) & ~15u)); // [2][NH][NW][Q], by step parity
+    const float* Es = red + (NH > 0 ? 2 * NH * NW * Q : 0);                // [emits][n_int]
     __shared__ unsigned s_work[2];
     __shared__ float s_bv[NW];
     __shared__ int s_bi[NW];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // provably warp-uniform: uniform branches on deg[]
     const SymT* __restrict__ sym = static_cast<const SymT*>(s.sym);
 
     // ---- one-time loads: emission table -> smem, this thread's edges -> registers ----
@@ -170,6 +179,7 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         o_n1[q] = 0;
     }
     bool drained = false;
+    [[maybe_unused]] int rpar = 0; // parity of the heavy-row partial buffer
     unsigned char* vcur = vbuf0;
     unsigned char* vnxt = vbuf1;
 
@@ -241,12 +251,6 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 if (p < n_light) store_v<Q>(vnxt, static_cast<uint32_t>(p) * Q * 4u, acc);
             }
         };
-        rank_step(std::integral_constant<int, 0>{});
-        rank_step(std::integral_constant<int, 1>{});
-        rank_step(std::integral_constant<int, 2>{});
-        rank_step(std::integral_constant<int, 3>{});
-        rank_step(std::integral_constant<int, 4>{});
-        static_assert(SV_ES_RMAX == 5, "rank_step calls above assume 5 ranks");
         if constexpr (NH > 0) {
             auto heavy_step = [&](auto hc) {
                 constexpr int h = decltype(hc)::value;
@@ -262,6 +266,9 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                                                                      he, acc);
 #pragma unroll
                     for (int q = 0; q < Q; ++q) {
+                        // first step of a sequence: v_0 = E[o_0] + start enters as warp 0's partial, the
+                        // other warps contribute +inf (min(x, +inf) = x: same bits)
+                        if (init[q]) acc[q] = (warp == 0 && lane == 0) ? he[q] + m.start_p[ph] : pos_inf();
                         if (m.nonneg) { // float order == signed-int order: one REDUX instead of five shuffle stages
                             acc[q] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(acc[q])));
                         } else {
@@ -269,41 +276,53 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                             for (int d = 16; d > 0; d >>= 1)
                                 acc[q] = fminf(acc[q], __shfl_xor_sync(0xffffffffu, acc[q], d));
                         }
-                        if (lane == 0) red[(h * NW + warp) * Q + q] = acc[q];
+                        if (lane == 0) red[((rpar * NH + h) * NW + warp) * Q + q] = acc[q];
                     }
                 }
             };
             heavy_step(std::integral_constant<int, 0>{});
             heavy_step(std::integral_constant<int, 1>{});
             static_assert(SV_ES_NHMAX == 2, "heavy_step calls above assume 2 heavy rows");
-            if (m.n_heavy > 0) {
-                __syncthreads();
-                if (warp < m.n_heavy) {
-                    const int h = warp;
-                    const int ph = n_light + h;
-                    float acc[Q];
-#pragma unroll
-                    for (int q = 0; q < Q; ++q) {
-                        float x = lane < NW ? red[(h * NW + lane) * Q + q] : pos_inf();
-                        if (m.nonneg) {
-                            x = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(x)));
-                        } else {
-#pragma unroll
-                            for (int d = 16; d > 0; d >>= 1)
-                                x = fminf(x, __shfl_xor_sync(0xffffffffu, x, d));
-                        }
-                        acc[q] = x;
-                        if (init[q]) acc[q] = erow[q][ph] + m.start_p[ph];
-                    }
-                    if (lane == 0) store_v<Q>(vnxt, static_cast<uint32_t>(ph) * Q * 4u, acc);
-                }
-            }
         }
-        __syncthreads();
+        // light rows after the heavy partials: the REDUX / shared-memory write of the partials overlaps them
+        rank_step(std::integral_constant<int, 0>{});
+        rank_step(std::integral_constant<int, 1>{});
+        rank_step(std::integral_constant<int, 2>{});
+        rank_step(std::integral_constant<int, 3>{});
+        rank_step(std::integral_constant<int, 4>{});
+        static_assert(SV_ES_RMAX == 5, "rank_step calls above assume 5 ranks");
+        __syncthreads(); // the ONE barrier of a step
         {
             unsigned char* sw = vcur;
             vcur = vnxt;
             vnxt = sw;
+        }
+        // heavy rows: EVERY warp reduces the NW partials itself and writes the (identical) result into
+        // the new current buffer -- its own lanes read it after the __syncwarp, so no second CTA barrier
+        // is needed (the partials are double buffered by step parity)
+        if constexpr (NH > 0) {
+            if (m.n_heavy > 0) {
+                static_assert(NW <= 32, "one lane per partial");
+#pragma unroll
+                for (int h = 0; h < NH; ++h) {
+                    if (h < m.n_heavy) {
+                        float x[Q];
+#pragma unroll
+                        for (int q = 0; q < Q; ++q) {
+                            x[q] = lane < NW ? red[((rpar * NH + h) * NW + lane) * Q + q] : pos_inf();
+                            if (m.nonneg) {
+                                x[q] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(x[q])));
+                            } else {
+#pragma unroll
+                                for (int d = 16; d > 0; d >>= 1) x[q] = fminf(x[q], __shfl_xor_sync(0xffffffffu, x[q], d));
+                            }
+                        }
+                        if (lane == 0) store_v<Q>(vcur, static_cast<uint32_t>(n_light + h) * Q * 4u, x);
+                    }
+                }
+                __syncwarp();
+            }
+            rpar ^= 1;
         }
 
         // ---- (C) advance lanes; emit results of finished sequences ----
