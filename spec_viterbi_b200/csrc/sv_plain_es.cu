@@ -164,17 +164,16 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 
     // ---- per-lane sequence state (CTA-uniform values) ----
     bool act[Q], init[Q];
-    uint32_t sid[Q];
-    uint64_t base[Q], len[Q], t[Q];
+    uint32_t sid[Q], rem[Q];      // sequence id, steps left
+    const SymT* sp[Q];            // symbol of the current step
     uint32_t o_cur[Q], o_n1[Q];
 #pragma unroll
     for (int q = 0; q < Q; ++q) {
         act[q] = false;
         init[q] = false;
         sid[q] = 0;
-        base[q] = 0;
-        len[q] = 0;
-        t[q] = 0;
+        rem[q] = 0;
+        sp[q] = sym;
         o_cur[q] = 0;
         o_n1[q] = 0;
     }
@@ -203,13 +202,13 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                         drained = true;
                     } else {
                         sid[q] = s.order[w];
-                        base[q] = s.off[sid[q]];
-                        len[q] = s.off[sid[q] + 1] - base[q];
-                        t[q] = 0;
+                        const uint64_t b0 = s.off[sid[q]];
+                        rem[q] = static_cast<uint32_t>(s.off[sid[q] + 1] - b0);
+                        sp[q] = sym + b0;
                         act[q] = true;
                         init[q] = true;
-                        o_cur[q] = sym[base[q]];
-                        o_n1[q] = sym[base[q] + 1]; // the symbol buffer is padded past the end
+                        o_cur[q] = sp[q][0];
+                        o_n1[q] = sp[q][1]; // the symbol buffer is padded past the end
                     }
                 }
             }
@@ -225,11 +224,28 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         // ---- (B) one time step for all lanes ----
         uint32_t o_n2[Q];
 #pragma unroll
-        for (int q = 0; q < Q; ++q) o_n2[q] = sym[base[q] + t[q] + 2]; // consumed two steps later
+        for (int q = 0; q < Q; ++q) o_n2[q] = sp[q][2]; // consumed two steps later
         const float* erow[Q];
 #pragma unroll
         for (int q = 0; q < Q; ++q) erow[q] = Es + static_cast<size_t>(o_cur[q]) * n_int;
 
+        // warp minimum of NV values under ONE uniform branch (the integer REDUX is valid when all scores
+        // are >= 0: float order == signed-int order)
+        auto warp_min_all = [&](auto& x) {
+            constexpr int NV = sizeof(x) / sizeof(float);
+            if (m.nonneg) {
+#pragma unroll
+                for (int k = 0; k < NV; ++k)
+                    (&x[0][0])[k] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int((&x[0][0])[k])));
+            } else {
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1)
+                        (&x[0][0])[k] = fminf((&x[0][0])[k], __shfl_xor_sync(0xffffffffu, (&x[0][0])[k], d));
+                }
+            }
+        };
         auto rank_step = [&](auto rc) {
             constexpr int r = decltype(rc)::value;
             if (r < nranks) {
@@ -242,47 +258,40 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                     acc[q] = pos_inf();
                 }
                 run_slots<Q, SH::base(r), SH::at(r), NSL>(deg[r], ew, eo, vcur, e, acc);
-                if (any_init) {
-                    const float st = m.start_p[pc];
-#pragma unroll
-                    for (int q = 0; q < Q; ++q)
-                        if (init[q]) acc[q] = e[q] + st; // v_0 = E[o_0] + start
-                }
                 if (p < n_light) store_v<Q>(vnxt, static_cast<uint32_t>(p) * Q * 4u, acc);
             }
         };
         if constexpr (NH > 0) {
-            auto heavy_step = [&](auto hc) {
-                constexpr int h = decltype(hc)::value;
-                if (h < NH && h < m.n_heavy) {
-                    const int ph = n_light + h;
-                    float he[Q], acc[Q];
+            if (m.n_heavy > 0) {
+                float hacc[NH][Q];
+                auto heavy_step = [&](auto hc) {
+                    constexpr int h = decltype(hc)::value;
+                    float he[Q];
 #pragma unroll
                     for (int q = 0; q < Q; ++q) {
-                        he[q] = erow[q][ph];
-                        acc[q] = pos_inf();
+                        he[q] = erow[q][n_light + (h < m.n_heavy ? h : 0)];
+                        hacc[h][q] = pos_inf();
                     }
-                    run_slots<Q, NL + (h < NH ? h : 0) * HS, HS, NSL>(m.heavy_slots[h], ew, eo, vcur,
-                                                                     he, acc);
+                    run_slots<Q, NL + h * HS, HS, NSL>(h < m.n_heavy ? m.heavy_slots[h] : 0, ew, eo, vcur, he, hacc[h]);
+                    if (any_init) { // first step of a sequence: v_0 = E[o_0] + start enters as ONE lane's partial,
+                                    // everybody else contributes +inf (min(x, +inf) = x: same bits)
 #pragma unroll
-                    for (int q = 0; q < Q; ++q) {
-                        // first step of a sequence: v_0 = E[o_0] + start enters as warp 0's partial, the
-                        // other warps contribute +inf (min(x, +inf) = x: same bits)
-                        if (init[q]) acc[q] = (warp == 0 && lane == 0) ? he[q] + m.start_p[ph] : pos_inf();
-                        if (m.nonneg) { // float order == signed-int order: one REDUX instead of five shuffle stages
-                            acc[q] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(acc[q])));
-                        } else {
-#pragma unroll
-                            for (int d = 16; d > 0; d >>= 1)
-                                acc[q] = fminf(acc[q], __shfl_xor_sync(0xffffffffu, acc[q], d));
-                        }
-                        if (lane == 0) red[((rpar * NH + h) * NW + warp) * Q + q] = acc[q];
+                        for (int q = 0; q < Q; ++q)
+                            if (init[q])
+                                hacc[h][q] = (warp == 0 && lane == 0 && h < m.n_heavy) ? he[q] + m.start_p[n_light + h] : pos_inf();
                     }
+                };
+                heavy_step(std::integral_constant<int, 0>{});
+                if constexpr (NH > 1) heavy_step(std::integral_constant<int, 1>{});
+                static_assert(NH <= 2 && SV_ES_NHMAX == 2, "heavy_step calls above assume 2 heavy rows");
+                warp_min_all(hacc);
+                if (lane == 0) {
+#pragma unroll
+                    for (int h = 0; h < NH; ++h)
+#pragma unroll
+                        for (int q = 0; q < Q; ++q) red[((rpar * NH + h) * NW + warp) * Q + q] = hacc[h][q];
                 }
-            };
-            heavy_step(std::integral_constant<int, 0>{});
-            heavy_step(std::integral_constant<int, 1>{});
-            static_assert(SV_ES_NHMAX == 2, "heavy_step calls above assume 2 heavy rows");
+            }
         }
         // light rows after the heavy partials: the REDUX / shared-memory write of the partials overlaps them
         rank_step(std::integral_constant<int, 0>{});
@@ -291,6 +300,18 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         rank_step(std::integral_constant<int, 3>{});
         rank_step(std::integral_constant<int, 4>{});
         static_assert(SV_ES_RMAX == 5, "rank_step calls above assume 5 ranks");
+        if (any_init) { // rare: v_0 = E[o_0] + start overwrites the relaxed scores (same thread, program order)
+#pragma unroll 1
+            for (int r = 0; r < nranks; ++r) {
+                const int p = tid + r * TPG;
+                if (p < n_light) {
+                    const float st = m.start_p[p];
+#pragma unroll
+                    for (int q = 0; q < Q; ++q)
+                        if (init[q]) reinterpret_cast<float*>(vnxt)[p * Q + q] = erow[q][p] + st;
+                }
+            }
+        }
         __syncthreads(); // the ONE barrier of a step
         {
             unsigned char* sw = vcur;
@@ -303,22 +324,17 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
         if constexpr (NH > 0) {
             if (m.n_heavy > 0) {
                 static_assert(NW <= 32, "one lane per partial");
+                float x[NH][Q];
 #pragma unroll
-                for (int h = 0; h < NH; ++h) {
-                    if (h < m.n_heavy) {
-                        float x[Q];
+                for (int h = 0; h < NH; ++h)
 #pragma unroll
-                        for (int q = 0; q < Q; ++q) {
-                            x[q] = lane < NW ? red[((rpar * NH + h) * NW + lane) * Q + q] : pos_inf();
-                            if (m.nonneg) {
-                                x[q] = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(x[q])));
-                            } else {
+                    for (int q = 0; q < Q; ++q)
+                        x[h][q] = lane < NW ? red[((rpar * NH + h) * NW + lane) * Q + q] : pos_inf();
+                warp_min_all(x);
+                if (lane == 0) {
 #pragma unroll
-                                for (int d = 16; d > 0; d >>= 1) x[q] = fminf(x[q], __shfl_xor_sync(0xffffffffu, x[q], d));
-                            }
-                        }
-                        if (lane == 0) store_v<Q>(vcur, static_cast<uint32_t>(n_light + h) * Q * 4u, x);
-                    }
+                    for (int h = 0; h < NH; ++h)
+                        if (h < m.n_heavy) store_v<Q>(vcur, static_cast<uint32_t>(n_light + h) * Q * 4u, x[h]);
                 }
                 __syncwarp();
             }
@@ -332,8 +348,8 @@ sv_es_kernel(SvEsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
             o_cur[q] = o_n1[q];
             o_n1[q] = o_n2[q];
             if (act[q]) {
-                t[q] += 1;
-                if (t[q] == len[q]) {
+                ++sp[q]; // only while active: an idle slot must not walk past the padded end of the symbols
+                if (--rem[q] == 0) {
                     act[q] = false;
                     const float* vq = reinterpret_cast<const float*>(vcur) + q;
                     float bv = pos_inf();
