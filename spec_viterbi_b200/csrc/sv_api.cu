@@ -117,8 +117,7 @@ int upload_generic(sv_model* m) {
     return SV_OK;
 }
 
-int upload_es(sv_model* m) {
-    const SvEsPlan& p = m->es;
+int upload_es(sv_model* m, const SvEsPlan& p, SvEsDev& d, void** blob) {
     size_t bytes = 0;
     const size_t o_w = blob_reserve<float>(&bytes, p.edge_w.size());
     const size_t o_off = blob_reserve<uint32_t>(&bytes, p.edge_off.size());
@@ -136,10 +135,9 @@ int upload_es(sv_model* m) {
     std::memcpy(host.data() + o_start, p.start_p.data(), p.start_p.size() * 4);
     std::memcpy(host.data() + o_cptr, p.copy_ptr.data(), p.copy_ptr.size() * 4);
     std::memcpy(host.data() + o_cp, p.copy_p.data(), p.copy_p.size() * 4);
-    SV_CUDA(cudaMalloc(&m->d_es_blob, bytes));
-    SV_CUDA(cudaMemcpy(m->d_es_blob, host.data(), bytes, cudaMemcpyHostToDevice));
-    auto* base = static_cast<unsigned char*>(m->d_es_blob);
-    SvEsDev& d = m->esdev;
+    SV_CUDA(cudaMalloc(blob, bytes));
+    SV_CUDA(cudaMemcpy(*blob, host.data(), bytes, cudaMemcpyHostToDevice));
+    auto* base = static_cast<unsigned char*>(*blob);
     d.n = static_cast<int>(m->n);
     d.n_int = p.n_int;
     d.n_light = p.n_light;
@@ -296,10 +294,20 @@ extern "C" int sv_model_create(uint64_t states, uint64_t emits, uint64_t trans,
 
     sv_es_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->es);
     if (m->es.valid) {
-        if ((rc = upload_es(m)) != SV_OK) return fail(rc);
+        if ((rc = upload_es(m, m->es, m->esdev, &m->d_es_blob)) != SV_OK) return fail(rc);
         if (sv_es_prepare(m->es.variant_index, m->es.smem_bytes) != 0) {
             cudaGetLastError();
             m->es.valid = false; // kernel attribute rejected: keep the generic kernel
+        }
+    }
+    if (m->es.valid && m->es.var.q == 2) { // one-sequence-per-CTA twin for small batches
+        sv_es_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->es1, 1);
+        if (m->es1.valid) {
+            if ((rc = upload_es(m, m->es1, m->esdev1, &m->d_es1_blob)) != SV_OK) return fail(rc);
+            if (sv_es_prepare(m->es1.variant_index, m->es1.smem_bytes) != 0) {
+                cudaGetLastError();
+                m->es1.valid = false;
+            }
         }
     }
     sv_ls_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->ls);
@@ -319,6 +327,7 @@ extern "C" void sv_model_destroy(sv_model* m) {
     cudaSetDevice(m->device);
     if (m->d_blob) cudaFree(m->d_blob);
     if (m->d_es_blob) cudaFree(m->d_es_blob);
+    if (m->d_es1_blob) cudaFree(m->d_es1_blob);
     if (m->d_ls_blob) cudaFree(m->d_ls_blob);
     if (m->d_pair_blob) cudaFree(m->d_pair_blob);
     if (m->d_counter) cudaFree(m->d_counter);
@@ -659,11 +668,17 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
         rc = sv_ls_launch(m->ls.variant_index, m->lsdev, seqs->dev, d_out, d_best, d_best_state,
                           m->d_counter, grid, m->ls.smem_bytes, st);
     } else if (kernel == SV_KERNEL_ES) {
-        const int per_sm = std::max(1, sv_es_max_ctas_per_sm(m->es.variant_index, m->es.smem_bytes));
-        const int64_t want = (static_cast<int64_t>(seqs->nseq) + m->es.var.q - 1) / m->es.var.q;
+        // a batch small enough that every sequence gets its own resident CTA runs one sequence per CTA
+        // (shorter steps); larger batches advance two sequences per CTA in lockstep
+        const bool solo = m->es1.valid &&
+                          static_cast<int64_t>(seqs->nseq) <=
+                              int64_t(m->sm_count) * std::max(1, sv_es_max_ctas_per_sm(m->es1.variant_index, m->es1.smem_bytes));
+        const SvEsPlan& pl = solo ? m->es1 : m->es;
+        const int per_sm = std::max(1, sv_es_max_ctas_per_sm(pl.variant_index, pl.smem_bytes));
+        const int64_t want = (static_cast<int64_t>(seqs->nseq) + pl.var.q - 1) / pl.var.q;
         const int grid = static_cast<int>(std::min<int64_t>(want, int64_t(m->sm_count) * per_sm));
-        rc = sv_es_launch(m->es.variant_index, m->esdev, seqs->dev, d_out, d_best, d_best_state,
-                          m->d_counter, grid, m->es.smem_bytes, st);
+        rc = sv_es_launch(pl.variant_index, solo ? m->esdev1 : m->esdev, seqs->dev, d_out, d_best, d_best_state,
+                          m->d_counter, grid, pl.smem_bytes, st);
     } else {
         const int grid = static_cast<int>(std::min<uint64_t>(seqs->nseq, m->sm_count));
         rc = sv_generic_launch(m->gen, seqs->dev, d_out, d_best, d_best_state, m->d_counter, grid,

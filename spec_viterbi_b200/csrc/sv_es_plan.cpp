@@ -398,7 +398,7 @@ uint64_t plan_cost(const SvEsPlan& p) {
 
 void sv_es_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
                       const std::vector<float>& start, uint64_t emits, size_t smem_limit,
-                      SvEsPlan* plan) {
+                      SvEsPlan* plan, int force_q) {
     plan->valid = false;
     const size_t n = csr.n;
     // thread count: enough threads that a thread owns ~2-5 rows
@@ -406,7 +406,7 @@ void sv_es_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
     if (n > 3 * 128) want_threads = 256;
     if (n > 3 * 256) want_threads = 512;
     if (const char* env = std::getenv("SV_ES_THREADS")) want_threads = std::atoi(env);
-    int want_q = 0;
+    int want_q = force_q;
     if (const char* env = std::getenv("SV_ES_Q")) want_q = std::atoi(env);
 
     SvEsPlan bestp;

@@ -200,6 +200,11 @@ struct sv_model {
     SvEsPlan es;
     SvEsDev esdev;
     void* d_es_blob = nullptr;
+    // the same with ONE sequence per CTA: lower step latency, used when every sequence of a batch
+    // gets its own resident CTA (the latency cases: a handful of long sequences)
+    SvEsPlan es1;
+    SvEsDev esdev1;
+    void* d_es1_blob = nullptr;
     // lockstep plan
     SvLsPlan ls;
     SvLsDev lsdev;
@@ -236,9 +241,10 @@ int sv_ws_download(sv_model* m, uint64_t nseq, const float* d_out, const float* 
                    const int32_t* d_arg, float* out, float* best, int32_t* best_state);
 
 // K0: build the edge-stationary schedule (sv_es_plan.cpp); plan.valid=false if no variant fits.
+// force_q: 0 = prefer two sequences per CTA, 1 / 2 = only variants with that many.
 void sv_es_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
                       const std::vector<float>& start, uint64_t emits, size_t smem_limit,
-                      SvEsPlan* plan);
+                      SvEsPlan* plan, int force_q = 0);
 
 // K0 for the lockstep kernel (sv_ls_plan.cpp); plan.valid=false if the model does not fit.
 void sv_ls_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
