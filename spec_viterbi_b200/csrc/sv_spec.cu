@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <new>
@@ -101,6 +102,80 @@ sparse_lhs_kernel(SvGenericDev m, const float* __restrict__ prev, uint64_t prev_
 #pragma unroll
         for (int c = 0; c < 4; ++c)
             if (k0 + c < n) O[k0 + c] = acc[c];
+    }
+}
+
+// K3' organised by PREFIX: one CTA owns (row i, prefix) and produces that row for all `emits` tuples
+// that extend the prefix, so every P[prefix][j][k] is loaded once and used `emits` times
+// (the kernel above re-reads it per tuple with a 16-byte lane stride: 4 L1 wavefronts per load and
+// four partial stores per line).  One column per thread per iteration: loads and stores are 128
+// contiguous bytes per warp.  Rows with more than 256 in-edges (the generic kernel's heavy list) are
+// split into 256-column tiles on a separate launch.  Same association => same bits.
+// EB = tuples of one prefix kept in registers at a time, KU = columns per thread (256 apart, so that a
+// CTA writes KU KB of every tuple's row back to back)
+#ifndef SV_LHS_EB
+#define SV_LHS_EB 10
+#define SV_LHS_KU 4
+#endif
+template <int EB, int KU>
+__global__ void __launch_bounds__(256, 3)
+sparse_lhs_prefix_kernel(SvGenericDev m, const float* __restrict__ prev, uint64_t prev_first,
+                         float* __restrict__ out, uint64_t out_first, uint64_t tb, uint64_t te,
+                         uint64_t prefix_first, int emits, int heavy_pass) {
+    const int n = m.n, tid = threadIdx.x;
+    int i, kbeg, kend;
+    uint64_t prefix;
+    if (heavy_pass) {
+        i = static_cast<int>(m.heavy_rows[blockIdx.y]);
+        kbeg = blockIdx.x * 256 * KU;
+        kend = min(n, kbeg + 256 * KU);
+        prefix = prefix_first + blockIdx.z;
+    } else {
+        i = blockIdx.x;
+        kbeg = 0;
+        kend = n;
+        prefix = prefix_first + blockIdx.y;
+    }
+    const uint32_t p0 = m.rowptr[i], p1 = m.rowptr[i + 1];
+    if (!heavy_pass && p1 - p0 > 256u) return; // same rule as the heavy list (sv_api.cu upload_generic)
+    const uint64_t t_lo = max(tb, prefix * emits), t_hi = min(te, (prefix + 1) * emits);
+    if (t_lo >= t_hi) return;
+    const size_t nn = static_cast<size_t>(n) * n;
+    const float* __restrict__ P = prev + (prefix - prev_first) * nn;
+    for (uint64_t t0 = t_lo; t0 < t_hi; t0 += EB) {
+        const int nb = static_cast<int>(min(static_cast<uint64_t>(EB), t_hi - t0));
+        float e[EB];
+#pragma unroll
+        for (int b = 0; b < EB; ++b) e[b] = m.emis[static_cast<size_t>((t0 + min(b, nb - 1)) % emits) * n + i];
+        float* __restrict__ O = out + (t0 - out_first) * nn + static_cast<size_t>(i) * n;
+        for (int k0 = kbeg + tid; k0 < kend; k0 += 256 * KU) {
+            float acc[EB][KU];
+#pragma unroll
+            for (int b = 0; b < EB; ++b)
+#pragma unroll
+                for (int u = 0; u < KU; ++u) acc[b][u] = pos_inf();
+#pragma unroll 2
+            for (uint32_t p = p0; p < p1; ++p) {
+                const float w = m.w[p];
+                const float* __restrict__ prow = P + static_cast<size_t>(m.col[p]) * n + k0;
+                float pv[KU];
+#pragma unroll
+                for (int u = 0; u < KU; ++u) pv[u] = k0 + 256 * u < kend ? prow[256 * u] : pos_inf();
+#pragma unroll
+                for (int b = 0; b < EB; ++b) {
+                    const float a = e[b] + w; // level-1 value M_sym[i][j]
+#pragma unroll
+                    for (int u = 0; u < KU; ++u) acc[b][u] = fminf(acc[b][u], a + pv[u]);
+                }
+            }
+#pragma unroll
+            for (int b = 0; b < EB; ++b)
+                if (b < nb) {
+#pragma unroll
+                    for (int u = 0; u < KU; ++u)
+                        if (k0 + 256 * u < kend) O[b * nn + k0 + 256 * u] = acc[b][u];
+                }
+        }
     }
 }
 
@@ -738,15 +813,52 @@ int build_sparse(sv_model* m, uint64_t lvl, uint64_t tb, uint64_t te, float* dst
     }
     int rc = build_sparse(m, lvl - 1, pb, pe, prev, st);
     if (rc == SV_OK) {
-        const uint64_t zmax = 32768;
-        for (uint64_t t0 = tb; t0 < te && rc == SV_OK; t0 += zmax) {
-            const uint64_t cnt = std::min(zmax, te - t0);
+        const uint64_t ymax = 32768;
+        const bool per_tuple = std::getenv("SV_SPEC_LHS_PER_TUPLE") != nullptr; // first version, kept for A/B runs
+        for (uint64_t t0 = tb; per_tuple && t0 < te && rc == SV_OK; t0 += ymax) {
+            const uint64_t cnt = std::min(ymax, te - t0);
             dim3 grid(static_cast<unsigned>((n + 1023) / 1024), static_cast<unsigned>(n),
                       static_cast<unsigned>(cnt));
             sparse_lhs_kernel<<<grid, 256, 0, st>>>(m->gen, prev, pb, dst + (t0 - tb) * mat, t0,
                                                     static_cast<int>(m->emits));
             if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "sparse_lhs launch failed");
         }
+        // the heavy rows' long-running CTAs go to a side stream: they write other rows than the light pass
+        cudaStream_t hst = nullptr;
+        cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+        if (!per_tuple && m->gen.n_heavy > 0) {
+            if (cudaStreamCreateWithFlags(&hst, cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming) != cudaSuccess)
+                rc = sv_fail(SV_ERR_CUDA, "spec precompute: side stream");
+            if (rc == SV_OK) {
+                cudaEventRecord(ev_fork, st); // prev is complete
+                cudaStreamWaitEvent(hst, ev_fork, 0);
+            }
+        }
+        for (uint64_t f0 = pb; !per_tuple && f0 < pe && rc == SV_OK; f0 += ymax) {
+            const uint64_t cnt = std::min(ymax, pe - f0);
+            if (m->gen.n_heavy > 0) {
+                dim3 hgrid(static_cast<unsigned>((n + 255) / 256), static_cast<unsigned>(m->gen.n_heavy),
+                           static_cast<unsigned>(cnt));
+                sparse_lhs_prefix_kernel<20, 1><<<hgrid, 256, 0, hst>>>(m->gen, prev, pb, dst, tb, tb, te, f0,
+                                                                        static_cast<int>(m->emits), 1);
+            }
+            dim3 grid(static_cast<unsigned>(n), static_cast<unsigned>(cnt));
+            sparse_lhs_prefix_kernel<SV_LHS_EB, SV_LHS_KU><<<grid, 256, 0, st>>>(m->gen, prev, pb, dst, tb, tb, te, f0,
+                                                                               static_cast<int>(m->emits), 0);
+            if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "sparse_lhs launch failed");
+        }
+        if (hst != nullptr) {
+            if (ev_join != nullptr) {
+                cudaEventRecord(ev_join, hst);
+                cudaStreamWaitEvent(st, ev_join, 0);
+            }
+            cudaStreamSynchronize(hst);
+            cudaStreamDestroy(hst);
+        }
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_join) cudaEventDestroy(ev_join);
     }
     cudaError_t e = cudaStreamSynchronize(st);
     cudaFree(prev);

@@ -8,6 +8,7 @@ sys.path.insert(0, str(ROOT))
 from spec_viterbi_b200 import api, _lib, generators  # noqa: E402
 
 def main():
+    method = {"pair": _lib.SPEC_PAIR_ROWS, "sparse": _lib.SPEC_SPARSE_LHS}[sys.argv[1] if len(sys.argv) > 1 else "pair"]
     peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
     hbm = peaks.get("hbm_gbs", 6546.2)
     res = {}
@@ -18,12 +19,12 @@ def main():
             hmm = generators.random_hmm(states_num=2405, trans_per_state=3, num_non_zero_start_probs=2, seed=2405)
         n, E = hmm.states_num, hmm.emit_num
         m = api.Model(hmm)
-        sp = api.Spec(m, 2, _lib.SPEC_PAIR_ROWS)
+        sp = api.Spec(m, 2, method)
         ptr, tb, te = sp.table()
         ts = []
         for _ in range(5):
             t0 = time.perf_counter()
-            sp2 = api.Spec(m, 2, _lib.SPEC_PAIR_ROWS, tb, te, d_table=ptr)
+            sp2 = api.Spec(m, 2, method, tb, te, d_table=ptr)
             ts.append((time.perf_counter() - t0) * 1e3)
             sp2.close()
         gb = E * E * n * n * 4 / 1e9
