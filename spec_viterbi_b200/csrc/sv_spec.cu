@@ -793,6 +793,9 @@ uint64_t ipow(uint64_t b, uint64_t e) {
 
 // Builds handlers [tb, te) of level `lvl` into dst (dense, ld = n) with the sparse-left
 // kernel, recursing over the prefixes.  Level 1 = dense scatter of M_o.
+bool pair_prepare(sv_model* m, SvPairDev* out);
+int build_pair_level2(sv_model* m, const SvPairDev& pd, uint64_t tb, uint64_t te, float* dst, cudaStream_t st);
+
 int build_sparse(sv_model* m, uint64_t lvl, uint64_t tb, uint64_t te, float* dst, cudaStream_t st) {
     const size_t n = m->n;
     const size_t mat = n * n;
@@ -811,7 +814,11 @@ int build_sparse(sv_model* m, uint64_t lvl, uint64_t tb, uint64_t te, float* dst
         cudaGetLastError();
         return sv_fail(SV_ERR_MEMORY, "spec precompute: prefix table does not fit device memory");
     }
-    int rc = build_sparse(m, lvl - 1, pb, pe, prev, st);
+    // the level-2 prefix table of a level-3 build comes from the streaming pair kernel when the model allows
+    SvPairDev pd;
+    int rc = (lvl == 3 && std::getenv("SV_SPEC_LHS_PER_TUPLE") == nullptr && pair_prepare(m, &pd))
+                 ? build_pair_level2(m, pd, pb, pe, prev, st)
+                 : build_sparse(m, lvl - 1, pb, pe, prev, st);
     if (rc == SV_OK) {
         const uint64_t ymax = 32768;
         const bool per_tuple = std::getenv("SV_SPEC_LHS_PER_TUPLE") != nullptr; // first version, kept for A/B runs
@@ -845,6 +852,8 @@ int build_sparse(sv_model* m, uint64_t lvl, uint64_t tb, uint64_t te, float* dst
                                                                         static_cast<int>(m->emits), 1);
             }
             dim3 grid(static_cast<unsigned>(n), static_cast<unsigned>(cnt));
+            // (<20, 2> for short rows was tried on 500.chmm level 3: 11.1 ms vs 6.4 ms -- fewer concurrent
+            //  output streams per CTA matter more than idle lanes)
             sparse_lhs_prefix_kernel<SV_LHS_EB, SV_LHS_KU><<<grid, 256, 0, st>>>(m->gen, prev, pb, dst, tb, tb, te, f0,
                                                                                static_cast<int>(m->emits), 0);
             if (cudaGetLastError() != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "sparse_lhs launch failed");
