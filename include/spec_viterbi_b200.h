@@ -173,6 +173,15 @@ int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out);
 int sv_spec_save(const sv_spec* s, const char* path);
 int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out);
 
+/* How sv_spec_run* applies a level-2 chunk (GraphBLAS_spec_impl.cpp:69-79, one GrB_mxm per chunk):
+ * SV_SPEC_RUN_TABLE (default) reads the precomputed dense handler (K4, 4*N^2 bytes per chunk);
+ * SV_SPEC_RUN_IMPLICIT recomputes the handler entries it needs from the two sparse level-1 factors
+ * (K4i) -- same sums, same association, same bits, no table traffic; the table may then be empty
+ * (sv_spec_create with tuple_begin == tuple_end == emits^level).  Level 2, models with at most 4
+ * dense rows; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.  Level 1 ignores the mode. */
+enum { SV_SPEC_RUN_TABLE = 0, SV_SPEC_RUN_IMPLICIT = 1 };
+int sv_spec_set_run_mode(sv_spec* s, int mode);
+
 int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out);
 int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
                       float* out, float* best, int32_t* best_state);

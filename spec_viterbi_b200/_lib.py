@@ -14,6 +14,7 @@ LIB_PATH = _PKG / "libspecviterbi_b200.so"
 SV_OK = 0
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_ES, KERNEL_LS = 0, 1, 2, 3
 SPEC_AUTO, SPEC_DENSE_GEMM, SPEC_SPARSE_LHS, SPEC_PAIR_ROWS = 0, 1, 2, 3
+SPEC_RUN_TABLE, SPEC_RUN_IMPLICIT = 0, 1
 
 u64p = C.POINTER(C.c_uint64)
 u8p = C.POINTER(C.c_uint8)
@@ -66,6 +67,7 @@ SIGNATURES = {
     "sv_spec_destroy": (None, [vp]),
     "sv_spec_level": (C.c_uint64, [vp]),
     "sv_spec_set_range": (C.c_int, [vp, C.c_uint64, C.c_uint64]),
+    "sv_spec_set_run_mode": (C.c_int, [vp, C.c_int]),
     "sv_spec_table": (vp, [vp, u64p, u64p]),
     "sv_spec_get_handler": (C.c_int, [vp, C.c_uint64, f32p]),
     "sv_spec_save": (C.c_int, [vp, C.c_char_p]),

@@ -324,6 +324,11 @@ class Spec:
     def set_range(self, b: int, e: int) -> None:
         L.check(self._lib.sv_spec_set_range(self._h, b, e))
 
+    def set_run_mode(self, mode: int) -> None:
+        """L.SPEC_RUN_TABLE (K4, reads the dense handlers) or L.SPEC_RUN_IMPLICIT (K4i, level 2: the
+        handler entries are recomputed from the sparse factors; bit-identical)."""
+        L.check(self._lib.sv_spec_set_run_mode(self._h, mode))
+
     def table(self):
         """-> (device pointer of the handler table, first tuple, end tuple)."""
         tb, te = C.c_uint64(), C.c_uint64()

@@ -30,6 +30,7 @@ struct sv_spec {
     uint64_t table_first = 0; // tuple index stored at d_table[0]
     bool owns_table = false;
     int method = SV_SPEC_SPARSE_LHS;
+    int run_mode = SV_SPEC_RUN_TABLE; // SV_SPEC_RUN_IMPLICIT: level-2 chunks recomputed from the sparse factors (K4i)
     // run-phase scratch
     float* d_v[2] = {nullptr, nullptr};
     uint64_t v_capacity = 0;
@@ -704,6 +705,131 @@ handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
     }
 }
 
+// K4i: the level-2 chunk WITHOUT reading the table ("recompute on demand").  fl(. + v[k]) is monotone,
+// so it commutes with the min over j inside a handler entry:
+//   vout[i] = min_k fl( H(a,b)[i][k] + v[k] )
+//           = min_{j in in(i)} min_{k in in(j)} fl( fl( fl(E[b][i]+T'[i][j]) + fl(E[a][j]+T'[j][k]) ) + v[k] )
+// -- the same singly rounded sums in the same association as table + K4, hence the same bits, but the
+// work is the number of two-step paths instead of N^2 table reads.  One thread per light row i: light j
+// are walked through the CSR; for a heavy j (dense row of T', staged per CTA as r_h[k] = fl(E[a][j] +
+// T'[j][k]) beside v) the thread streams all k with broadcast 16-byte shared loads.  Heavy rows i get a
+// CTA each (blockIdx.x >= ntiles).  Up to kImplicitMaxHeavy dense rows.
+constexpr int kImplicitMaxHeavy = 4;
+constexpr int kImplicitThreads = 128;
+
+__device__ __forceinline__ float heavy_stream(float u, const float4* __restrict__ r4,
+                                              const float4* __restrict__ v4, int n4, int k0, int kstep) {
+    float b0 = pos_inf(), b1 = pos_inf(), b2 = pos_inf(), b3 = pos_inf();
+#pragma unroll 2
+    for (int k = k0; k < n4; k += kstep) {
+        const float4 r = r4[k];
+        const float4 v = v4[k];
+        b0 = fminf(b0, (u + r.x) + v.x);
+        b1 = fminf(b1, (u + r.y) + v.y);
+        b2 = fminf(b2, (u + r.z) + v.z);
+        b3 = fminf(b3, (u + r.w) + v.w);
+    }
+    return fminf(fminf(b0, b1), fminf(b2, b3));
+}
+
+__global__ void __launch_bounds__(kImplicitThreads)
+implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* __restrict__ vin,
+                          float* __restrict__ vout, int seq_base, int ntiles, int npad) {
+    extern __shared__ float4 sm4[];
+    float* sv = reinterpret_cast<float*>(sm4);  // [npad] v, +inf padded
+    float* sr = sv + npad;                      // [n_heavy][npad] r_h
+    __shared__ float s_red[kImplicitThreads / 32];
+    const int n = pd.n;
+    const int q = seq_base + blockIdx.y;
+    const uint64_t o0 = s.off[q];
+    const uint64_t len = s.off[q + 1] - o0;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
+    float* __restrict__ vo = vout + static_cast<size_t>(q) * n;
+    const bool heavy_cta = static_cast<int>(blockIdx.x) >= ntiles;
+    const int hme = static_cast<int>(blockIdx.x) - ntiles;
+    if (chunk >= (len - 1) / 2) {
+        if (heavy_cta) {
+            if (threadIdx.x == 0) vo[pd.hrow[hme]] = vi[pd.hrow[hme]];
+        } else {
+            const int i = blockIdx.x * kImplicitThreads + threadIdx.x;
+            if (i < n && pd.hidx[i] < 0) vo[i] = vi[i];
+        }
+        return;
+    }
+    const unsigned a = load_sym(s, o0 + 1 + chunk * 2), b = load_sym(s, o0 + 2 + chunk * 2);
+    const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
+    const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
+    for (int k = threadIdx.x; k < npad; k += kImplicitThreads) sv[k] = k < n ? vi[k] : pos_inf();
+    for (int h = 0; h < pd.n_heavy; ++h) {
+        const float e = ea[pd.hrow[h]];
+        const float* __restrict__ wrow = pd.wd + static_cast<size_t>(h) * n;
+        for (int k = threadIdx.x; k < npad; k += kImplicitThreads)
+            sr[h * npad + k] = k < n ? e + wrow[k] : pos_inf();
+    }
+    __syncthreads();
+    const float4* __restrict__ v4 = reinterpret_cast<const float4*>(sv);
+    const int n4 = npad >> 2;
+    if (!heavy_cta) {
+        const int i = blockIdx.x * kImplicitThreads + threadIdx.x;
+        const bool live = i < n && pd.hidx[i] < 0;
+        float uh[kImplicitMaxHeavy];
+#pragma unroll
+        for (int h = 0; h < kImplicitMaxHeavy; ++h) uh[h] = pos_inf();
+        float best = pos_inf();
+        if (live) {
+            const float e = eb[i];
+            for (uint32_t p = pd.rowptr[i]; p < pd.rowptr[i + 1]; ++p) {
+                const uint32_t j = pd.col[p];
+                const float u = e + pd.w[p];
+                const int hj = pd.hidx[j];
+                if (hj >= 0) {
+#pragma unroll
+                    for (int h = 0; h < kImplicitMaxHeavy; ++h)
+                        if (hj == h) uh[h] = u;
+                } else {
+                    const float ej = ea[j];
+                    for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
+                        best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
+                }
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < kImplicitMaxHeavy; ++h) {
+            if (h < pd.n_heavy && __any_sync(0xffffffffu, uh[h] < pos_inf()))
+                best = fminf(best, heavy_stream(uh[h], reinterpret_cast<const float4*>(sr + h * npad), v4, n4, 0, 1));
+        }
+        if (live) vo[i] = best;
+        return;
+    }
+    // heavy row: the CTA strides over its entries; heavy sources are streamed by all threads
+    const int i = static_cast<int>(pd.hrow[hme]);
+    const float e = eb[i];
+    float best = pos_inf();
+    for (uint32_t p = pd.rowptr[i] + threadIdx.x; p < pd.rowptr[i + 1]; p += kImplicitThreads) {
+        const uint32_t j = pd.col[p];
+        if (pd.hidx[j] >= 0) continue;
+        const float u = e + pd.w[p];
+        const float ej = ea[j];
+        for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
+            best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
+    }
+    for (int h = 0; h < pd.n_heavy; ++h) {
+        const float w = pd.wd[static_cast<size_t>(hme) * n + pd.hrow[h]]; // T'[i][hrow[h]], +inf = absent
+        if (w < pos_inf())
+            best = fminf(best, heavy_stream(e + w, reinterpret_cast<const float4*>(sr + h * npad), v4, n4,
+                                            threadIdx.x, kImplicitThreads));
+    }
+    best = warp_min(best);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float r = s_red[0];
+#pragma unroll
+        for (int wv = 1; wv < kImplicitThreads / 32; ++wv) r = fminf(r, s_red[wv]);
+        vo[i] = r;
+    }
+}
+
 // Level-1 tail step number `tail` (0-based) of every sequence that still has one
 // (GraphBLAS_spec_impl.cpp:84-89); others copy.  One CTA per sequence.
 __global__ void __launch_bounds__(1024)
@@ -1290,6 +1416,37 @@ extern "C" int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_sp
     return SV_OK;
 }
 
+namespace {
+size_t implicit_smem(const SvPairDev& pd) {
+    return static_cast<size_t>(1 + pd.n_heavy) * ((pd.n + 3) / 4 * 4) * sizeof(float);
+}
+
+// K4i applies to level 2 of models with at most kImplicitMaxHeavy dense rows whose staged copies fit
+// the shared memory of one CTA.
+bool implicit_supported(sv_spec* s, SvPairDev* pd) {
+    if (s->level != 2 || !pair_prepare(s->m, pd) || pd->n_heavy > kImplicitMaxHeavy) return false;
+    const size_t bytes = implicit_smem(*pd);
+    if (bytes > 200 * 1024) return false;
+    return cudaFuncSetAttribute(implicit_pair_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(bytes)) == cudaSuccess;
+}
+} // namespace
+
+extern "C" int sv_spec_set_run_mode(sv_spec* s, int mode) {
+    if (s == nullptr || (mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT))
+        return sv_fail(SV_ERR_ARG, "sv_spec_set_run_mode: bad argument");
+    if (mode == SV_SPEC_RUN_IMPLICIT && s->level > 1) {
+        SV_CUDA(cudaSetDevice(s->m->device));
+        SvPairDev pd;
+        if (!implicit_supported(s, &pd)) {
+            cudaGetLastError();
+            return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_set_run_mode: implicit run needs level 2 and at most 4 dense rows");
+        }
+    }
+    s->run_mode = mode;
+    return SV_OK;
+}
+
 extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out, float* d_best,
                                   int32_t* d_best_state, void* stream) {
     if (s == nullptr || seqs == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run_device: NULL");
@@ -1297,10 +1454,14 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     if (s->level == 1) return sv_viterbi_device(m, seqs, d_out, d_best, d_best_state, stream);
     if (seqs->device != m->device)
         return sv_fail(SV_ERR_ARG, "sv_spec_run_device: sequences live on another device");
-    if (s->t_begin != 0 || s->t_end != s->ntuples)
+    const bool implicit = s->run_mode == SV_SPEC_RUN_IMPLICIT;
+    if (!implicit && (s->t_begin != 0 || s->t_end != s->ntuples))
         return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SV_CUDA(cudaSetDevice(m->device));
+    SvPairDev pd;
+    if (implicit && !implicit_supported(s, &pd))
+        return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_run: implicit run needs level 2 and at most 4 dense rows");
     const size_t n = m->n;
     const uint64_t nseq = seqs->nseq;
     if (s->v_capacity < nseq) {
@@ -1343,6 +1504,15 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     for (uint64_t c = 0; c < max_chunks; ++c) {
         for (int g = 0; g < ngroups; ++g) {
             const uint64_t q0 = nseq * g / ngroups, q1 = nseq * (g + 1) / ngroups;
+            if (implicit) {
+                const int ntiles = static_cast<int>((n + kImplicitThreads - 1) / kImplicitThreads);
+                const int npad = static_cast<int>((n + 3) / 4 * 4);
+                dim3 igrid(static_cast<unsigned>(ntiles + pd.n_heavy), static_cast<unsigned>(q1 - q0));
+                implicit_pair_step_kernel<<<igrid, kImplicitThreads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
+                    pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles, npad);
+                ++launches;
+                continue;
+            }
             dim3 grid(static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta), static_cast<unsigned>(q1 - q0));
             handler_gemv_kernel<<<grid, 256, n * sizeof(float), g == 0 ? st : s->aux[g - 1]>>>(
                 static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c,

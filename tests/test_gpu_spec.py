@@ -146,3 +146,76 @@ def test_handler_table_save_load(api, oracle, tmp_path):
         api.Spec.load(m, tmp_path / "junk")
     with pytest.raises(_lib.SvError):
         api.Spec(m, 1).save(tmp_path / "l1")
+
+
+def test_implicit_run_reference_fixture(api, load_model, load_seqs, golden):
+    """K4i (level-2 chunks recomputed from the sparse factors, no table) gives the reference's bits:
+    profile HMMs (two dense rows, one dense column) against the fixtures generated from
+    GraphBLAS_spec_impl (level 2), with an EMPTY handler table."""
+    from spec_viterbi_b200 import _lib
+    for name in ("100", "200"):
+        hmm = load_model(name)
+        m = api.Model(hmm)
+        sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)  # nothing precomputed
+        sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+        syms, offs = api.pack_sequences(load_seqs("emit_3_3500_20"))
+        out, best, arg = sp.run_batch(syms, offs)
+        for k in range(3):
+            assert same_bits(out[k], golden[f"{name}_emit3_3500_seq{k}_spec2"])
+            assert best[k] == out[k].min() and arg[k] == out[k].argmin()
+        with pytest.raises(_lib.SvError):  # the table path refuses an incomplete table
+            sp.set_run_mode(_lib.SPEC_RUN_TABLE)
+            sp.run_batch(syms, offs)
+
+
+def test_implicit_run_equals_table_run(api, oracle, load_model, load_seqs):
+    """K4i against table + K4 (pinned to the oracle above) and the oracle itself: ragged lengths
+    (1..7 cover init-only, tail-only and odd/even chunking), random sparse models with +inf weights,
+    a model with 3 dense rows, the largest profile HMM on the ragged covid set."""
+    from spec_viterbi_b200 import generators, _lib
+    rng = np.random.default_rng(11)
+    dense3 = generators.random_hmm(states_num=90, trans_per_state=3, seed=12)
+    extra_dst = np.repeat(np.array([4, 17, 60], np.uint64), 90)       # three states reachable from everywhere
+    extra_src = np.tile(np.arange(90, dtype=np.uint64), 3)
+    keep = ~np.isin(dense3.trans_rows * 1000 + dense3.trans_cols, extra_src * 1000 + extra_dst)
+    cases = [(generators.random_hmm(states_num=130, seed=9), True),
+             (generators.random_hmm(states_num=700, trans_per_state=5, seed=5), True),
+             (api.HMM(90, 20, int(keep.sum()) + 270,
+                      np.concatenate([dense3.trans_rows[keep], extra_src]),
+                      np.concatenate([dense3.trans_cols[keep], extra_dst]),
+                      np.concatenate([dense3.trans_probs[keep], rng.uniform(0.1, 6, 270).astype(np.float32)]),
+                      dense3.emissions, dense3.non_zero_start_probs, dense3.start_probabilities_cols,
+                      dense3.start_probabilities), True)]
+    for hmm, use_oracle in cases:
+        m = api.Model(hmm)
+        seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 50, 301, 1000)]
+        syms, offs = api.pack_sequences(seqs)
+        table = api.Spec(m, 2)
+        exp, ebest, earg = table.run_batch(syms, offs)
+        table.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+        got, best, arg = table.run_batch(syms, offs)
+        assert same_bits(got, exp)
+        assert np.array_equal(best, ebest) and np.array_equal(arg, earg)
+        if use_oracle:
+            osp = oracle.spec(hmm, 2)
+            for k in (0, 1, 2, 6, 8):
+                assert same_bits(got[k], osp.run(seqs[k])), k
+    hmm = load_model("2405")
+    m = api.Model(hmm)
+    syms, offs = api.pack_sequences(load_seqs("covid-19"))
+    table = api.Spec(m, 2)
+    exp, _, _ = table.run_batch(syms, offs)
+    table.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+    got, _, _ = table.run_batch(syms, offs)
+    assert same_bits(got, exp)
+
+
+def test_implicit_run_unsupported(api):
+    """More dense rows than K4i stages (or level != 2): SV_ERR_UNSUPPORTED, mode unchanged."""
+    from spec_viterbi_b200 import generators, _lib
+    m = api.Model(generators.random_hmm(states_num=60, trans_per_state=40, seed=7))  # every row heavy
+    sp = api.Spec(m, 2)
+    with pytest.raises(_lib.SvError):
+        sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+    s = np.arange(9, dtype=np.uint64) % 20
+    assert sp.run(s).shape == (60,)

@@ -58,6 +58,23 @@ def main():
             res["run_handler_read_GBs"] = chunks * n * n * 4 / 1e9 / (min(rt) * 1e-3)
             res["run_frac_of_hbm"] = res["run_handler_read_GBs"] / peaks["hbm_gbs"]
             res["run_state_updates_per_s"] = sum(len(s) for s in seqs) * n / (min(rt) * 1e-3)
+            # K4i: the same chunks recomputed from the sparse factors (no table reads), bit-identical
+            sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+            it = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                iout, ibest, iarg = sp.run_batch(syms, offs)
+                it.append((time.perf_counter() - t0) * 1e3)
+            sp.set_run_mode(_lib.SPEC_RUN_TABLE)
+            res["run_ms_level2_implicit"] = min(it)
+            res["implicit_bits_equal_table_run"] = bool(np.array_equal(iout.view(np.uint32), out.view(np.uint32)))
+            res["implicit_launches"] = m.last_launches()
+            # two-step paths of the model = terms K4i evaluates per (sequence, chunk): 2 FADD + 1 FMNMX each
+            indeg = np.bincount(np.asarray(hmm.trans_cols, np.int64), minlength=n)  # in-degree of each destination
+            paths = int(indeg[np.asarray(hmm.trans_rows, np.int64)].sum())        # sum over edges (j->i) of indeg(j)
+            res["implicit_terms_per_chunk"] = paths
+            res["implicit_terms_per_s"] = paths * chunks / (min(it) * 1e-3)
+            res["implicit_frac_of_fp32_issue"] = res["implicit_terms_per_s"] * 2.5 / (148 * 128 * 1.965e9)
             # plain path on the same input for the honest comparison
             pt = []
             for _ in range(3):
