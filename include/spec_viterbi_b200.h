@@ -179,7 +179,11 @@ int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out);
  * (K4i) -- same sums, same association, same bits, no table traffic; the table may then be empty
  * (sv_spec_create with tuple_begin == tuple_end == emits^level).  Level 2, models with at most 4
  * dense rows; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.  Level 1 ignores the mode. */
-enum { SV_SPEC_RUN_TABLE = 0, SV_SPEC_RUN_IMPLICIT = 1 };
+enum {
+    SV_SPEC_RUN_TABLE = 0,
+    SV_SPEC_RUN_IMPLICIT = 1,     /* K4p: one persistent launch, a thread-block cluster per sequence */
+    SV_SPEC_RUN_IMPLICIT_STEP = 2 /* K4i: one launch per chunk (also the fallback for > 8192 states) */
+};
 int sv_spec_set_run_mode(sv_spec* s, int mode);
 
 int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out);

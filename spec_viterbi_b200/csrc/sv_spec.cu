@@ -11,6 +11,8 @@
 // Level 1 needs no tables: the plain kernels form fl(E + T') on the fly with identical bits.
 #include "sv_internal.h"
 
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -40,6 +42,8 @@ struct sv_spec {
     cudaStream_t aux[kRunStreams - 1] = {nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join[kRunStreams - 1] = {nullptr, nullptr, nullptr};
 };
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -717,21 +721,123 @@ handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
 constexpr int kImplicitMaxHeavy = 4;
 constexpr int kImplicitThreads = 128;
 
-__device__ __forceinline__ float heavy_stream(float u, const float4* __restrict__ r4,
-                                              const float4* __restrict__ v4, int n4, int k0, int kstep) {
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v; // volatile: never hoisted over the barriers that publish v and r_h
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+#define SV_HEAVY_TERMS(r, v)               \
+    b0 = fminf(b0, (u + (r).x) + (v).x);   \
+    b1 = fminf(b1, (u + (r).y) + (v).y);   \
+    b2 = fminf(b2, (u + (r).z) + (v).z);   \
+    b3 = fminf(b3, (u + (r).w) + (v).w);
+
+// min_k fl(fl(u + r[k]) + v[k]) over all npad columns (npad is a multiple of 16, +inf padded): 16 terms per
+// trip = 8 broadcast LDS.128 with immediate offsets, 32 FADD, 8 FMNMX3 and two pointer bumps.
+__device__ __forceinline__ float heavy_stream_all(float u, uint32_t r_addr, uint32_t v_addr, int npad) {
     float b0 = pos_inf(), b1 = pos_inf(), b2 = pos_inf(), b3 = pos_inf();
-#pragma unroll 2
-    for (int k = k0; k < n4; k += kstep) {
-        const float4 r = r4[k];
-        const float4 v = v4[k];
-        b0 = fminf(b0, (u + r.x) + v.x);
-        b1 = fminf(b1, (u + r.y) + v.y);
-        b2 = fminf(b2, (u + r.z) + v.z);
-        b3 = fminf(b3, (u + r.w) + v.w);
+    const uint32_t r_end = r_addr + static_cast<uint32_t>(npad) * 4u;
+#pragma unroll 1
+    for (; r_addr != r_end; r_addr += 64, v_addr += 64) {
+        const float4 r0 = lds128(r_addr), v0 = lds128(v_addr);
+        const float4 r1 = lds128(r_addr + 16), v1 = lds128(v_addr + 16);
+        const float4 r2 = lds128(r_addr + 32), v2 = lds128(v_addr + 32);
+        const float4 r3 = lds128(r_addr + 48), v3 = lds128(v_addr + 48);
+        SV_HEAVY_TERMS(r0, v0)
+        SV_HEAVY_TERMS(r1, v1)
+        SV_HEAVY_TERMS(r2, v2)
+        SV_HEAVY_TERMS(r3, v3)
     }
     return fminf(fminf(b0, b1), fminf(b2, b3));
 }
 
+// the same columns dealt to the threads of a CTA (heavy rows): thread k0 of kstep takes every kstep-th float4
+__device__ __forceinline__ float heavy_stream(float u, const float4* __restrict__ r4,
+                                              const float4* __restrict__ v4, int n4, int k0, int kstep) {
+    float b0 = pos_inf(), b1 = pos_inf(), b2 = pos_inf(), b3 = pos_inf();
+    for (int k = k0; k < n4; k += kstep) {
+        const float4 r = r4[k];
+        const float4 v = v4[k];
+        SV_HEAVY_TERMS(r, v)
+    }
+    return fminf(fminf(b0, b1), fminf(b2, b3));
+}
+
+// One light row i: returns min over its two-step paths (see above).  Must be called by whole warps
+// (`live` = this lane owns a light row): the heavy streams are entered on a warp vote.
+__device__ __forceinline__ float implicit_light_row(const SvPairDev& pd, const float* __restrict__ ea,
+                                                    const float* __restrict__ eb, int i, bool live,
+                                                    const float* __restrict__ sv, const float* __restrict__ sr,
+                                                    int npad) {
+    float uh[kImplicitMaxHeavy];
+#pragma unroll
+    for (int h = 0; h < kImplicitMaxHeavy; ++h) uh[h] = pos_inf();
+    float best = pos_inf();
+    if (live) {
+        const float e = eb[i];
+        for (uint32_t p = pd.rowptr[i]; p < pd.rowptr[i + 1]; ++p) {
+            const uint32_t j = pd.col[p];
+            const float u = e + pd.w[p];
+            const int hj = pd.hidx[j];
+            if (hj >= 0) {
+#pragma unroll
+                for (int h = 0; h < kImplicitMaxHeavy; ++h)
+                    if (hj == h) uh[h] = u;
+            } else {
+                const float ej = ea[j];
+                for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
+                    best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
+            }
+        }
+    }
+    const uint32_t sv_addr = static_cast<uint32_t>(__cvta_generic_to_shared(sv));
+    const uint32_t sr_addr = static_cast<uint32_t>(__cvta_generic_to_shared(sr));
+#pragma unroll
+    for (int h = 0; h < kImplicitMaxHeavy; ++h) {
+        if (h < pd.n_heavy && __any_sync(0xffffffffu, uh[h] < pos_inf()))
+            best = fminf(best, heavy_stream_all(uh[h], sr_addr + static_cast<uint32_t>(h * npad) * 4u, sv_addr, npad));
+    }
+    return best;
+}
+
+// Heavy row number hme, spread over the `nthr` threads of the CTA: returns this thread's partial minimum.
+__device__ __forceinline__ float implicit_heavy_row(const SvPairDev& pd, const float* __restrict__ ea,
+                                                    const float* __restrict__ eb, int hme,
+                                                    const float* __restrict__ sv, const float* __restrict__ sr,
+                                                    int npad, int tid, int nthr) {
+    const int n = pd.n;
+    const int i = static_cast<int>(pd.hrow[hme]);
+    const float e = eb[i];
+    float best = pos_inf();
+    for (uint32_t p = pd.rowptr[i] + tid; p < pd.rowptr[i + 1]; p += nthr) {
+        const uint32_t j = pd.col[p];
+        if (pd.hidx[j] >= 0) continue; // heavy sources are streamed below
+        const float u = e + pd.w[p];
+        const float ej = ea[j];
+        for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
+            best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
+    }
+    const float4* __restrict__ v4 = reinterpret_cast<const float4*>(sv);
+    for (int h = 0; h < pd.n_heavy; ++h) {
+        const float w = pd.wd[static_cast<size_t>(hme) * n + pd.hrow[h]]; // T'[i][hrow[h]], +inf = absent
+        if (w < pos_inf())
+            best = fminf(best, heavy_stream(e + w, reinterpret_cast<const float4*>(sr + h * npad), v4, npad >> 2, tid, nthr));
+    }
+    return best;
+}
+
+// r_h[k] = fl(E[a][hrow[h]] + T'[hrow[h]][k]) for the dense rows, +inf padded
+__device__ __forceinline__ void implicit_stage_heavy(const SvPairDev& pd, const float* __restrict__ ea,
+                                                     float* __restrict__ sr, int npad, int tid, int nthr) {
+    for (int h = 0; h < pd.n_heavy; ++h) {
+        const float e = ea[pd.hrow[h]];
+        const float* __restrict__ wrow = pd.wd + static_cast<size_t>(h) * pd.n;
+        for (int k = tid; k < npad; k += nthr) sr[h * npad + k] = k < pd.n ? e + wrow[k] : pos_inf();
+    }
+}
+
+// per-chunk launch: grid x = row tile (then one CTA per heavy row), y = sequence
 __global__ void __launch_bounds__(kImplicitThreads)
 implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* __restrict__ vin,
                           float* __restrict__ vout, int seq_base, int ntiles, int npad) {
@@ -760,74 +866,96 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
     const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
     for (int k = threadIdx.x; k < npad; k += kImplicitThreads) sv[k] = k < n ? vi[k] : pos_inf();
-    for (int h = 0; h < pd.n_heavy; ++h) {
-        const float e = ea[pd.hrow[h]];
-        const float* __restrict__ wrow = pd.wd + static_cast<size_t>(h) * n;
-        for (int k = threadIdx.x; k < npad; k += kImplicitThreads)
-            sr[h * npad + k] = k < n ? e + wrow[k] : pos_inf();
-    }
+    implicit_stage_heavy(pd, ea, sr, npad, threadIdx.x, kImplicitThreads);
     __syncthreads();
-    const float4* __restrict__ v4 = reinterpret_cast<const float4*>(sv);
-    const int n4 = npad >> 2;
     if (!heavy_cta) {
         const int i = blockIdx.x * kImplicitThreads + threadIdx.x;
         const bool live = i < n && pd.hidx[i] < 0;
-        float uh[kImplicitMaxHeavy];
-#pragma unroll
-        for (int h = 0; h < kImplicitMaxHeavy; ++h) uh[h] = pos_inf();
-        float best = pos_inf();
-        if (live) {
-            const float e = eb[i];
-            for (uint32_t p = pd.rowptr[i]; p < pd.rowptr[i + 1]; ++p) {
-                const uint32_t j = pd.col[p];
-                const float u = e + pd.w[p];
-                const int hj = pd.hidx[j];
-                if (hj >= 0) {
-#pragma unroll
-                    for (int h = 0; h < kImplicitMaxHeavy; ++h)
-                        if (hj == h) uh[h] = u;
-                } else {
-                    const float ej = ea[j];
-                    for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
-                        best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
-                }
-            }
-        }
-#pragma unroll
-        for (int h = 0; h < kImplicitMaxHeavy; ++h) {
-            if (h < pd.n_heavy && __any_sync(0xffffffffu, uh[h] < pos_inf()))
-                best = fminf(best, heavy_stream(uh[h], reinterpret_cast<const float4*>(sr + h * npad), v4, n4, 0, 1));
-        }
+        const float best = implicit_light_row(pd, ea, eb, i, live, sv, sr, npad);
         if (live) vo[i] = best;
         return;
     }
-    // heavy row: the CTA strides over its entries; heavy sources are streamed by all threads
-    const int i = static_cast<int>(pd.hrow[hme]);
-    const float e = eb[i];
-    float best = pos_inf();
-    for (uint32_t p = pd.rowptr[i] + threadIdx.x; p < pd.rowptr[i + 1]; p += kImplicitThreads) {
-        const uint32_t j = pd.col[p];
-        if (pd.hidx[j] >= 0) continue;
-        const float u = e + pd.w[p];
-        const float ej = ea[j];
-        for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
-            best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
-    }
-    for (int h = 0; h < pd.n_heavy; ++h) {
-        const float w = pd.wd[static_cast<size_t>(hme) * n + pd.hrow[h]]; // T'[i][hrow[h]], +inf = absent
-        if (w < pos_inf())
-            best = fminf(best, heavy_stream(e + w, reinterpret_cast<const float4*>(sr + h * npad), v4, n4,
-                                            threadIdx.x, kImplicitThreads));
-    }
-    best = warp_min(best);
+    float best = warp_min(implicit_heavy_row(pd, ea, eb, hme, sv, sr, npad, threadIdx.x, kImplicitThreads));
     if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
     __syncthreads();
     if (threadIdx.x == 0) {
         float r = s_red[0];
 #pragma unroll
         for (int wv = 1; wv < kImplicitThreads / 32; ++wv) r = fminf(r, s_red[wv]);
-        vo[i] = r;
+        vo[pd.hrow[hme]] = r;
     }
+}
+
+// K4p: the same, persistent: a cluster of kClusterCtas CTAs owns one sequence for ALL its chunks (one launch,
+// no per-chunk kernel boundary).  Every CTA keeps the whole score vector double buffered in shared memory,
+// computes rows [rank * rows_per_cta, ...) and pushes them into the next buffer of all CTAs of the cluster
+// through distributed shared memory; one cluster barrier per chunk.  Independent sequences share an SM, so
+// the barrier and set-up latencies of one overlap the streaming loops of the others.
+constexpr int kClusterCtas = 8;
+
+template <int MAXT>
+__global__ void __cluster_dims__(kClusterCtas, 1, 1) __launch_bounds__(MAXT)
+implicit_pair_persistent_kernel(SvPairDev pd, RunSeqs s, const float* __restrict__ vin,
+                                float* __restrict__ vout, int npad, int rows_per_cta) {
+    extern __shared__ float4 sm4[];
+    float* vb = reinterpret_cast<float*>(sm4); // [2][npad] v, +inf padded
+    float* sr = vb + 2 * npad;                 // [n_heavy][npad] r_h
+    __shared__ float s_red[32];
+    __shared__ float s_part[2][kImplicitMaxHeavy][kClusterCtas]; // [buffer][dense row][rank] partial minima
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = static_cast<int>(cluster.block_rank());
+    const int n = pd.n;
+    const int q = blockIdx.x / kClusterCtas;
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const uint64_t o0 = s.off[q];
+    const uint64_t nchunks = (s.off[q + 1] - o0 - 1) / 2;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
+    for (int k = tid; k < npad; k += nthr) {
+        vb[k] = k < n ? vi[k] : pos_inf();
+        vb[npad + k] = pos_inf();
+    }
+    cluster.sync(); // every buffer of the cluster is initialised before anybody pushes into it
+    const int i = rank * rows_per_cta + tid;
+    const bool mine = tid < rows_per_cta && i < n;
+    const bool live = mine && pd.hidx[i] < 0;
+    int cur = 0;
+    for (uint64_t c = 0; c < nchunks; ++c) {
+        const unsigned a = load_sym(s, o0 + 1 + c * 2), b = load_sym(s, o0 + 2 + c * 2);
+        const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
+        const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
+        const float* __restrict__ sv = vb + cur * npad;
+        const int nxt = (cur ^ 1) * npad;
+        implicit_stage_heavy(pd, ea, sr, npad, tid, nthr);
+        __syncthreads();
+        const float best = implicit_light_row(pd, ea, eb, i, live, sv, sr, npad);
+        if (live) {
+#pragma unroll
+            for (int r = 0; r < kClusterCtas; ++r) cluster.map_shared_rank(vb, r)[nxt + i] = best;
+        }
+        // dense rows: their entries are dealt to ALL threads of the cluster (a chain of dependent loads per
+        // entry: the fewer per thread the better); the 8 partial minima meet in every CTA's s_part
+        for (int h = 0; h < pd.n_heavy; ++h) {
+            float hb = warp_min(implicit_heavy_row(pd, ea, eb, h, sv, sr, npad, rank * nthr + tid, kClusterCtas * nthr));
+            __syncthreads(); // s_red free
+            if ((tid & 31) == 0) s_red[tid >> 5] = hb;
+            __syncthreads();
+            if (tid < kClusterCtas) {
+                hb = s_red[0];
+                for (int wv = 1; wv < (nthr >> 5); ++wv) hb = fminf(hb, s_red[wv]);
+                cluster.map_shared_rank(&s_part[0][0][0], tid)[((cur ^ 1) * kImplicitMaxHeavy + h) * kClusterCtas + rank] = hb;
+            }
+        }
+        cluster.sync(); // pushes visible, reads of v and r_h done
+        cur ^= 1;
+        if (tid < pd.n_heavy) {
+            float hb = s_part[cur][tid][0];
+#pragma unroll
+            for (int r = 1; r < kClusterCtas; ++r) hb = fminf(hb, s_part[cur][tid][r]);
+            vb[cur * npad + pd.hrow[tid]] = hb; // published by the __syncthreads of the next chunk / the one below
+        }
+    }
+    __syncthreads();
+    if (mine) vout[static_cast<size_t>(q) * n + i] = vb[cur * npad + i];
 }
 
 // Level-1 tail step number `tail` (0-based) of every sequence that still has one
@@ -1418,7 +1546,7 @@ extern "C" int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_sp
 
 namespace {
 size_t implicit_smem(const SvPairDev& pd) {
-    return static_cast<size_t>(1 + pd.n_heavy) * ((pd.n + 3) / 4 * 4) * sizeof(float);
+    return static_cast<size_t>(1 + pd.n_heavy) * ((pd.n + 15) / 16 * 16) * sizeof(float);
 }
 
 // K4i applies to level 2 of models with at most kImplicitMaxHeavy dense rows whose staged copies fit
@@ -1433,9 +1561,9 @@ bool implicit_supported(sv_spec* s, SvPairDev* pd) {
 } // namespace
 
 extern "C" int sv_spec_set_run_mode(sv_spec* s, int mode) {
-    if (s == nullptr || (mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT))
+    if (s == nullptr || (mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT && mode != SV_SPEC_RUN_IMPLICIT_STEP))
         return sv_fail(SV_ERR_ARG, "sv_spec_set_run_mode: bad argument");
-    if (mode == SV_SPEC_RUN_IMPLICIT && s->level > 1) {
+    if (mode != SV_SPEC_RUN_TABLE && s->level > 1) {
         SV_CUDA(cudaSetDevice(s->m->device));
         SvPairDev pd;
         if (!implicit_supported(s, &pd)) {
@@ -1454,7 +1582,7 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     if (s->level == 1) return sv_viterbi_device(m, seqs, d_out, d_best, d_best_state, stream);
     if (seqs->device != m->device)
         return sv_fail(SV_ERR_ARG, "sv_spec_run_device: sequences live on another device");
-    const bool implicit = s->run_mode == SV_SPEC_RUN_IMPLICIT;
+    const bool implicit = s->run_mode != SV_SPEC_RUN_TABLE;
     if (!implicit && (s->t_begin != 0 || s->t_end != s->ntuples))
         return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1480,7 +1608,24 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         spec_init_kernel<<<grid, 256, 0, st>>>(m->gen, rs, s->d_v[cur]);
         ++launches;
     }
-    const uint64_t max_chunks = (seqs->max_len - 1) / s->level;
+    uint64_t max_chunks = (seqs->max_len - 1) / s->level;
+    if (implicit && s->run_mode == SV_SPEC_RUN_IMPLICIT && max_chunks > 0) {
+        // K4p: one persistent launch, a cluster per sequence walks all its chunks
+        const int rows = static_cast<int>((n + kClusterCtas - 1) / kClusterCtas);
+        const int threads = std::max(64, (rows + 31) / 32 * 32);
+        const int npad = static_cast<int>((n + 15) / 16 * 16);
+        const size_t smem = implicit_smem(pd) + static_cast<size_t>(npad) * sizeof(float);
+        if (threads <= 1024 && smem <= 200 * 1024) {
+            auto kern = threads <= 512 ? implicit_pair_persistent_kernel<512> : implicit_pair_persistent_kernel<1024>;
+            SV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            kern<<<static_cast<unsigned>(nseq * kClusterCtas), threads, smem, st>>>(pd, rs, s->d_v[cur], s->d_v[cur ^ 1],
+                                                                                     npad, rows);
+            SV_CUDA(cudaGetLastError());
+            ++launches;
+            cur ^= 1;
+            max_chunks = 0; // the chunk loop below is done
+        }
+    }
     // rows per CTA: at least ~6 waves of resident CTAs (8 x 256 threads per SM), so that the last,
     // partial wave costs a few percent instead of the ~20 % it cost with 64 rows at 50 sequences
     int rows_per_cta = 64;
@@ -1506,7 +1651,7 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
             const uint64_t q0 = nseq * g / ngroups, q1 = nseq * (g + 1) / ngroups;
             if (implicit) {
                 const int ntiles = static_cast<int>((n + kImplicitThreads - 1) / kImplicitThreads);
-                const int npad = static_cast<int>((n + 3) / 4 * 4);
+                const int npad = static_cast<int>((n + 15) / 16 * 16);
                 dim3 igrid(static_cast<unsigned>(ntiles + pd.n_heavy), static_cast<unsigned>(q1 - q0));
                 implicit_pair_step_kernel<<<igrid, kImplicitThreads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
                     pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles, npad);

@@ -148,8 +148,17 @@ def test_handler_table_save_load(api, oracle, tmp_path):
         api.Spec(m, 1).save(tmp_path / "l1")
 
 
-def test_implicit_run_reference_fixture(api, load_model, load_seqs, golden):
-    """K4i (level-2 chunks recomputed from the sparse factors, no table) gives the reference's bits:
+IMPLICIT_MODES = ["persistent", "step"]
+
+
+def _implicit(mode):
+    from spec_viterbi_b200 import _lib
+    return {"persistent": _lib.SPEC_RUN_IMPLICIT, "step": _lib.SPEC_RUN_IMPLICIT_STEP}[mode]
+
+
+@pytest.mark.parametrize("mode", IMPLICIT_MODES)
+def test_implicit_run_reference_fixture(mode, api, load_model, load_seqs, golden):
+    """K4p / K4i (level-2 chunks recomputed from the sparse factors, no table) gives the reference's bits:
     profile HMMs (two dense rows, one dense column) against the fixtures generated from
     GraphBLAS_spec_impl (level 2), with an EMPTY handler table."""
     from spec_viterbi_b200 import _lib
@@ -157,7 +166,7 @@ def test_implicit_run_reference_fixture(api, load_model, load_seqs, golden):
         hmm = load_model(name)
         m = api.Model(hmm)
         sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)  # nothing precomputed
-        sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+        sp.set_run_mode(_implicit(mode))
         syms, offs = api.pack_sequences(load_seqs("emit_3_3500_20"))
         out, best, arg = sp.run_batch(syms, offs)
         for k in range(3):
@@ -168,7 +177,8 @@ def test_implicit_run_reference_fixture(api, load_model, load_seqs, golden):
             sp.run_batch(syms, offs)
 
 
-def test_implicit_run_equals_table_run(api, oracle, load_model, load_seqs):
+@pytest.mark.parametrize("mode", IMPLICIT_MODES)
+def test_implicit_run_equals_table_run(mode, api, oracle, load_model, load_seqs):
     """K4i against table + K4 (pinned to the oracle above) and the oracle itself: ragged lengths
     (1..7 cover init-only, tail-only and odd/even chunking), random sparse models with +inf weights,
     a model with 3 dense rows, the largest profile HMM on the ragged covid set."""
@@ -192,7 +202,7 @@ def test_implicit_run_equals_table_run(api, oracle, load_model, load_seqs):
         syms, offs = api.pack_sequences(seqs)
         table = api.Spec(m, 2)
         exp, ebest, earg = table.run_batch(syms, offs)
-        table.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+        table.set_run_mode(_implicit(mode))
         got, best, arg = table.run_batch(syms, offs)
         assert same_bits(got, exp)
         assert np.array_equal(best, ebest) and np.array_equal(arg, earg)
@@ -205,7 +215,7 @@ def test_implicit_run_equals_table_run(api, oracle, load_model, load_seqs):
     syms, offs = api.pack_sequences(load_seqs("covid-19"))
     table = api.Spec(m, 2)
     exp, _, _ = table.run_batch(syms, offs)
-    table.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+    table.set_run_mode(_implicit(mode))
     got, _, _ = table.run_batch(syms, offs)
     assert same_bits(got, exp)
 
