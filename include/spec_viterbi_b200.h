@@ -181,8 +181,9 @@ int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out);
  * dense rows; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.  Level 1 ignores the mode. */
 enum {
     SV_SPEC_RUN_TABLE = 0,
-    SV_SPEC_RUN_IMPLICIT = 1,     /* K4p: one persistent launch, a thread-block cluster per sequence */
-    SV_SPEC_RUN_IMPLICIT_STEP = 2 /* K4i: one launch per chunk (also the fallback for > 8192 states) */
+    SV_SPEC_RUN_IMPLICIT = 1,        /* K4i: one launch per chunk and sequence group */
+    SV_SPEC_RUN_IMPLICIT_CLUSTER = 2 /* K4p: one persistent launch, a thread-block cluster of 8 CTAs per sequence
+                                        (experimental: measured slower than K4i; K4i beyond 8192 states) */
 };
 int sv_spec_set_run_mode(sv_spec* s, int mode);
 

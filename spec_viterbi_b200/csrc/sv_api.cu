@@ -330,6 +330,7 @@ extern "C" void sv_model_destroy(sv_model* m) {
     if (m->d_es1_blob) cudaFree(m->d_es1_blob);
     if (m->d_ls_blob) cudaFree(m->d_ls_blob);
     if (m->d_pair_blob) cudaFree(m->d_pair_blob);
+    if (m->d_path_blob) cudaFree(m->d_path_blob);
     if (m->d_counter) cudaFree(m->d_counter);
     if (m->ws.seqs) sv_seqs_destroy(m->ws.seqs);
     if (m->ws.d_out) cudaFree(m->ws.d_out);

@@ -211,6 +211,9 @@ struct sv_model {
     void* d_ls_blob = nullptr;
     // level-2 pair precompute (sv_spec.cu): dense copies of the heavy rows + CSC, built on first use
     void* d_pair_blob = nullptr;
+    void* d_path_blob = nullptr; // K4i/K4p: flattened two-step paths (sv_spec.cu: path_prepare)
+    int path_state = 0;          // 0 = not built, 1 = ready, -1 = not eligible
+    int path_slots = 0, path_heavy_total = 0;
     int pair_state = 0; // 0 = not built, 1 = ready, -1 = model not eligible (too many heavy rows)
     int kernel_pref = SV_KERNEL_AUTO;
     int last_launches = 0;

@@ -216,6 +216,14 @@ struct SvPairDev {
     const uint32_t* longcol = nullptr; // columns with more than kPairLongCol entries
     const uint32_t* hrow = nullptr;    // [heavy] row of each dense copy
     int n_heavy = 0;
+    // K4i/K4p only (path_prepare): two-step paths i <- j <- k through LIGHT j, flattened so that a thread
+    // meets no chain of dependent loads: {T'[i][j], T'[j][k], j, k}
+    const uint4* lpath = nullptr;     // [path_slots][n] paths of light row i (slot-major: coalesced)
+    const uint32_t* lcount = nullptr; // [n] paths of row i (0 for dense rows)
+    const float* wcol = nullptr;      // [heavy][n] T'[i][hrow[h]], +inf where absent (dense column copies)
+    const uint4* hpath = nullptr;     // paths of the dense rows, concatenated
+    const uint32_t* hpath_ptr = nullptr; // [heavy + 1]
+    int path_slots = 0;
     int stage_row = 0; // light pass: (n + 8) floats of dynamic shared memory hold the row's first dense source
 };
 
@@ -733,23 +741,35 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     b2 = fminf(b2, (u + (r).z) + (v).z);   \
     b3 = fminf(b3, (u + (r).w) + (v).w);
 
-// min_k fl(fl(u + r[k]) + v[k]) over all npad columns (npad is a multiple of 16, +inf padded): 16 terms per
-// trip = 8 broadcast LDS.128 with immediate offsets, 32 FADD, 8 FMNMX3 and two pointer bumps.
-__device__ __forceinline__ float heavy_stream_all(float u, uint32_t r_addr, uint32_t v_addr, int npad) {
-    float b0 = pos_inf(), b1 = pos_inf(), b2 = pos_inf(), b3 = pos_inf();
+// best[x] = min(best[x], min_k fl(fl(u[x] + r[k]) + v[k])) over all npad columns (npad is a multiple of 16, +inf
+// padded) for R rows at once: a broadcast LDS costs shared-memory wavefronts like any other, so every loaded
+// (r, v) quad is used for R rows.  16 columns per trip = 8 LDS.128 with immediate offsets, 32 R FADD, 8 R FMNMX3.
+template <int R>
+__device__ __forceinline__ void heavy_stream_all(const float (&u)[R], uint32_t r_addr, uint32_t v_addr, int npad,
+                                                 float (&best)[R]) {
+    float b0[R], b1[R];
+#pragma unroll
+    for (int x = 0; x < R; ++x) b0[x] = b1[x] = pos_inf();
     const uint32_t r_end = r_addr + static_cast<uint32_t>(npad) * 4u;
 #pragma unroll 1
     for (; r_addr != r_end; r_addr += 64, v_addr += 64) {
-        const float4 r0 = lds128(r_addr), v0 = lds128(v_addr);
-        const float4 r1 = lds128(r_addr + 16), v1 = lds128(v_addr + 16);
-        const float4 r2 = lds128(r_addr + 32), v2 = lds128(v_addr + 32);
-        const float4 r3 = lds128(r_addr + 48), v3 = lds128(v_addr + 48);
-        SV_HEAVY_TERMS(r0, v0)
-        SV_HEAVY_TERMS(r1, v1)
-        SV_HEAVY_TERMS(r2, v2)
-        SV_HEAVY_TERMS(r3, v3)
+        float4 r[4], v[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            r[g] = lds128(r_addr + 16 * g);
+            v[g] = lds128(v_addr + 16 * g);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+#pragma unroll
+            for (int x = 0; x < R; ++x) {
+                b0[x] = fminf(fminf(b0[x], (u[x] + r[g].x) + v[g].x), (u[x] + r[g].y) + v[g].y);
+                b1[x] = fminf(fminf(b1[x], (u[x] + r[g].z) + v[g].z), (u[x] + r[g].w) + v[g].w);
+            }
+        }
     }
-    return fminf(fminf(b0, b1), fminf(b2, b3));
+#pragma unroll
+    for (int x = 0; x < R; ++x) best[x] = fminf(best[x], fminf(b0[x], b1[x]));
 }
 
 // the same columns dealt to the threads of a CTA (heavy rows): thread k0 of kstep takes every kstep-th float4
@@ -766,58 +786,68 @@ __device__ __forceinline__ float heavy_stream(float u, const float4* __restrict_
 
 // One light row i: returns min over its two-step paths (see above).  Must be called by whole warps
 // (`live` = this lane owns a light row): the heavy streams are entered on a warp vote.
-__device__ __forceinline__ float implicit_light_row(const SvPairDev& pd, const float* __restrict__ ea,
-                                                    const float* __restrict__ eb, int i, bool live,
+__device__ __forceinline__ float path_term(const uint4 t, float e, const float* __restrict__ ea,
+                                           const float* __restrict__ sv) {
+    return ((e + __uint_as_float(t.x)) + (ea[t.z] + __uint_as_float(t.y))) + sv[t.w];
+}
+
+// R light rows per thread (rows i0 + x * stride, x < R; `live` = bit x set when the lane owns that row).
+// Must be called by whole warps: the heavy streams are entered on a warp vote.
+template <int R>
+__device__ __forceinline__ void implicit_light_rows(const SvPairDev& pd, const float* __restrict__ ea,
+                                                    const float* __restrict__ eb, int i0, int stride, unsigned live,
                                                     const float* __restrict__ sv, const float* __restrict__ sr,
-                                                    int npad) {
-    float uh[kImplicitMaxHeavy];
+                                                    int npad, float (&best)[R]) {
+    float uh[kImplicitMaxHeavy][R];
 #pragma unroll
-    for (int h = 0; h < kImplicitMaxHeavy; ++h) uh[h] = pos_inf();
-    float best = pos_inf();
-    if (live) {
+    for (int h = 0; h < kImplicitMaxHeavy; ++h)
+#pragma unroll
+        for (int x = 0; x < R; ++x) uh[h][x] = pos_inf();
+#pragma unroll
+    for (int x = 0; x < R; ++x) {
+        best[x] = pos_inf();
+        if (!((live >> x) & 1u)) continue;
+        const int i = i0 + x * stride;
         const float e = eb[i];
-        for (uint32_t p = pd.rowptr[i]; p < pd.rowptr[i + 1]; ++p) {
-            const uint32_t j = pd.col[p];
-            const float u = e + pd.w[p];
-            const int hj = pd.hidx[j];
-            if (hj >= 0) {
 #pragma unroll
-                for (int h = 0; h < kImplicitMaxHeavy; ++h)
-                    if (hj == h) uh[h] = u;
-            } else {
-                const float ej = ea[j];
-                for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
-                    best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
-            }
+        for (int h = 0; h < kImplicitMaxHeavy; ++h)
+            if (h < pd.n_heavy) uh[h][x] = e + pd.wcol[static_cast<size_t>(h) * pd.n + i];
+        const int cnt = static_cast<int>(pd.lcount[i]);
+        const uint4* __restrict__ lp = pd.lpath + i;
+        float bx = pos_inf();
+        int c = 0;
+        for (; c + 4 <= cnt; c += 4) { // independent loads, four in flight
+            const uint4 t0 = lp[static_cast<size_t>(c) * pd.n], t1 = lp[static_cast<size_t>(c + 1) * pd.n];
+            const uint4 t2 = lp[static_cast<size_t>(c + 2) * pd.n], t3 = lp[static_cast<size_t>(c + 3) * pd.n];
+            bx = fminf(fminf(bx, path_term(t0, e, ea, sv)), path_term(t1, e, ea, sv));
+            bx = fminf(fminf(bx, path_term(t2, e, ea, sv)), path_term(t3, e, ea, sv));
         }
+        for (; c < cnt; ++c) bx = fminf(bx, path_term(lp[static_cast<size_t>(c) * pd.n], e, ea, sv));
+        best[x] = bx;
     }
     const uint32_t sv_addr = static_cast<uint32_t>(__cvta_generic_to_shared(sv));
     const uint32_t sr_addr = static_cast<uint32_t>(__cvta_generic_to_shared(sr));
 #pragma unroll
     for (int h = 0; h < kImplicitMaxHeavy; ++h) {
-        if (h < pd.n_heavy && __any_sync(0xffffffffu, uh[h] < pos_inf()))
-            best = fminf(best, heavy_stream_all(uh[h], sr_addr + static_cast<uint32_t>(h * npad) * 4u, sv_addr, npad));
+        if (h >= pd.n_heavy) continue;
+        bool any = false;
+#pragma unroll
+        for (int x = 0; x < R; ++x) any = any || uh[h][x] < pos_inf();
+        if (__any_sync(0xffffffffu, any))
+            heavy_stream_all<R>(uh[h], sr_addr + static_cast<uint32_t>(h * npad) * 4u, sv_addr, npad, best);
     }
-    return best;
 }
 
-// Heavy row number hme, spread over the `nthr` threads of the CTA: returns this thread's partial minimum.
+// Heavy row number hme, spread over `nthr` threads (tid = this thread's place): returns its partial minimum.
 __device__ __forceinline__ float implicit_heavy_row(const SvPairDev& pd, const float* __restrict__ ea,
                                                     const float* __restrict__ eb, int hme,
                                                     const float* __restrict__ sv, const float* __restrict__ sr,
                                                     int npad, int tid, int nthr) {
     const int n = pd.n;
-    const int i = static_cast<int>(pd.hrow[hme]);
-    const float e = eb[i];
+    const float e = eb[pd.hrow[hme]];
     float best = pos_inf();
-    for (uint32_t p = pd.rowptr[i] + tid; p < pd.rowptr[i + 1]; p += nthr) {
-        const uint32_t j = pd.col[p];
-        if (pd.hidx[j] >= 0) continue; // heavy sources are streamed below
-        const float u = e + pd.w[p];
-        const float ej = ea[j];
-        for (uint32_t t = pd.rowptr[j]; t < pd.rowptr[j + 1]; ++t)
-            best = fminf(best, (u + (ej + pd.w[t])) + sv[pd.col[t]]);
-    }
+    const uint32_t p1 = pd.hpath_ptr[hme + 1];
+    for (uint32_t p = pd.hpath_ptr[hme] + tid; p < p1; p += nthr) best = fminf(best, path_term(pd.hpath[p], e, ea, sv));
     const float4* __restrict__ v4 = reinterpret_cast<const float4*>(sv);
     for (int h = 0; h < pd.n_heavy; ++h) {
         const float w = pd.wd[static_cast<size_t>(hme) * n + pd.hrow[h]]; // T'[i][hrow[h]], +inf = absent
@@ -838,6 +868,7 @@ __device__ __forceinline__ void implicit_stage_heavy(const SvPairDev& pd, const 
 }
 
 // per-chunk launch: grid x = row tile (then one CTA per heavy row), y = sequence
+template <int R>
 __global__ void __launch_bounds__(kImplicitThreads)
 implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* __restrict__ vin,
                           float* __restrict__ vout, int seq_base, int ntiles, int npad) {
@@ -857,8 +888,11 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
         if (heavy_cta) {
             if (threadIdx.x == 0) vo[pd.hrow[hme]] = vi[pd.hrow[hme]];
         } else {
-            const int i = blockIdx.x * kImplicitThreads + threadIdx.x;
-            if (i < n && pd.hidx[i] < 0) vo[i] = vi[i];
+#pragma unroll
+            for (int x = 0; x < R; ++x) {
+                const int i = (blockIdx.x * R + x) * kImplicitThreads + threadIdx.x;
+                if (i < n && pd.hidx[i] < 0) vo[i] = vi[i];
+            }
         }
         return;
     }
@@ -869,10 +903,18 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     implicit_stage_heavy(pd, ea, sr, npad, threadIdx.x, kImplicitThreads);
     __syncthreads();
     if (!heavy_cta) {
-        const int i = blockIdx.x * kImplicitThreads + threadIdx.x;
-        const bool live = i < n && pd.hidx[i] < 0;
-        const float best = implicit_light_row(pd, ea, eb, i, live, sv, sr, npad);
-        if (live) vo[i] = best;
+        const int i0 = blockIdx.x * R * kImplicitThreads + threadIdx.x;
+        unsigned live = 0;
+#pragma unroll
+        for (int x = 0; x < R; ++x) {
+            const int i = i0 + x * kImplicitThreads;
+            if (i < n && pd.hidx[i] < 0) live |= 1u << x;
+        }
+        float best[R];
+        implicit_light_rows<R>(pd, ea, eb, i0, kImplicitThreads, live, sv, sr, npad, best);
+#pragma unroll
+        for (int x = 0; x < R; ++x)
+            if ((live >> x) & 1u) vo[i0 + x * kImplicitThreads] = best[x];
         return;
     }
     float best = warp_min(implicit_heavy_row(pd, ea, eb, hme, sv, sr, npad, threadIdx.x, kImplicitThreads));
@@ -927,10 +969,11 @@ implicit_pair_persistent_kernel(SvPairDev pd, RunSeqs s, const float* __restrict
         const int nxt = (cur ^ 1) * npad;
         implicit_stage_heavy(pd, ea, sr, npad, tid, nthr);
         __syncthreads();
-        const float best = implicit_light_row(pd, ea, eb, i, live, sv, sr, npad);
+        float best[1];
+        implicit_light_rows<1>(pd, ea, eb, i, 0, live ? 1u : 0u, sv, sr, npad, best);
         if (live) {
 #pragma unroll
-            for (int r = 0; r < kClusterCtas; ++r) cluster.map_shared_rank(vb, r)[nxt + i] = best;
+            for (int r = 0; r < kClusterCtas; ++r) cluster.map_shared_rank(vb, r)[nxt + i] = best[0];
         }
         // dense rows: their entries are dealt to ALL threads of the cluster (a chain of dependent loads per
         // entry: the fewer per thread the better); the 8 partial minima meet in every CTA's s_part
@@ -1208,6 +1251,102 @@ bool pair_prepare(sv_model* m, SvPairDev* out) {
     out->longcol = reinterpret_cast<const uint32_t*>(base + o_long);
     out->hrow = reinterpret_cast<const uint32_t*>(base + o_hrow);
     out->n_heavy = static_cast<int>(heavy.size());
+    return true;
+}
+
+// K4i/K4p: flattens the two-step paths through light intermediate states (see SvPairDev).  Rows with more
+// than kPathMaxSlots such paths make the model ineligible (the table run is used).
+constexpr int kPathMaxSlots = 1024;
+
+bool path_prepare(sv_model* m, SvPairDev* pd) {
+    if (m->path_state < 0 || pd->n_heavy > kImplicitMaxHeavy) return false;
+    const size_t n = m->n;
+    const size_t nh = std::max<size_t>(static_cast<size_t>(pd->n_heavy), 1);
+    auto align = [](size_t x) { return (x + 255) / 256 * 256; };
+    if (m->path_state == 0) {
+        const auto& rp = m->csr.rowptr;
+        const auto& cl = m->csr.col;
+        const auto& cw = m->csr.w;
+        auto heavy = [&](size_t r) { return rp[r + 1] - rp[r] > static_cast<uint32_t>(kPairHeavy); };
+        std::vector<uint32_t> hrow;
+        for (size_t i = 0; i < n; ++i) if (heavy(i)) hrow.push_back(static_cast<uint32_t>(i));
+        std::vector<uint32_t> lcount(n, 0), hptr(nh + 1, 0);
+        size_t slots = 0;
+        for (size_t i = 0; i < n; ++i) {
+            size_t c = 0;
+            for (uint32_t p = rp[i]; p < rp[i + 1]; ++p)
+                if (!heavy(cl[p])) c += rp[cl[p] + 1] - rp[cl[p]];
+            if (heavy(i)) {
+                const size_t h = std::find(hrow.begin(), hrow.end(), static_cast<uint32_t>(i)) - hrow.begin();
+                hptr[h + 1] = static_cast<uint32_t>(c);
+            } else {
+                lcount[i] = static_cast<uint32_t>(c);
+                slots = std::max(slots, c);
+            }
+        }
+        if (slots > static_cast<size_t>(kPathMaxSlots)) {
+            m->path_state = -1;
+            return false;
+        }
+        for (size_t h = 0; h < nh; ++h) hptr[h + 1] += hptr[h];
+        const size_t htotal = hptr[nh];
+        struct P4 { float w1, w2; uint32_t j, k; };
+        std::vector<P4> lpath(std::max<size_t>(slots * n, 1), P4{0, 0, 0, 0}), hpath(std::max<size_t>(htotal, 1), P4{0, 0, 0, 0});
+        std::vector<float> wcol(nh * n, std::numeric_limits<float>::infinity());
+        for (size_t i = 0; i < n; ++i) {
+            size_t c = 0;
+            const size_t hi = heavy(i) ? std::find(hrow.begin(), hrow.end(), static_cast<uint32_t>(i)) - hrow.begin() : 0;
+            for (uint32_t p = rp[i]; p < rp[i + 1]; ++p) {
+                const uint32_t j = cl[p];
+                if (heavy(j)) {
+                    const size_t hj = std::find(hrow.begin(), hrow.end(), j) - hrow.begin();
+                    wcol[hj * n + i] = cw[p];
+                    continue;
+                }
+                for (uint32_t t = rp[j]; t < rp[j + 1]; ++t, ++c) {
+                    const P4 e{cw[p], cw[t], j, cl[t]};
+                    if (heavy(i)) hpath[hptr[hi] + c] = e; else lpath[c * n + i] = e;
+                }
+            }
+        }
+        const size_t o_lp = 0;
+        const size_t o_hp = align(o_lp + lpath.size() * 16);
+        const size_t o_lc = align(o_hp + hpath.size() * 16);
+        const size_t o_wc = align(o_lc + n * 4);
+        const size_t o_ptr = align(o_wc + wcol.size() * 4);
+        const size_t bytes = o_ptr + (nh + 1) * 4 + 256;
+        std::vector<unsigned char> host(bytes, 0);
+        std::memcpy(host.data() + o_lp, lpath.data(), lpath.size() * 16);
+        std::memcpy(host.data() + o_hp, hpath.data(), hpath.size() * 16);
+        std::memcpy(host.data() + o_lc, lcount.data(), n * 4);
+        std::memcpy(host.data() + o_wc, wcol.data(), wcol.size() * 4);
+        std::memcpy(host.data() + o_ptr, hptr.data(), (nh + 1) * 4);
+        if (cudaMalloc(&m->d_path_blob, bytes) != cudaSuccess ||
+            cudaMemcpy(m->d_path_blob, host.data(), bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+            cudaGetLastError();
+            if (m->d_path_blob) cudaFree(m->d_path_blob);
+            m->d_path_blob = nullptr;
+            m->path_state = -1;
+            return false;
+        }
+        m->path_state = 1;
+        m->path_slots = static_cast<int>(slots);
+        m->path_heavy_total = static_cast<int>(htotal);
+    }
+    const size_t lp_count = std::max<size_t>(static_cast<size_t>(m->path_slots) * n, 1);
+    const size_t hp_count = std::max<size_t>(static_cast<size_t>(m->path_heavy_total), 1);
+    const size_t o_lp = 0;
+    const size_t o_hp = align(o_lp + lp_count * 16);
+    const size_t o_lc = align(o_hp + hp_count * 16);
+    const size_t o_wc = align(o_lc + n * 4);
+    const size_t o_ptr = align(o_wc + nh * n * 4);
+    auto* base = static_cast<unsigned char*>(m->d_path_blob);
+    pd->lpath = reinterpret_cast<const uint4*>(base + o_lp);
+    pd->hpath = reinterpret_cast<const uint4*>(base + o_hp);
+    pd->lcount = reinterpret_cast<const uint32_t*>(base + o_lc);
+    pd->wcol = reinterpret_cast<const float*>(base + o_wc);
+    pd->hpath_ptr = reinterpret_cast<const uint32_t*>(base + o_ptr);
+    pd->path_slots = m->path_slots;
     return true;
 }
 
@@ -1545,6 +1684,22 @@ extern "C" int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_sp
 }
 
 namespace {
+// light rows per thread of K4i (register blocking of the heavy streams); SV_IMPLICIT_ROWS = 1 | 2 | 4
+int implicit_rows_per_thread() {
+    const char* e = std::getenv("SV_IMPLICIT_ROWS");
+    const int r = e ? std::atoi(e) : 1; // measured on config 3: 1 -> 76 ms, 2 -> 82 ms, 4 -> 77 ms (fewer, fatter CTAs)
+    return r == 2 || r == 4 ? r : 1;
+}
+
+// sequence groups (side streams) of K4i; SV_IMPLICIT_GROUPS = 1..4
+int implicit_groups() {
+    const char* e = std::getenv("SV_IMPLICIT_GROUPS");
+    // one grid of 21 x 50 CTAs is 14 CTAs more than one resident wave (7 per SM): 93 ms; four groups on
+    // four streams fill each other's tails: 76 ms
+    const int g = e ? std::atoi(e) : sv_spec::kRunStreams;
+    return g >= 1 && g <= sv_spec::kRunStreams ? g : sv_spec::kRunStreams;
+}
+
 size_t implicit_smem(const SvPairDev& pd) {
     return static_cast<size_t>(1 + pd.n_heavy) * ((pd.n + 15) / 16 * 16) * sizeof(float);
 }
@@ -1552,16 +1707,17 @@ size_t implicit_smem(const SvPairDev& pd) {
 // K4i applies to level 2 of models with at most kImplicitMaxHeavy dense rows whose staged copies fit
 // the shared memory of one CTA.
 bool implicit_supported(sv_spec* s, SvPairDev* pd) {
-    if (s->level != 2 || !pair_prepare(s->m, pd) || pd->n_heavy > kImplicitMaxHeavy) return false;
+    if (s->level != 2 || !pair_prepare(s->m, pd) || pd->n_heavy > kImplicitMaxHeavy || !path_prepare(s->m, pd)) return false;
     const size_t bytes = implicit_smem(*pd);
     if (bytes > 200 * 1024) return false;
-    return cudaFuncSetAttribute(implicit_pair_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(bytes)) == cudaSuccess;
+    return cudaFuncSetAttribute(implicit_pair_step_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)) == cudaSuccess &&
+           cudaFuncSetAttribute(implicit_pair_step_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)) == cudaSuccess &&
+           cudaFuncSetAttribute(implicit_pair_step_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)) == cudaSuccess;
 }
 } // namespace
 
 extern "C" int sv_spec_set_run_mode(sv_spec* s, int mode) {
-    if (s == nullptr || (mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT && mode != SV_SPEC_RUN_IMPLICIT_STEP))
+    if (s == nullptr || (mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT && mode != SV_SPEC_RUN_IMPLICIT_CLUSTER))
         return sv_fail(SV_ERR_ARG, "sv_spec_set_run_mode: bad argument");
     if (mode != SV_SPEC_RUN_TABLE && s->level > 1) {
         SV_CUDA(cudaSetDevice(s->m->device));
@@ -1609,7 +1765,7 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         ++launches;
     }
     uint64_t max_chunks = (seqs->max_len - 1) / s->level;
-    if (implicit && s->run_mode == SV_SPEC_RUN_IMPLICIT && max_chunks > 0) {
+    if (implicit && s->run_mode == SV_SPEC_RUN_IMPLICIT_CLUSTER && max_chunks > 0) {
         // K4p: one persistent launch, a cluster per sequence walks all its chunks
         const int rows = static_cast<int>((n + kClusterCtas - 1) / kClusterCtas);
         const int threads = std::max(64, (rows + 31) / 32 * 32);
@@ -1634,7 +1790,8 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         while (rows_per_cta > 8 && ((n + rows_per_cta - 1) / rows_per_cta) * nseq < 6ull * slots) rows_per_cta /= 2;
     }
     // sequence groups on up to kRunStreams streams (group 0 stays on the caller's stream)
-    const int ngroups = static_cast<int>(std::min<uint64_t>(sv_spec::kRunStreams, nseq));
+    int ngroups = static_cast<int>(std::min<uint64_t>(sv_spec::kRunStreams, nseq));
+    if (implicit) ngroups = std::min(ngroups, implicit_groups());
     if (ngroups > 1 && s->ev_fork == nullptr) {
         SV_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
         for (int g = 0; g < sv_spec::kRunStreams - 1; ++g) {
@@ -1650,10 +1807,13 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         for (int g = 0; g < ngroups; ++g) {
             const uint64_t q0 = nseq * g / ngroups, q1 = nseq * (g + 1) / ngroups;
             if (implicit) {
-                const int ntiles = static_cast<int>((n + kImplicitThreads - 1) / kImplicitThreads);
+                static const int rows = implicit_rows_per_thread();
+                const int per_cta = kImplicitThreads * rows;
+                const int ntiles = static_cast<int>((n + per_cta - 1) / per_cta);
                 const int npad = static_cast<int>((n + 15) / 16 * 16);
                 dim3 igrid(static_cast<unsigned>(ntiles + pd.n_heavy), static_cast<unsigned>(q1 - q0));
-                implicit_pair_step_kernel<<<igrid, kImplicitThreads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
+                auto kern = rows == 1 ? implicit_pair_step_kernel<1> : rows == 2 ? implicit_pair_step_kernel<2> : implicit_pair_step_kernel<4>;
+                kern<<<igrid, kImplicitThreads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
                     pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles, npad);
                 ++launches;
                 continue;

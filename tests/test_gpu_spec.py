@@ -148,12 +148,12 @@ def test_handler_table_save_load(api, oracle, tmp_path):
         api.Spec(m, 1).save(tmp_path / "l1")
 
 
-IMPLICIT_MODES = ["persistent", "step"]
+IMPLICIT_MODES = ["step", "cluster"]
 
 
 def _implicit(mode):
     from spec_viterbi_b200 import _lib
-    return {"persistent": _lib.SPEC_RUN_IMPLICIT, "step": _lib.SPEC_RUN_IMPLICIT_STEP}[mode]
+    return {"step": _lib.SPEC_RUN_IMPLICIT, "cluster": _lib.SPEC_RUN_IMPLICIT_CLUSTER}[mode]
 
 
 @pytest.mark.parametrize("mode", IMPLICIT_MODES)
