@@ -224,6 +224,8 @@ struct SvPairDev {
     const uint4* hpath = nullptr;     // paths of the dense rows, concatenated
     const uint32_t* hpath_ptr = nullptr; // [heavy + 1]
     int path_slots = 0;
+    int n_stage = 0;                 // dense rows that are a SOURCE of some row: only these are staged as r_h
+    int stage_h[4] = {0, 0, 0, 0};   // their dense-copy indices
     int stage_row = 0; // light pass: (n + 8) floats of dynamic shared memory hold the row's first dense source
 };
 
@@ -811,7 +813,7 @@ __device__ __forceinline__ void implicit_light_rows(const SvPairDev& pd, const f
         const float e = eb[i];
 #pragma unroll
         for (int h = 0; h < kImplicitMaxHeavy; ++h)
-            if (h < pd.n_heavy) uh[h][x] = e + pd.wcol[static_cast<size_t>(h) * pd.n + i];
+            if (h < pd.n_stage) uh[h][x] = e + pd.wcol[static_cast<size_t>(pd.stage_h[h]) * pd.n + i];
         const int cnt = static_cast<int>(pd.lcount[i]);
         const uint4* __restrict__ lp = pd.lpath + i;
         float bx = pos_inf();
@@ -829,7 +831,7 @@ __device__ __forceinline__ void implicit_light_rows(const SvPairDev& pd, const f
     const uint32_t sr_addr = static_cast<uint32_t>(__cvta_generic_to_shared(sr));
 #pragma unroll
     for (int h = 0; h < kImplicitMaxHeavy; ++h) {
-        if (h >= pd.n_heavy) continue;
+        if (h >= pd.n_stage) continue;
         bool any = false;
 #pragma unroll
         for (int x = 0; x < R; ++x) any = any || uh[h][x] < pos_inf();
@@ -849,21 +851,44 @@ __device__ __forceinline__ float implicit_heavy_row(const SvPairDev& pd, const f
     const uint32_t p1 = pd.hpath_ptr[hme + 1];
     for (uint32_t p = pd.hpath_ptr[hme] + tid; p < p1; p += nthr) best = fminf(best, path_term(pd.hpath[p], e, ea, sv));
     const float4* __restrict__ v4 = reinterpret_cast<const float4*>(sv);
-    for (int h = 0; h < pd.n_heavy; ++h) {
-        const float w = pd.wd[static_cast<size_t>(hme) * n + pd.hrow[h]]; // T'[i][hrow[h]], +inf = absent
+    for (int h = 0; h < pd.n_stage; ++h) {
+        const float w = pd.wd[static_cast<size_t>(hme) * n + pd.hrow[pd.stage_h[h]]]; // T'[i][source row], +inf = absent
         if (w < pos_inf())
             best = fminf(best, heavy_stream(e + w, reinterpret_cast<const float4*>(sr + h * npad), v4, npad >> 2, tid, nthr));
     }
     return best;
 }
 
-// r_h[k] = fl(E[a][hrow[h]] + T'[hrow[h]][k]) for the dense rows, +inf padded
-__device__ __forceinline__ void implicit_stage_heavy(const SvPairDev& pd, const float* __restrict__ ea,
-                                                     float* __restrict__ sr, int npad, int tid, int nthr) {
-    for (int h = 0; h < pd.n_heavy; ++h) {
-        const float e = ea[pd.hrow[h]];
-        const float* __restrict__ wrow = pd.wd + static_cast<size_t>(h) * pd.n;
-        for (int k = tid; k < npad; k += nthr) sr[h * npad + k] = k < pd.n ? e + wrow[k] : pos_inf();
+// Stages v (when vi != nullptr) and r_h[k] = fl(E[a][hrow[h]] + T'[hrow[h]][k]) of the dense rows, +inf padded.
+// The loads of four strides of all arrays are issued before the first store: a loop that stores after each
+// load serialises ~60 L2 round trips per thread (it was most of the kernel: 29 us per launch in ncu).
+__device__ __forceinline__ void implicit_stage(const SvPairDev& pd, const float* __restrict__ ea,
+                                               const float* __restrict__ vi, float* __restrict__ sv,
+                                               float* __restrict__ sr, int npad, int tid, int nthr) {
+    const int n = pd.n;
+    float e[kImplicitMaxHeavy];
+#pragma unroll
+    for (int h = 0; h < kImplicitMaxHeavy; ++h) e[h] = h < pd.n_stage ? ea[pd.hrow[pd.stage_h[h]]] : 0.0f;
+    for (int k0 = tid; k0 < npad; k0 += 4 * nthr) {
+        float x[4][1 + kImplicitMaxHeavy];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k0 + u * nthr;
+            const bool ok = k < n;
+            x[u][0] = (vi != nullptr && ok) ? vi[k] : pos_inf();
+#pragma unroll
+            for (int h = 0; h < kImplicitMaxHeavy; ++h)
+                x[u][1 + h] = (h < pd.n_stage && ok) ? pd.wd[static_cast<size_t>(pd.stage_h[h]) * n + k] : pos_inf();
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k0 + u * nthr;
+            if (k >= npad) continue;
+            if (vi != nullptr) sv[k] = x[u][0];
+#pragma unroll
+            for (int h = 0; h < kImplicitMaxHeavy; ++h)
+                if (h < pd.n_stage) sr[h * npad + k] = e[h] + x[u][1 + h];
+        }
     }
 }
 
@@ -899,8 +924,7 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     const unsigned a = load_sym(s, o0 + 1 + chunk * 2), b = load_sym(s, o0 + 2 + chunk * 2);
     const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
     const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
-    for (int k = threadIdx.x; k < npad; k += kImplicitThreads) sv[k] = k < n ? vi[k] : pos_inf();
-    implicit_stage_heavy(pd, ea, sr, npad, threadIdx.x, kImplicitThreads);
+    implicit_stage(pd, ea, vi, sv, sr, npad, threadIdx.x, kImplicitThreads);
     __syncthreads();
     if (!heavy_cta) {
         const int i0 = blockIdx.x * R * kImplicitThreads + threadIdx.x;
@@ -967,7 +991,7 @@ implicit_pair_persistent_kernel(SvPairDev pd, RunSeqs s, const float* __restrict
         const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
         const float* __restrict__ sv = vb + cur * npad;
         const int nxt = (cur ^ 1) * npad;
-        implicit_stage_heavy(pd, ea, sr, npad, tid, nthr);
+        implicit_stage(pd, ea, nullptr, nullptr, sr, npad, tid, nthr);
         __syncthreads();
         float best[1];
         implicit_light_rows<1>(pd, ea, eb, i, 0, live ? 1u : 0u, sv, sr, npad, best);
@@ -1293,6 +1317,7 @@ bool path_prepare(sv_model* m, SvPairDev* pd) {
         struct P4 { float w1, w2; uint32_t j, k; };
         std::vector<P4> lpath(std::max<size_t>(slots * n, 1), P4{0, 0, 0, 0}), hpath(std::max<size_t>(htotal, 1), P4{0, 0, 0, 0});
         std::vector<float> wcol(nh * n, std::numeric_limits<float>::infinity());
+        unsigned used = 0;
         for (size_t i = 0; i < n; ++i) {
             size_t c = 0;
             const size_t hi = heavy(i) ? std::find(hrow.begin(), hrow.end(), static_cast<uint32_t>(i)) - hrow.begin() : 0;
@@ -1301,6 +1326,7 @@ bool path_prepare(sv_model* m, SvPairDev* pd) {
                 if (heavy(j)) {
                     const size_t hj = std::find(hrow.begin(), hrow.end(), j) - hrow.begin();
                     wcol[hj * n + i] = cw[p];
+                    if (cw[p] < std::numeric_limits<float>::infinity()) used |= 1u << hj;
                     continue;
                 }
                 for (uint32_t t = rp[j]; t < rp[j + 1]; ++t, ++c) {
@@ -1332,6 +1358,7 @@ bool path_prepare(sv_model* m, SvPairDev* pd) {
         m->path_state = 1;
         m->path_slots = static_cast<int>(slots);
         m->path_heavy_total = static_cast<int>(htotal);
+        m->path_used_mask = used;
     }
     const size_t lp_count = std::max<size_t>(static_cast<size_t>(m->path_slots) * n, 1);
     const size_t hp_count = std::max<size_t>(static_cast<size_t>(m->path_heavy_total), 1);
@@ -1347,6 +1374,9 @@ bool path_prepare(sv_model* m, SvPairDev* pd) {
     pd->wcol = reinterpret_cast<const float*>(base + o_wc);
     pd->hpath_ptr = reinterpret_cast<const uint32_t*>(base + o_ptr);
     pd->path_slots = m->path_slots;
+    pd->n_stage = 0;
+    for (int h = 0; h < pd->n_heavy; ++h)
+        if ((m->path_used_mask >> h) & 1u) pd->stage_h[pd->n_stage++] = h;
     return true;
 }
 
@@ -1687,8 +1717,8 @@ namespace {
 // light rows per thread of K4i (register blocking of the heavy streams); SV_IMPLICIT_ROWS = 1 | 2 | 4
 int implicit_rows_per_thread() {
     const char* e = std::getenv("SV_IMPLICIT_ROWS");
-    const int r = e ? std::atoi(e) : 1; // measured on config 3: 1 -> 76 ms, 2 -> 82 ms, 4 -> 77 ms (fewer, fatter CTAs)
-    return r == 2 || r == 4 ? r : 1;
+    const int r = e ? std::atoi(e) : 2;
+    return r == 1 || r == 4 ? r : 2;
 }
 
 // sequence groups (side streams) of K4i; SV_IMPLICIT_GROUPS = 1..4
@@ -1701,7 +1731,7 @@ int implicit_groups() {
 }
 
 size_t implicit_smem(const SvPairDev& pd) {
-    return static_cast<size_t>(1 + pd.n_heavy) * ((pd.n + 15) / 16 * 16) * sizeof(float);
+    return static_cast<size_t>(1 + pd.n_stage) * ((pd.n + 15) / 16 * 16) * sizeof(float);
 }
 
 // K4i applies to level 2 of models with at most kImplicitMaxHeavy dense rows whose staged copies fit

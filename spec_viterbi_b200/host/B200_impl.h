@@ -158,6 +158,14 @@ class B200_spec_impl : public Viterbi_spec_impl {
         return res;
     }
 
+    // Not in the reference: how a level-2 chunk is applied (sv_spec_set_run_mode) -- SV_SPEC_RUN_TABLE reads the
+    // precomputed handler (the reference's GrB_mxm per chunk), SV_SPEC_RUN_IMPLICIT recomputes the entries from
+    // the sparse factors (bit-identical, no table traffic).  Throws if the model / level is not eligible.
+    void set_run_mode(int mode) {
+        if (spec == nullptr) throw std::runtime_error("B200_spec_impl: spec_with(hmm) must be called first");
+        b200_detail::check(sv_spec_set_run_mode(spec, mode), "sv_spec_set_run_mode");
+    }
+
     // Not in the reference (it recomputes in every spec_with): keep the handler tables of level >= 2
     // across processes.  spec_with_saved attaches a table written by save_tables; it throws if the file
     // was built from a different model.
