@@ -63,6 +63,16 @@ int main(int argc, char** argv) {
                 ++failures;
             }
         }
+        // level 2 again with the chunks recomputed from the sparse factors (K4i): same bits, no table reads
+        if (spec.size() > 1) {
+            B200_spec_impl implicit(hmm, 2);
+            implicit.set_run_mode(SV_SPEC_RUN_IMPLICIT);
+            for (const auto& sq : sequences)
+                if (!harness::bit_equal(spec[1]->run_Viterbi_spec(sq), implicit.run_Viterbi_spec(sq))) {
+                    std::cout << "MISMATCH implicit level-2 run " << f << "\n";
+                    ++failures;
+                }
+        }
         // smallest model: the level-2 tables survive a save / attach round trip (not in the reference)
         if (&f == &files.front() && spec.size() > 1) {
             const std::string tmp = "/tmp/sv_tables_" + std::to_string(::getpid()) + ".svht";

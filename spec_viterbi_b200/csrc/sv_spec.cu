@@ -900,8 +900,9 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     extern __shared__ float4 sm4[];
     float* sv = reinterpret_cast<float*>(sm4);  // [npad] v, +inf padded
     float* sr = sv + npad;                      // [n_heavy][npad] r_h
-    __shared__ float s_red[kImplicitThreads / 32];
+    __shared__ float s_red[kImplicitThreads / 32 /*max*/];
     const int n = pd.n;
+    const int nthr = blockDim.x; // 64 or 128
     const int q = seq_base + blockIdx.y;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
@@ -915,7 +916,7 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
         } else {
 #pragma unroll
             for (int x = 0; x < R; ++x) {
-                const int i = (blockIdx.x * R + x) * kImplicitThreads + threadIdx.x;
+                const int i = (blockIdx.x * R + x) * nthr + threadIdx.x;
                 if (i < n && pd.hidx[i] < 0) vo[i] = vi[i];
             }
         }
@@ -924,30 +925,30 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     const unsigned a = load_sym(s, o0 + 1 + chunk * 2), b = load_sym(s, o0 + 2 + chunk * 2);
     const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
     const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
-    implicit_stage(pd, ea, vi, sv, sr, npad, threadIdx.x, kImplicitThreads);
+    implicit_stage(pd, ea, vi, sv, sr, npad, threadIdx.x, nthr);
     __syncthreads();
     if (!heavy_cta) {
-        const int i0 = blockIdx.x * R * kImplicitThreads + threadIdx.x;
+        const int i0 = blockIdx.x * R * nthr + threadIdx.x;
         unsigned live = 0;
 #pragma unroll
         for (int x = 0; x < R; ++x) {
-            const int i = i0 + x * kImplicitThreads;
+            const int i = i0 + x * nthr;
             if (i < n && pd.hidx[i] < 0) live |= 1u << x;
         }
         float best[R];
-        implicit_light_rows<R>(pd, ea, eb, i0, kImplicitThreads, live, sv, sr, npad, best);
+        implicit_light_rows<R>(pd, ea, eb, i0, nthr, live, sv, sr, npad, best);
 #pragma unroll
         for (int x = 0; x < R; ++x)
-            if ((live >> x) & 1u) vo[i0 + x * kImplicitThreads] = best[x];
+            if ((live >> x) & 1u) vo[i0 + x * nthr] = best[x];
         return;
     }
-    float best = warp_min(implicit_heavy_row(pd, ea, eb, hme, sv, sr, npad, threadIdx.x, kImplicitThreads));
+    float best = warp_min(implicit_heavy_row(pd, ea, eb, hme, sv, sr, npad, threadIdx.x, nthr));
     if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
     __syncthreads();
     if (threadIdx.x == 0) {
         float r = s_red[0];
 #pragma unroll
-        for (int wv = 1; wv < kImplicitThreads / 32; ++wv) r = fminf(r, s_red[wv]);
+        for (int wv = 1; wv < nthr / 32; ++wv) r = fminf(r, s_red[wv]);
         vo[pd.hrow[hme]] = r;
     }
 }
@@ -1721,6 +1722,12 @@ int implicit_rows_per_thread() {
     return r == 1 || r == 4 ? r : 2;
 }
 
+// threads per CTA of K4i; SV_IMPLICIT_THREADS = 64 | 128
+int implicit_threads() {
+    const char* e = std::getenv("SV_IMPLICIT_THREADS");
+    return e && std::atoi(e) == 64 ? 64 : kImplicitThreads;
+}
+
 // sequence groups (side streams) of K4i; SV_IMPLICIT_GROUPS = 1..4
 int implicit_groups() {
     const char* e = std::getenv("SV_IMPLICIT_GROUPS");
@@ -1838,12 +1845,13 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
             const uint64_t q0 = nseq * g / ngroups, q1 = nseq * (g + 1) / ngroups;
             if (implicit) {
                 static const int rows = implicit_rows_per_thread();
-                const int per_cta = kImplicitThreads * rows;
+                static const int threads = implicit_threads();
+                const int per_cta = threads * rows;
                 const int ntiles = static_cast<int>((n + per_cta - 1) / per_cta);
                 const int npad = static_cast<int>((n + 15) / 16 * 16);
                 dim3 igrid(static_cast<unsigned>(ntiles + pd.n_heavy), static_cast<unsigned>(q1 - q0));
                 auto kern = rows == 1 ? implicit_pair_step_kernel<1> : rows == 2 ? implicit_pair_step_kernel<2> : implicit_pair_step_kernel<4>;
-                kern<<<igrid, kImplicitThreads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
+                kern<<<igrid, threads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
                     pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles, npad);
                 ++launches;
                 continue;
