@@ -1807,7 +1807,10 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         const int rows = static_cast<int>((n + kClusterCtas - 1) / kClusterCtas);
         const int threads = std::max(64, (rows + 31) / 32 * 32);
         const int npad = static_cast<int>((n + 15) / 16 * 16);
-        const size_t smem = implicit_smem(pd) + static_cast<size_t>(npad) * sizeof(float);
+        size_t smem = implicit_smem(pd) + static_cast<size_t>(npad) * sizeof(float);
+        // clusters are packed onto few SMs when many CTAs fit one SM; a larger shared-memory request per CTA
+        // (SV_K4P_SMEM_KB) caps the CTAs per SM and spreads the clusters over the chip
+        if (const char* e = std::getenv("SV_K4P_SMEM_KB")) smem = std::max(smem, static_cast<size_t>(std::atoi(e)) * 1024);
         if (threads <= 1024 && smem <= 200 * 1024) {
             auto kern = threads <= 512 ? implicit_pair_persistent_kernel<512> : implicit_pair_persistent_kernel<1024>;
             SV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
