@@ -214,7 +214,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_line(line)
 
 
 def workload_config(name, hmm, offs, n_gpus):
@@ -416,13 +416,31 @@ def run_b200(args):
                       "the whole table afterwards), min of 3, max over ranks"}
         if not args.no_cpu:
             line["cpu_baseline"] = cpu_port_baseline(hmm, syms, offs)
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit_line(line) -> None:
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    print(json.dumps(line), file=out, flush=True)
+
+
+def claim_stdout() -> None:
+    """stdout carries ONE JSON line: everything else written to fd 1 (NCCL prints its version banner there from C)
+    is sent to stderr; the JSON line goes to a private duplicate of the original stdout."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
