@@ -62,26 +62,43 @@ enum {
     SV_KERNEL_AUTO = 0,
     SV_KERNEL_GENERIC = 1, /* CSR in L1/L2, any model size */
     SV_KERNEL_ES = 2,      /* edge-stationary: transitions in registers, E and v in smem */
-    SV_KERNEL_LS = 3       /* lockstep: 4/8 sequences per CTA, transitions in registers, v in
+    SV_KERNEL_LS = 3,      /* lockstep: 4/8 sequences per CTA, transitions in registers, v in
                               smem as float4, E in tensor memory (the batched throughput kernel) */
+    SV_KERNEL_CHAIN = 4    /* chain + specials models (every profile HMM the reference ships): v of 1..8
+                              sequences in REGISTERS, band edge from the neighbouring register, dense rows
+                              through the chain minimum, E in tensor memory; FP32-issue bound */
 };
 
-/* Builds the device-resident model (K0 repack) from the reference's HMM layout:
+/* Builds the device-resident model from the reference's HMM layout:
  * COO transitions (src = HMM::trans_rows, dst = HMM::trans_cols, w = -log2 p),
  * emissions [emits][states], sparse start vector.  Duplicate COO / start entries keep
- * the FIRST occurrence (GrB_FIRST_FP32).  `device` is a CUDA ordinal. */
+ * the FIRST occurrence (GrB_FIRST_FP32).  `device` is a CUDA ordinal.
+ * Cost: CSR build + one upload (about a millisecond at 2405 states).  The kernel-specific K0
+ * schedules are built by the FIRST launch that needs them (chain < 1 ms, edge-stationary ~5 ms,
+ * lockstep ~0.1 s with the full bank-colouring search continuing on a background host thread and its
+ * result kept in an on-disk plan cache: $SV_PLAN_CACHE_DIR, default ~/.cache/spec_viterbi_b200,
+ * SV_PLAN_CACHE=0 disables; SV_PLAN_REFINE=bg|sync|off).  A level >= 2 spec never builds them.
+ *
+ * Concurrency: a model may be used from several host threads / streams.  sv_viterbi_device launches
+ * are independent (each takes its own work-queue counter); the host-buffer entry points
+ * (sv_viterbi, sv_viterbi_batch*, sv_spec_run, sv_spec_run_batch*) share one workspace per model and
+ * serialise on it; sv_spec_run_device calls on ONE spec are ordered on the device (they share the
+ * spec's state vectors).  Creating / destroying handles is not thread-safe against their use. */
 int sv_model_create(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
                     const uint64_t* trans_dst, const float* trans_w, const float* emissions,
                     uint64_t nstart, const uint64_t* start_cols, const float* start_w, int device,
                     sv_model** out);
 void sv_model_destroy(sv_model* m);
 int sv_model_set_kernel(sv_model* m, int kernel);
+/* Builds every K0 schedule now and waits for the background refinement of the lockstep plan, so
+ * that measurements taken afterwards see the final schedules (optional). */
+int sv_model_prepare(sv_model* m);
 
 typedef struct sv_model_info {
     uint64_t states, emits, nnz;   /* nnz after duplicate removal */
     uint64_t max_in_degree;
     int32_t device;
-    int32_t kernel;                /* SV_KERNEL_* that sv_viterbi* will launch */
+    int32_t kernel;                /* SV_KERNEL_* of the last sv_viterbi* launch (0 before the first) */
     /* edge-stationary schedule (zeros when the model does not fit that kernel) */
     int32_t es_threads, es_seqs_per_cta, es_ranks, es_heavy_rows;
     uint64_t es_slots_per_thread;  /* register-resident edge slots per thread (padded) */
@@ -89,7 +106,7 @@ typedef struct sv_model_info {
     uint64_t es_gather_ideal;      /* same with zero bank conflicts */
     uint64_t es_smem_bytes;
     uint64_t es_split_states;      /* virtual states added by in-degree capping */
-    /* lockstep schedule (zeros when the model does not fit that kernel) */
+    /* lockstep schedule (zeros when the model does not fit that kernel, or not asked for yet) */
     int32_t ls_threads, ls_seqs_per_cta, ls_ranks, ls_heavy_rows;
     int32_t ls_tmem_cols, ls_reserved;
     uint64_t ls_gather_wavefronts; /* LDS.128 wavefronts of the v gather per step and float4 group */
@@ -97,6 +114,10 @@ typedef struct sv_model_info {
     uint64_t ls_smem_bytes;
     uint64_t ls_split_states;
     uint64_t ls_colour_cost_before, ls_colour_cost_after; /* K0 bank-colouring search */
+    uint64_t ls_sa_iters;          /* length of the search behind the current lockstep plan */
+    /* chain schedule (zeros when the model is not chain + specials, or not asked for yet) */
+    int32_t chain_threads, chain_states, chain_specials, chain_seqs_per_cta, chain_tmem_cols, chain_reserved;
+    double plan_ms;                /* host milliseconds spent in K0 planners so far */
 } sv_model_info;
 int sv_model_get_info(const sv_model* m, sv_model_info* info);
 
@@ -135,6 +156,28 @@ int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out, float* d_b
 /* Kernel launches issued by the last sv_viterbi*_ / sv_spec_run* call on this model. */
 int sv_model_last_launches(const sv_model* m);
 
+/* ------------------------------------------------------------- multi-GPU ---- */
+/* The HMM replicated on several devices of one box, the sequences of a batch dealt to them in contiguous
+ * ranges of about equal symbol counts (independent sequences, no exchange inside the time loop,
+ * hence no collective: each device delivers its share of the results into the caller's host arrays).
+ * One host thread per device drives that device's replica.  devices = NULL, ndev = 0: every visible device.
+ * Replaces the harness loop of benchmark/bench_Viterbi.h:51-57 at box scale. */
+typedef struct sv_multi sv_multi;
+int sv_multi_create(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                    const uint64_t* trans_dst, const float* trans_w, const float* emissions, uint64_t nstart,
+                    const uint64_t* start_cols, const float* start_w, const int* devices, int ndev,
+                    sv_multi** out);
+void sv_multi_destroy(sv_multi* mm);
+int sv_multi_device_count(const sv_multi* mm);
+sv_model* sv_multi_model(sv_multi* mm, int k);    /* replica k (owned by mm) */
+int sv_multi_prepare(sv_multi* mm);               /* sv_model_prepare on every replica, in parallel */
+int sv_multi_viterbi_batch(sv_multi* mm, const uint64_t* symbols, const uint64_t* offsets, uint64_t nseq,
+                           float* out, float* best, int32_t* best_state);
+int sv_multi_viterbi_batch_u8(sv_multi* mm, const uint8_t* symbols, const uint64_t* offsets, uint64_t nseq,
+                              float* out, float* best, int32_t* best_state);
+/* Host only: the partition the two calls above use; cut[parts + 1], device k gets sequences [cut[k], cut[k+1]). */
+int sv_multi_split(const uint64_t* offsets, uint64_t nseq, int parts, uint64_t* cut);
+
 /* ------------------------------------------------------ specialised path ---- */
 typedef struct sv_spec sv_spec;
 
@@ -148,17 +191,21 @@ enum {
 
 /* spec_with(hmm): level-1 tables, and for level > 1 the dense handler of every symbol
  * tuple in [tuple_begin, tuple_end) (pass 0, 0 for all emits^level tuples).  Tuple index =
- * sum_j k_j * emits^(level-j), k_1 = first consumed symbol.  If d_table is not NULL it must
- * be a device buffer of (tuple_end-tuple_begin)*states*states floats that the caller owns
- * (used to all-gather shards across GPUs); otherwise the table is allocated internally. */
+ * sum_j k_j * emits^(level-j), k_1 = first consumed symbol.  If d_table is not NULL it is a device
+ * buffer the caller owns and handler `tuple_begin` is written at d_table[0] (so it needs
+ * (tuple_end-tuple_begin)*states*states floats); otherwise the table is allocated internally. */
 int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t tuple_begin,
                    uint64_t tuple_end, float* d_table, void* stream, sv_spec** out);
 void sv_spec_destroy(sv_spec* s);
 uint64_t sv_spec_level(const sv_spec* s);
-/* Declares that tuples [tuple_begin, tuple_end) of the table are now valid (after an
- * external all-gather into the caller-owned d_table). */
-int sv_spec_set_range(sv_spec* s, uint64_t tuple_begin, uint64_t tuple_end);
-/* Device pointer of the handler table (tuple_begin first) and its tuple range. */
+/* Re-points a spec with a CALLER-OWNED table at `d_table`, whose first handler is tuple `table_first`,
+ * and declares tuples [tuple_begin, tuple_end) of it valid (table_first <= tuple_begin).  This is the
+ * step after an all-gather of tuple shards: every rank builds its shard with sv_spec_create into its
+ * slice of one full-size buffer, the shards are exchanged, then each rank calls
+ * sv_spec_set_range(s, full_buffer, 0, 0, emits^level).  Ranges below table_first are rejected. */
+int sv_spec_set_range(sv_spec* s, float* d_table, uint64_t table_first, uint64_t tuple_begin,
+                      uint64_t tuple_end);
+/* Device pointer of the handler table (its first handler is tuple *table_first) and the valid range. */
 float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_t* tuple_end);
 /* Copies one dense handler (states*states floats, row = destination state) to the host. */
 int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out);
@@ -174,16 +221,16 @@ int sv_spec_save(const sv_spec* s, const char* path);
 int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out);
 
 /* How sv_spec_run* applies a level-2 chunk (GraphBLAS_spec_impl.cpp:69-79, one GrB_mxm per chunk):
- * SV_SPEC_RUN_TABLE (default) reads the precomputed dense handler (K4, 4*N^2 bytes per chunk);
+ * SV_SPEC_RUN_TABLE reads the precomputed dense handler (K4, 4*N^2 bytes per chunk);
  * SV_SPEC_RUN_IMPLICIT recomputes the handler entries it needs from the two sparse level-1 factors
  * (K4i) -- same sums, same association, same bits, no table traffic; the table may then be empty
  * (sv_spec_create with tuple_begin == tuple_end == emits^level).  Level 2, models with at most 4
- * dense rows; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.  Level 1 ignores the mode. */
+ * dense rows; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.
+ * SV_SPEC_RUN_AUTO (default) = IMPLICIT whenever the spec is eligible, else TABLE.  Level 1 ignores the mode. */
 enum {
     SV_SPEC_RUN_TABLE = 0,
-    SV_SPEC_RUN_IMPLICIT = 1,        /* K4i: one launch per chunk and sequence group */
-    SV_SPEC_RUN_IMPLICIT_CLUSTER = 2 /* K4p: one persistent launch, a thread-block cluster of 8 CTAs per sequence
-                                        (experimental: measured slower than K4i; K4i beyond 8192 states) */
+    SV_SPEC_RUN_IMPLICIT = 1, /* K4i */
+    SV_SPEC_RUN_AUTO = 3
 };
 int sv_spec_set_run_mode(sv_spec* s, int mode);
 
@@ -211,18 +258,6 @@ int sv_io_ess_copy(const sv_ess_file* f, uint64_t* offsets /*[nseq+1]*/, uint64_
 int sv_io_ess_write_packed(const sv_ess_file* f, const char* path);
 void sv_io_ess_close(sv_ess_file* f);
 
-/* ------------------------------------------------------- micro-benchmarks ---- */
-/* FP32 pipe probe used to fix the non-tensor roofline: runs `iters` dependent-chain
- * iterations of the chosen instruction mix on every SM and returns lane-instructions/s.
- * mix: 0 = FADD, 1 = FMNMX (2-input min), 2 = FMNMX3 (3-input min), 3 = 2 FADD + 1 FMNMX3,
- *      4 = 4 FADD + 1 FMNMX3 (the step's inner loop), 5 = LDS.32 conflict-free + 2 FADD + FMNMX */
-int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_per_s, double* sm_clock_mhz);
-/* Tensor-memory probe: fills all 512 TMEM columns of every SM through tcgen05.st, reads them
- * back with run-time (warp-uniform) column addresses -- the access pattern of the emission
- * lookup in the lockstep step kernel -- and reports mismatches and the tcgen05.ld read rate. */
-int sv_probe_tmem(int device, int iters, unsigned* errors, double* bytes_per_clk_per_sm);
-
-
 /* K0 self-check (host only, no GPU, NOT a compute path): builds the lockstep schedule of a model
  * and replays its register images for one sequence the way a CTA would, so the K0
  * transformation can be verified against the oracle without a device.  stats[12] = {valid,
@@ -233,6 +268,14 @@ int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t trans, const 
                          const uint64_t* trans_dst, const float* trans_w, const float* emissions,
                          uint64_t nstart, const uint64_t* start_cols, const float* start_w,
                          const uint64_t* seq, uint64_t len, float* out, uint64_t stats[12]);
+
+/* The same for the chain kernel: detects the chain + specials structure and replays the kernel's
+ * algebra (band edge from position p-1, hub broadcast, special rows through the chain minimum) on the
+ * host.  stats[8] = {valid, threads, chain states, specials, tmem columns, nonneg, special 0, special 1}. */
+int sv_k0_chain_check(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                      const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                      uint64_t nstart, const uint64_t* start_cols, const float* start_w,
+                      const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]);
 
 #ifdef __cplusplus
 }

@@ -12,9 +12,9 @@ _PKG = Path(__file__).resolve().parent
 LIB_PATH = _PKG / "libspecviterbi_b200.so"
 
 SV_OK = 0
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_ES, KERNEL_LS = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_ES, KERNEL_LS, KERNEL_CHAIN = 0, 1, 2, 3, 4
 SPEC_AUTO, SPEC_DENSE_GEMM, SPEC_SPARSE_LHS, SPEC_PAIR_ROWS = 0, 1, 2, 3
-SPEC_RUN_TABLE, SPEC_RUN_IMPLICIT, SPEC_RUN_IMPLICIT_CLUSTER = 0, 1, 2
+SPEC_RUN_TABLE, SPEC_RUN_IMPLICIT, SPEC_RUN_AUTO = 0, 1, 3
 
 u64p = C.POINTER(C.c_uint64)
 u8p = C.POINTER(C.c_uint8)
@@ -39,6 +39,10 @@ class ModelInfo(C.Structure):
         ("ls_gather_wavefronts", C.c_uint64), ("ls_gather_ideal", C.c_uint64),
         ("ls_smem_bytes", C.c_uint64), ("ls_split_states", C.c_uint64),
         ("ls_colour_cost_before", C.c_uint64), ("ls_colour_cost_after", C.c_uint64),
+        ("ls_sa_iters", C.c_uint64),
+        ("chain_threads", C.c_int32), ("chain_states", C.c_int32), ("chain_specials", C.c_int32),
+        ("chain_seqs_per_cta", C.c_int32), ("chain_tmem_cols", C.c_int32), ("chain_reserved", C.c_int32),
+        ("plan_ms", C.c_double),
     ]
 
 
@@ -51,6 +55,7 @@ SIGNATURES = {
                                   C.c_uint64, u64p, f32p, C.c_int, C.POINTER(vp)]),
     "sv_model_destroy": (None, [vp]),
     "sv_model_set_kernel": (C.c_int, [vp, C.c_int]),
+    "sv_model_prepare": (C.c_int, [vp]),
     "sv_model_get_info": (C.c_int, [vp, C.POINTER(ModelInfo)]),
     "sv_model_last_launches": (C.c_int, [vp]),
     "sv_seqs_create": (C.c_int, [vp, u64p, u64p, C.c_uint64, C.POINTER(vp)]),
@@ -66,7 +71,7 @@ SIGNATURES = {
                                  C.POINTER(vp)]),
     "sv_spec_destroy": (None, [vp]),
     "sv_spec_level": (C.c_uint64, [vp]),
-    "sv_spec_set_range": (C.c_int, [vp, C.c_uint64, C.c_uint64]),
+    "sv_spec_set_range": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64, C.c_uint64]),
     "sv_spec_set_run_mode": (C.c_int, [vp, C.c_int]),
     "sv_spec_table": (vp, [vp, u64p, u64p]),
     "sv_spec_get_handler": (C.c_int, [vp, C.c_uint64, f32p]),
@@ -86,10 +91,43 @@ SIGNATURES = {
     "sv_io_ess_close": (None, [vp]),
     "sv_k0_lockstep_check": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
                                        C.c_uint64, u64p, f32p, u64p, C.c_uint64, f32p, u64p]),
-    "sv_probe_tmem": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]),
-    "sv_probe_fp32": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
-                                C.POINTER(C.c_double)]),
+    "sv_k0_chain_check": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
+                                    C.c_uint64, u64p, f32p, u64p, C.c_uint64, f32p, u64p]),
+    "sv_multi_create": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
+                                  C.c_uint64, u64p, f32p, C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]),
+    "sv_multi_destroy": (None, [vp]),
+    "sv_multi_device_count": (C.c_int, [vp]),
+    "sv_multi_model": (vp, [vp, C.c_int]),
+    "sv_multi_prepare": (C.c_int, [vp]),
+    "sv_multi_viterbi_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, f32p, f32p, i32p]),
+    "sv_multi_viterbi_batch_u8": (C.c_int, [vp, u8p, u64p, C.c_uint64, f32p, f32p, i32p]),
+    "sv_multi_split": (C.c_int, [u64p, C.c_uint64, C.c_int, u64p]),
 }
+
+# the micro-benchmark library (include/sv_probe_b200.h) -- separate from the product
+PROBE_LIB_PATH = _PKG / "libsvprobe_b200.so"
+PROBE_SIGNATURES = {
+    "sv_probe_last_error": (C.c_char_p, []),
+    "sv_probe_tmem": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_double)]),
+    "sv_probe_fp32": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "sv_probe_smem": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+}
+_probe = None
+
+
+def probe_lib() -> C.CDLL:
+    global _probe
+    if _probe is None:
+        if not PROBE_LIB_PATH.exists():
+            from . import build as _build
+            _build.build()
+        handle = C.CDLL(str(PROBE_LIB_PATH))
+        for name, (res, args) in PROBE_SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _probe = handle
+    return _probe
 
 _lib = None
 

@@ -165,6 +165,34 @@ def k0_lockstep_check(hmm: "HMM", seq=None):
     return dict(zip(names, (int(x) for x in stats))), out
 
 
+def k0_chain_check(hmm: "HMM", seq=None):
+    """Host-only K0 diagnostic of the chain kernel: (stats dict, replayed final vector or None)."""
+    lib = L.lib()
+    h = hmm.normalized()
+    stats = np.zeros(8, np.uint64)
+    out = None
+    sp, sl = None, 0
+    if seq is not None:
+        s = np.ascontiguousarray(seq, np.uint64)
+        out = np.empty(h.states_num, np.float32)
+        sp, sl = _p(s, C.c_uint64), s.size
+    L.check(lib.sv_k0_chain_check(
+        h.states_num, h.emit_num, h.trans_num, _p(h.trans_rows, C.c_uint64), _p(h.trans_cols, C.c_uint64),
+        _p(h.trans_probs, C.c_float), _p(h.emissions, C.c_float), h.non_zero_start_probs,
+        _p(h.start_probabilities_cols, C.c_uint64), _p(h.start_probabilities, C.c_float),
+        sp, sl, _p(out, C.c_float) if out is not None else None, _p(stats, C.c_uint64)))
+    names = ["valid", "threads", "chain_states", "specials", "tmem_cols", "nonneg", "special0", "special1"]
+    return dict(zip(names, (int(x) for x in stats))), out
+
+
+def multi_split(offsets: np.ndarray, parts: int) -> np.ndarray:
+    """The contiguous partition sv_multi_viterbi_batch* deals to `parts` devices: cut[parts + 1]."""
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    cut = np.zeros(parts + 1, np.uint64)
+    L.check(L.lib().sv_multi_split(_p(offsets, C.c_uint64), offsets.size - 1, parts, _p(cut, C.c_uint64)))
+    return cut
+
+
 class Model:
     """Device-resident model handle (sv_model)."""
 
@@ -202,6 +230,10 @@ class Model:
 
     def set_kernel(self, kernel: int) -> None:
         L.check(self._lib.sv_model_set_kernel(self._h, kernel))
+
+    def prepare(self) -> None:
+        """Builds every K0 schedule now and waits for the background plan refinement (sv_model_prepare)."""
+        L.check(self._lib.sv_model_prepare(self._h))
 
     def last_launches(self) -> int:
         return int(self._lib.sv_model_last_launches(self._h))
@@ -243,6 +275,62 @@ class Model:
         """Device pointers as ints (e.g. torch.Tensor.data_ptr()); asynchronous."""
         L.check(self._lib.sv_viterbi_device(self._h, seqs.handle, d_out or None, d_best or None,
                                             d_arg or None, stream or None))
+
+
+class MultiModel:
+    """The HMM replicated on several devices of one box (sv_multi); batches are dealt to them."""
+
+    def __init__(self, hmm: HMM, devices: Optional[Sequence[int]] = None):
+        self._lib = L.lib()
+        self.hmm = hmm.normalized()
+        h = self.hmm
+        self._h = C.c_void_p()
+        devs = np.ascontiguousarray(devices if devices is not None else [], np.int32)
+        L.check(self._lib.sv_multi_create(
+            h.states_num, h.emit_num, h.trans_num, _p(h.trans_rows, C.c_uint64),
+            _p(h.trans_cols, C.c_uint64), _p(h.trans_probs, C.c_float), _p(h.emissions, C.c_float),
+            h.non_zero_start_probs, _p(h.start_probabilities_cols, C.c_uint64),
+            _p(h.start_probabilities, C.c_float), _p(devs, C.c_int) if devs.size else None, devs.size,
+            C.byref(self._h)))
+
+    @property
+    def ndev(self) -> int:
+        return int(self._lib.sv_multi_device_count(self._h))
+
+    def prepare(self) -> None:
+        L.check(self._lib.sv_multi_prepare(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.sv_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def viterbi_batch(self, symbols: np.ndarray, offsets: np.ndarray, want_vectors=True, want_best=True,
+                      out=None, best=None, arg=None):
+        nseq = offsets.size - 1
+        if symbols.dtype != np.uint8:
+            symbols = np.ascontiguousarray(symbols, np.uint64)
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        if out is None and want_vectors:
+            out = np.empty((nseq, self.hmm.states_num), np.float32)
+        if best is None and want_best:
+            best = np.empty(nseq, np.float32)
+        if arg is None and want_best:
+            arg = np.empty(nseq, np.int32)
+        fn, st = (self._lib.sv_multi_viterbi_batch_u8, C.c_uint8) if symbols.dtype == np.uint8 else \
+                 (self._lib.sv_multi_viterbi_batch, C.c_uint64)
+        L.check(fn(
+            self._h, _p(symbols, st), _p(offsets, C.c_uint64), nseq,
+            _p(out, C.c_float) if out is not None else None,
+            _p(best, C.c_float) if best is not None else None,
+            _p(arg, C.c_int32) if arg is not None else None))
+        return out, best, arg
 
 
 class Seqs:
@@ -321,8 +409,9 @@ class Spec:
         except Exception:
             pass
 
-    def set_range(self, b: int, e: int) -> None:
-        L.check(self._lib.sv_spec_set_range(self._h, b, e))
+    def set_range(self, d_table: int, table_first: int, b: int, e: int) -> None:
+        """Re-points a caller-owned table: `d_table` holds handler `table_first` first; [b, e) is valid."""
+        L.check(self._lib.sv_spec_set_range(self._h, d_table or None, table_first, b, e))
 
     def set_run_mode(self, mode: int) -> None:
         """L.SPEC_RUN_TABLE (K4, reads the dense handlers) or L.SPEC_RUN_IMPLICIT (K4i, level 2: the
@@ -414,10 +503,11 @@ class B200_impl:
 class B200_spec_impl:
     """Drop-in for a reference `Viterbi_spec_impl` backend (Viterbi_spec_impl.h:6-24)."""
 
-    def __init__(self, level: int, device: int = 0, method: int = L.SPEC_AUTO):
+    def __init__(self, level: int, device: int = 0, method: int = L.SPEC_AUTO, run_mode: int = L.SPEC_RUN_AUTO):
         self.level = int(level)
         self.device = device
         self.method = method
+        self.run_mode = run_mode
         self._model: Optional[Model] = None
         self._spec: Optional[Spec] = None
 
@@ -432,6 +522,8 @@ class B200_spec_impl:
             self._model.close()
         self._model = Model(hmm, self.device)
         self._spec = Spec(self._model, self.level, self.method)
+        if self.run_mode != L.SPEC_RUN_AUTO:
+            self._spec.set_run_mode(self.run_mode)
 
     def run_Viterbi_spec(self, seq) -> np.ndarray:
         if self._spec is None:

@@ -2,11 +2,16 @@
 #include "sv_internal.h"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <mutex>
 #include <new>
 #include <numeric>
+#include <thread>
 
 // ------------------------------------------------------------------ errors ----
 namespace {
@@ -22,12 +27,14 @@ int sv_fail(int code, const std::string& msg) {
 extern "C" const char* sv_last_error(void) { return g_last_error.c_str(); }
 extern "C" const char* sv_version(void) { return "spec_viterbi_b200 0.1 (sm_100a)"; }
 extern "C" int sv_device_count(void) {
+    SV_API_BEGIN
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) {
         cudaGetLastError();
         return 0;
     }
     return n;
+    SV_API_END
 }
 
 // ------------------------------------------------------------------- model ----
@@ -163,8 +170,7 @@ int upload_es(sv_model* m, const SvEsPlan& p, SvEsDev& d, void** blob) {
     return SV_OK;
 }
 
-int upload_ls(sv_model* m) {
-    const SvLsPlan& p = m->ls;
+int upload_ls(sv_model* m, const SvLsPlan& p, SvLsDev& d, void** blob) {
     size_t bytes = 0;
     const size_t o_w = blob_reserve<float>(&bytes, p.edge_w.size());
     const size_t o_off = blob_reserve<uint32_t>(&bytes, p.edge_off.size());
@@ -182,10 +188,9 @@ int upload_ls(sv_model* m) {
     std::memcpy(host.data() + o_start, p.start_p.data(), p.start_p.size() * 4);
     std::memcpy(host.data() + o_cptr, p.copy_ptr.data(), p.copy_ptr.size() * 4);
     std::memcpy(host.data() + o_cp, p.copy_p.data(), p.copy_p.size() * 4);
-    SV_CUDA(cudaMalloc(&m->d_ls_blob, bytes));
-    SV_CUDA(cudaMemcpy(m->d_ls_blob, host.data(), bytes, cudaMemcpyHostToDevice));
-    auto* base = static_cast<unsigned char*>(m->d_ls_blob);
-    SvLsDev& d = m->lsdev;
+    SV_CUDA(cudaMalloc(blob, bytes));
+    SV_CUDA(cudaMemcpy(*blob, host.data(), bytes, cudaMemcpyHostToDevice));
+    auto* base = static_cast<unsigned char*>(*blob);
     d.n = static_cast<int>(m->n);
     d.n_int = p.n_int;
     d.n_lpad = p.n_lpad;
@@ -206,18 +211,247 @@ int upload_ls(sv_model* m) {
     return SV_OK;
 }
 
-// Kernel a launch over `nseq` sequences will use.  AUTO: the lockstep kernel when the batch
-// can fill its sequence lanes on every SM, else one sequence per CTA (ES), else generic.
-int chosen_kernel(const sv_model* m, uint64_t nseq) {
+int upload_chain(sv_model* m) {
+    const SvChainPlan& p = m->chain;
+    size_t bytes = 0;
+    const size_t o_wp = blob_reserve<float>(&bytes, p.w_pred.size());
+    const size_t o_wh = blob_reserve<float>(&bytes, p.w_hub.size());
+    const size_t o_emis = blob_reserve<float>(&bytes, p.emis_p.size());
+    const size_t o_start = blob_reserve<float>(&bytes, p.start_p.size());
+    const size_t o_es = blob_reserve<float>(&bytes, p.emis_s.size());
+    const size_t o_orig = blob_reserve<int32_t>(&bytes, p.orig_of_pos.size());
+    bytes += 256;
+    std::vector<unsigned char> host(bytes, 0);
+    std::memcpy(host.data() + o_wp, p.w_pred.data(), p.w_pred.size() * 4);
+    std::memcpy(host.data() + o_wh, p.w_hub.data(), p.w_hub.size() * 4);
+    std::memcpy(host.data() + o_emis, p.emis_p.data(), p.emis_p.size() * 4);
+    std::memcpy(host.data() + o_start, p.start_p.data(), p.start_p.size() * 4);
+    std::memcpy(host.data() + o_es, p.emis_s.data(), p.emis_s.size() * 4);
+    std::memcpy(host.data() + o_orig, p.orig_of_pos.data(), p.orig_of_pos.size() * 4);
+    SV_CUDA(cudaMalloc(&m->d_chain_blob, bytes));
+    SV_CUDA(cudaMemcpy(m->d_chain_blob, host.data(), bytes, cudaMemcpyHostToDevice));
+    auto* base = static_cast<unsigned char*>(m->d_chain_blob);
+    SvChainDev& d = m->chaindev;
+    d.n = static_cast<int>(m->n);
+    d.n_pos = p.n_pos;
+    d.emits = static_cast<int>(m->emits);
+    d.nsp = p.nsp;
+    d.tmem_cols = p.tmem_cols;
+    d.nonneg = p.nonneg ? 1 : 0;
+    for (int a = 0; a < SV_CHAIN_NSP; ++a) {
+        d.special[a] = a < p.nsp ? static_cast<int>(p.special[a]) : -1;
+        d.u[a] = p.u[a];
+        d.start_s[a] = p.start_s[a];
+        for (int b = 0; b < SV_CHAIN_NSP; ++b) d.ss[a][b] = p.ss[a][b];
+    }
+    d.w_pred = reinterpret_cast<const float*>(base + o_wp);
+    d.w_hub = reinterpret_cast<const float*>(base + o_wh);
+    d.emis_p = reinterpret_cast<const float*>(base + o_emis);
+    d.start_p = reinterpret_cast<const float*>(base + o_start);
+    d.emis_s = reinterpret_cast<const float*>(base + o_es);
+    d.orig_of_pos = reinterpret_cast<const int32_t*>(base + o_orig);
+    return SV_OK;
+}
+
+struct PlanTimer {
+    sv_model* m;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    explicit PlanTimer(sv_model* mm) : m(mm) {}
+    ~PlanTimer() { m->plan_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
+int host_threads() {
+    const unsigned hc = std::thread::hardware_concurrency();
+    return static_cast<int>(std::max(1u, std::min(16u, hc)));
+}
+
+} // namespace
+
+// ------------------------------------------------------------ lazy K0 plans ----
+// Plans are built the first time a launch needs them (a level >= 2 spec_with never does): ES ~5 ms,
+// chain < 1 ms, lockstep: short colouring search now (~0.1 s for 2405 random states), full search on a
+// background thread, finished plans kept in the on-disk plan cache (sv_plan_cache.cpp).
+struct SvLsRefine {
+    std::thread th;
+    std::atomic<int> state{0}; // 0 = idle, 1 = running, 2 = plan ready, 3 = done (taken or failed)
+    volatile int cancel = 0;
+    SvLsPlan plan;
+};
+
+bool sv_model_ensure_es(sv_model* m) {
+    if (m->es_state != 0) return m->es_state > 0;
+    PlanTimer timer(m);
+    m->es_state = -1;
+    sv_es_build_plan(m->csr, m->emis, m->start, m->emits, m->smem_optin, &m->es);
+    if (!m->es.valid) return false;
+    if (upload_es(m, m->es, m->esdev, &m->d_es_blob) != SV_OK ||
+        sv_es_prepare(m->es.variant_index, m->es.smem_bytes) != 0) {
+        cudaGetLastError();
+        m->es.valid = false; // kernel attribute rejected: keep the generic kernel
+        return false;
+    }
+    m->es_state = 1;
+    return true;
+}
+
+bool sv_model_ensure_es1(sv_model* m) {
+    if (m->es1_state != 0) return m->es1_state > 0;
+    m->es1_state = -1;
+    if (!sv_model_ensure_es(m) || m->es.var.q != 2) return false; // one-sequence-per-CTA twin of a 2-sequence plan
+    PlanTimer timer(m);
+    sv_es_build_plan(m->csr, m->emis, m->start, m->emits, m->smem_optin, &m->es1, 1);
+    if (!m->es1.valid) return false;
+    if (upload_es(m, m->es1, m->esdev1, &m->d_es1_blob) != SV_OK ||
+        sv_es_prepare(m->es1.variant_index, m->es1.smem_bytes) != 0) {
+        cudaGetLastError();
+        m->es1.valid = false;
+        return false;
+    }
+    m->es1_state = 1;
+    return true;
+}
+
+namespace {
+bool install_ls(sv_model* m, SvLsPlan&& plan) {
+    void* blob = nullptr;
+    SvLsDev dev;
+    if (upload_ls(m, plan, dev, &blob) != SV_OK || sv_ls_prepare(plan.variant_index, 2, plan.smem_bytes) != 0 ||
+        sv_ls_prepare(plan.variant_index, 1, plan.smem_bytes4) != 0) {
+        cudaGetLastError();
+        if (blob) cudaFree(blob);
+        return false;
+    }
+    if (m->d_ls_blob) m->retired_blobs.push_back(m->d_ls_blob); // a kernel in flight may still read it
+    m->d_ls_blob = blob;
+    m->lsdev = dev;
+    m->ls = std::move(plan);
+    return true;
+}
+
+// Takes over the refined plan if the background search has finished (wait = block until it has).
+void adopt_refined_ls(sv_model* m, bool wait) {
+    SvLsRefine* r = m->refine;
+    if (r == nullptr) return;
+    if (wait && r->th.joinable()) r->th.join();
+    if (r->state.load(std::memory_order_acquire) != 2) return;
+    if (r->th.joinable()) r->th.join();
+    if (r->plan.valid && r->plan.gather_wavefronts < m->ls.gather_wavefronts) install_ls(m, std::move(r->plan));
+    r->state.store(3, std::memory_order_release);
+}
+} // namespace
+
+bool sv_model_ensure_ls(sv_model* m) {
+    if (m->ls_state != 0) {
+        if (m->ls_state > 0) adopt_refined_ls(m, false);
+        return m->ls_state > 0;
+    }
+    PlanTimer timer(m);
+    m->ls_state = -1;
+    // refine policy: "bg" (default) = short search now, full search on a host thread; "sync" = full search now;
+    // "off" = short search only
+    const char* pol = std::getenv("SV_PLAN_REFINE");
+    const std::string policy = pol ? pol : "bg";
+    const uint64_t full_iters = sv_ls_default_sa_iters(m->n);
+    uint64_t quick_iters = std::min<uint64_t>(full_iters, 60ull * m->n);
+    if (const char* q = std::getenv("SV_LS_SA_QUICK_ITERS")) quick_iters = std::strtoull(q, nullptr, 10);
+    SvLsPlan plan;
+    bool refined = sv_plan_cache_load(m->fingerprint, &plan);
+    if (!refined) {
+        SvLsPlanOpts opts;
+        opts.threads = host_threads();
+        opts.sa_iters = policy == "sync" ? full_iters : std::max<uint64_t>(1, quick_iters);
+        sv_ls_build_plan(m->csr, m->emis, m->start, m->emits, m->smem_optin, &plan, opts);
+        refined = opts.sa_iters >= full_iters || plan.colour_cost_after == 0;
+        if (plan.valid && refined) sv_plan_cache_store(m->fingerprint, plan);
+    }
+    if (!plan.valid || !install_ls(m, std::move(plan))) return false;
+    m->ls_state = 1;
+    if (!refined && policy == "bg") {
+        SvLsRefine* r = new (std::nothrow) SvLsRefine;
+        if (r != nullptr) {
+            m->refine = r;
+            r->state.store(1);
+            const uint64_t fp = m->fingerprint;
+            r->th = std::thread([m, r, full_iters, fp]() {
+                try {
+                    SvLsPlanOpts opts;
+                    opts.sa_iters = full_iters;
+                    opts.cancel = &r->cancel;
+                    opts.threads = 2;
+                    // reads only data that is immutable after sv_model_create
+                    sv_ls_build_plan(m->csr, m->emis, m->start, m->emits, m->smem_optin, &r->plan, opts);
+                    if (r->plan.valid) sv_plan_cache_store(fp, r->plan);
+                } catch (...) {
+                    r->plan.valid = false;
+                }
+                r->state.store(2, std::memory_order_release);
+            });
+        }
+    }
+    return true;
+}
+
+bool sv_model_ensure_chain(sv_model* m) {
+    if (m->chain_state != 0) return m->chain_state > 0;
+    PlanTimer timer(m);
+    m->chain_state = -1;
+    sv_chain_build_plan(m->csr, m->emis, m->start, m->emits, &m->chain);
+    if (!m->chain.valid) return false;
+    if (upload_chain(m) != SV_OK) {
+        cudaGetLastError();
+        m->chain.valid = false;
+        return false;
+    }
+    for (const int q : {8, 4, 2, 1}) {
+        size_t smem = 0;
+        int per_sm = 0;
+        if (sv_chain_prepare(m->chain.threads, q, &smem, &per_sm) != 0) {
+            cudaGetLastError();
+            m->chain.valid = false;
+            return false;
+        }
+        m->chain_smem[q == 8 ? 3 : q == 4 ? 2 : q == 2 ? 1 : 0] = smem;
+        m->chain_ctas_per_sm = per_sm;
+    }
+    m->chain_state = 1;
+    return true;
+}
+
+namespace {
+
+// Sequences per CTA of the chain kernel for a batch: the step of a CTA costs about (2 + Q) units (fixed part:
+// barrier, managers, special rows; Q sequences of relaxations), CTAs run in waves over the resident slots.
+int chain_q_for(const sv_model* m, uint64_t nseq) {
+    const uint64_t slots = static_cast<uint64_t>(std::max(1, m->sm_count)) * std::max(1, m->chain_ctas_per_sm);
+    int best_q = 1;
+    uint64_t best_cost = ~0ull;
+    for (const int q : {8, 4, 2, 1}) {
+        const uint64_t ctas = (nseq + q - 1) / q;
+        const uint64_t waves = (ctas + slots - 1) / slots;
+        const uint64_t cost = waves * static_cast<uint64_t>(2 + q);
+        if (cost < best_cost) {
+            best_cost = cost;
+            best_q = q;
+        }
+    }
+    return best_q;
+}
+
+// Kernel a launch over `nseq` sequences will use.  AUTO: the chain kernel whenever the model has the chain +
+// specials structure; else the lockstep kernel when the batch can fill its sequence lanes on every SM; else one
+// or two sequences per CTA (ES); else generic.  Builds the plans it asks about.
+int chosen_kernel(sv_model* m, uint64_t nseq) {
     switch (m->kernel_pref) {
     case SV_KERNEL_GENERIC: return SV_KERNEL_GENERIC;
-    case SV_KERNEL_ES: return m->es.valid ? SV_KERNEL_ES : SV_KERNEL_GENERIC;
-    case SV_KERNEL_LS: return m->ls.valid ? SV_KERNEL_LS : SV_KERNEL_GENERIC;
+    case SV_KERNEL_ES: return sv_model_ensure_es(m) ? SV_KERNEL_ES : SV_KERNEL_GENERIC;
+    case SV_KERNEL_LS: return sv_model_ensure_ls(m) ? SV_KERNEL_LS : SV_KERNEL_GENERIC;
+    case SV_KERNEL_CHAIN: return sv_model_ensure_chain(m) ? SV_KERNEL_CHAIN : SV_KERNEL_GENERIC;
     default: break;
     }
-    if (m->ls.valid && nseq >= static_cast<uint64_t>(2) * m->sm_count) return SV_KERNEL_LS;
-    if (m->es.valid) return SV_KERNEL_ES;
-    if (m->ls.valid) return SV_KERNEL_LS;
+    if (sv_model_ensure_chain(m)) return SV_KERNEL_CHAIN;
+    if (nseq >= static_cast<uint64_t>(2) * m->sm_count && sv_model_ensure_ls(m)) return SV_KERNEL_LS;
+    if (sv_model_ensure_es(m)) return SV_KERNEL_ES;
+    if (sv_model_ensure_ls(m)) return SV_KERNEL_LS;
     return SV_KERNEL_GENERIC;
 }
 
@@ -228,6 +462,7 @@ extern "C" int sv_model_create(uint64_t states, uint64_t emits, uint64_t trans,
                                const float* trans_w, const float* emissions, uint64_t nstart,
                                const uint64_t* start_cols, const float* start_w, int device,
                                sv_model** out) {
+    SV_API_BEGIN
     if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_model_create: out is NULL");
     *out = nullptr;
     if (states == 0 || emits == 0) return sv_fail(SV_ERR_ARG, "sv_model_create: empty model");
@@ -287,72 +522,78 @@ extern "C" int sv_model_create(uint64_t states, uint64_t emits, uint64_t trans,
     if (sv_generic_smem(SvGenericDev{static_cast<int>(states)}) + 4096 > m->smem_optin)
         return fail(sv_fail(SV_ERR_UNSUPPORTED, "model too large for the shared-memory kernels"));
     if ((rc = upload_generic(m)) != SV_OK) return fail(rc);
-    if (cudaMalloc(&m->d_counter, 64) != cudaSuccess)
-        return fail(sv_fail(SV_ERR_CUDA, "cudaMalloc(counter) failed"));
+    if (cudaMalloc(&m->d_counters, SV_COUNTER_RING * 64) != cudaSuccess)
+        return fail(sv_fail(SV_ERR_CUDA, "cudaMalloc(counters) failed"));
     if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess)
         return fail(sv_fail(SV_ERR_CUDA, "cudaStreamCreate failed"));
-
-    sv_es_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->es);
-    if (m->es.valid) {
-        if ((rc = upload_es(m, m->es, m->esdev, &m->d_es_blob)) != SV_OK) return fail(rc);
-        if (sv_es_prepare(m->es.variant_index, m->es.smem_bytes) != 0) {
-            cudaGetLastError();
-            m->es.valid = false; // kernel attribute rejected: keep the generic kernel
-        }
-    }
-    if (m->es.valid && m->es.var.q == 2) { // one-sequence-per-CTA twin for small batches
-        sv_es_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->es1, 1);
-        if (m->es1.valid) {
-            if ((rc = upload_es(m, m->es1, m->esdev1, &m->d_es1_blob)) != SV_OK) return fail(rc);
-            if (sv_es_prepare(m->es1.variant_index, m->es1.smem_bytes) != 0) {
-                cudaGetLastError();
-                m->es1.valid = false;
-            }
-        }
-    }
-    sv_ls_build_plan(m->csr, m->emis, m->start, emits, m->smem_optin, &m->ls);
-    if (m->ls.valid) {
-        if ((rc = upload_ls(m)) != SV_OK) return fail(rc);
-        if (sv_ls_prepare(m->ls.variant_index, m->ls.smem_bytes) != 0) {
-            cudaGetLastError();
-            m->ls.valid = false;
-        }
-    }
+    m->ws_mutex = new (std::nothrow) std::mutex;
+    if (m->ws_mutex == nullptr) return fail(sv_fail(SV_ERR_MEMORY, "sv_model_create: out of host memory"));
+    m->fingerprint = sv_model_fingerprint(m->csr, m->emis, m->start, emits);
+    // K0 plans (ES / lockstep / chain) are built by the first launch that needs them: sv_model_ensure_*
     *out = m;
     return SV_OK;
+    SV_API_END
 }
 
 extern "C" void sv_model_destroy(sv_model* m) {
     if (m == nullptr) return;
+    if (m->refine) { // stop the background search before its inputs go away
+        m->refine->cancel = 1;
+        if (m->refine->th.joinable()) m->refine->th.join();
+        delete m->refine;
+    }
     cudaSetDevice(m->device);
     if (m->d_blob) cudaFree(m->d_blob);
     if (m->d_es_blob) cudaFree(m->d_es_blob);
     if (m->d_es1_blob) cudaFree(m->d_es1_blob);
     if (m->d_ls_blob) cudaFree(m->d_ls_blob);
+    for (void* b : m->retired_blobs) cudaFree(b);
+    if (m->d_chain_blob) cudaFree(m->d_chain_blob);
     if (m->d_pair_blob) cudaFree(m->d_pair_blob);
     if (m->d_path_blob) cudaFree(m->d_path_blob);
-    if (m->d_counter) cudaFree(m->d_counter);
+    if (m->d_counters) cudaFree(m->d_counters);
     if (m->ws.seqs) sv_seqs_destroy(m->ws.seqs);
     if (m->ws.d_out) cudaFree(m->ws.d_out);
     if (m->ws.d_best) cudaFree(m->ws.d_best);
     if (m->ws.d_arg) cudaFree(m->ws.d_arg);
     if (m->stream) cudaStreamDestroy(m->stream);
+    delete static_cast<std::mutex*>(m->ws_mutex);
     delete m;
 }
 
 extern "C" int sv_model_set_kernel(sv_model* m, int kernel) {
+    SV_API_BEGIN
     if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_model_set_kernel: NULL model");
-    if (kernel == SV_KERNEL_ES && !m->es.valid)
-        return sv_fail(SV_ERR_UNSUPPORTED, "model does not fit the edge-stationary kernel");
-    if (kernel == SV_KERNEL_LS && !m->ls.valid)
-        return sv_fail(SV_ERR_UNSUPPORTED, "model does not fit the lockstep kernel");
-    if (kernel < SV_KERNEL_AUTO || kernel > SV_KERNEL_LS)
+    if (kernel < SV_KERNEL_AUTO || kernel > SV_KERNEL_CHAIN)
         return sv_fail(SV_ERR_ARG, "sv_model_set_kernel: unknown kernel");
+    SV_CUDA(cudaSetDevice(m->device));
+    if (kernel == SV_KERNEL_ES && !sv_model_ensure_es(m))
+        return sv_fail(SV_ERR_UNSUPPORTED, "model does not fit the edge-stationary kernel");
+    if (kernel == SV_KERNEL_LS && !sv_model_ensure_ls(m))
+        return sv_fail(SV_ERR_UNSUPPORTED, "model does not fit the lockstep kernel");
+    if (kernel == SV_KERNEL_CHAIN && !sv_model_ensure_chain(m))
+        return sv_fail(SV_ERR_UNSUPPORTED, "model does not have the chain + specials structure");
     m->kernel_pref = kernel;
     return SV_OK;
+    SV_API_END
+}
+
+// Builds every plan now (what sv_model_create did eagerly in version 0.1) and waits for the background
+// refinement of the lockstep plan, so that timings taken afterwards see the final schedule.
+extern "C" int sv_model_prepare(sv_model* m) {
+    SV_API_BEGIN
+    if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_model_prepare: NULL model");
+    SV_CUDA(cudaSetDevice(m->device));
+    sv_model_ensure_chain(m);
+    sv_model_ensure_es(m);
+    sv_model_ensure_es1(m);
+    if (sv_model_ensure_ls(m)) adopt_refined_ls(m, true);
+    return SV_OK;
+    SV_API_END
 }
 
 extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
+    SV_API_BEGIN
     if (m == nullptr || info == nullptr) return sv_fail(SV_ERR_ARG, "sv_model_get_info: NULL");
     std::memset(info, 0, sizeof(*info));
     info->states = m->n;
@@ -360,7 +601,8 @@ extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
     info->nnz = m->nnz;
     info->max_in_degree = m->max_deg;
     info->device = m->device;
-    info->kernel = chosen_kernel(m, m->last_nseq ? m->last_nseq : ~0ull);
+    info->kernel = m->last_kernel; // kernel of the last launch (0 before the first one)
+    info->plan_ms = m->plan_ms;
     if (m->es.valid) {
         info->es_threads = m->es.var.threads;
         info->es_seqs_per_cta = m->es.var.q;
@@ -374,7 +616,7 @@ extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
     }
     if (m->ls.valid) {
         info->ls_threads = m->ls.var.threads;
-        info->ls_seqs_per_cta = 4 * m->ls.var.nq4 * m->ls.var.halves;
+        info->ls_seqs_per_cta = m->last_seqs_per_cta && m->last_kernel == SV_KERNEL_LS ? m->last_seqs_per_cta : 8;
         info->ls_ranks = m->ls.ranks;
         info->ls_heavy_rows = m->ls.n_heavy;
         info->ls_tmem_cols = m->ls.tmem_cols;
@@ -384,8 +626,17 @@ extern "C" int sv_model_get_info(const sv_model* m, sv_model_info* info) {
         info->ls_split_states = m->ls.split_states;
         info->ls_colour_cost_before = m->ls.colour_cost_before;
         info->ls_colour_cost_after = m->ls.colour_cost_after;
+        info->ls_sa_iters = m->ls.sa_iters;
+    }
+    if (m->chain.valid) {
+        info->chain_threads = m->chain.threads;
+        info->chain_states = m->chain.n_chain;
+        info->chain_specials = m->chain.nsp;
+        info->chain_seqs_per_cta = m->last_kernel == SV_KERNEL_CHAIN ? m->last_seqs_per_cta : 0;
+        info->chain_tmem_cols = m->chain.tmem_cols;
     }
     return SV_OK;
+    SV_API_END
 }
 
 extern "C" int sv_model_last_launches(const sv_model* m) { return m ? m->last_launches : 0; }
@@ -574,11 +825,15 @@ int seqs_create_impl(const sv_model* m, const SrcT* symbols, const uint64_t* off
 
 extern "C" int sv_seqs_create(const sv_model* m, const uint64_t* symbols, const uint64_t* offsets,
                               uint64_t nseq, sv_seqs** out) {
+    SV_API_BEGIN
     return seqs_create_impl(m, symbols, offsets, nseq, out);
+    SV_API_END
 }
 extern "C" int sv_seqs_create_u8(const sv_model* m, const uint8_t* symbols,
                                  const uint64_t* offsets, uint64_t nseq, sv_seqs** out) {
+    SV_API_BEGIN
     return seqs_create_impl(m, symbols, offsets, nseq, out);
+    SV_API_END
 }
 extern "C" void sv_seqs_destroy(sv_seqs* s) {
     if (s == nullptr) return;
@@ -652,42 +907,59 @@ int sv_ws_download(sv_model* m, uint64_t nseq, const float* d_out, const float* 
 // ---------------------------------------------------------------- plain path ----
 extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out, float* d_best,
                                  int32_t* d_best_state, void* stream) {
+    SV_API_BEGIN
     if (m == nullptr || seqs == nullptr) return sv_fail(SV_ERR_ARG, "sv_viterbi_device: NULL");
     if (seqs->device != m->device)
         return sv_fail(SV_ERR_ARG, "sv_viterbi_device: sequences live on another device");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SV_CUDA(cudaSetDevice(m->device));
-    SV_CUDA(cudaMemsetAsync(m->d_counter, 0, sizeof(unsigned), st));
+    // a private work-queue counter per launch: launches of one model may overlap on different streams
+    unsigned* counter = m->d_counters + static_cast<size_t>(m->launch_seq++ % SV_COUNTER_RING) * 16;
+    SV_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), st));
     int rc;
     const int kernel = chosen_kernel(m, seqs->nseq);
     m->last_nseq = seqs->nseq;
     m->last_kernel = kernel;
-    if (kernel == SV_KERNEL_LS) {
-        const int q = 4 * m->ls.var.nq4 * m->ls.var.halves;
+    if (kernel == SV_KERNEL_CHAIN) {
+        const int q = chain_q_for(m, seqs->nseq);
+        const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
+        const int grid = static_cast<int>(std::min<int64_t>(want, int64_t(m->sm_count) * m->chain_ctas_per_sm));
+        m->last_seqs_per_cta = q;
+        rc = sv_chain_launch(m->chain.threads, q, m->chaindev, seqs->dev, d_out, d_best, d_best_state, counter, grid,
+                             m->chain_smem[q == 8 ? 3 : q == 4 ? 2 : q == 2 ? 1 : 0], st);
+    } else if (kernel == SV_KERNEL_LS) {
+        // 8 sequences per CTA when that fills every SM, else 4 (twice the CTAs, about half the step time each)
+        int nq4 = seqs->nseq <= static_cast<uint64_t>(4) * m->sm_count ? 1 : 2;
+        if (const char* env = std::getenv("SV_LS_NQ4")) nq4 = std::atoi(env) == 1 ? 1 : 2;
+        const int q = 4 * nq4;
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
         const int grid = static_cast<int>(std::min<int64_t>(want, m->sm_count));
-        rc = sv_ls_launch(m->ls.variant_index, m->lsdev, seqs->dev, d_out, d_best, d_best_state,
-                          m->d_counter, grid, m->ls.smem_bytes, st);
+        m->last_seqs_per_cta = q;
+        rc = sv_ls_launch(m->ls.variant_index, nq4, m->lsdev, seqs->dev, d_out, d_best, d_best_state, counter, grid,
+                          nq4 == 2 ? m->ls.smem_bytes : m->ls.smem_bytes4, st);
     } else if (kernel == SV_KERNEL_ES) {
         // a batch small enough that every sequence gets its own resident CTA runs one sequence per CTA
         // (shorter steps); larger batches advance two sequences per CTA in lockstep
-        const bool solo = m->es1.valid &&
-                          static_cast<int64_t>(seqs->nseq) <=
-                              int64_t(m->sm_count) * std::max(1, sv_es_max_ctas_per_sm(m->es1.variant_index, m->es1.smem_bytes));
+        bool solo = false;
+        if (m->es.var.q == 2 && static_cast<int64_t>(seqs->nseq) <= int64_t(m->sm_count) * 2 && sv_model_ensure_es1(m))
+            solo = static_cast<int64_t>(seqs->nseq) <=
+                   int64_t(m->sm_count) * std::max(1, sv_es_max_ctas_per_sm(m->es1.variant_index, m->es1.smem_bytes));
         const SvEsPlan& pl = solo ? m->es1 : m->es;
         const int per_sm = std::max(1, sv_es_max_ctas_per_sm(pl.variant_index, pl.smem_bytes));
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + pl.var.q - 1) / pl.var.q;
         const int grid = static_cast<int>(std::min<int64_t>(want, int64_t(m->sm_count) * per_sm));
+        m->last_seqs_per_cta = pl.var.q;
         rc = sv_es_launch(pl.variant_index, solo ? m->esdev1 : m->esdev, seqs->dev, d_out, d_best, d_best_state,
-                          m->d_counter, grid, pl.smem_bytes, st);
+                          counter, grid, pl.smem_bytes, st);
     } else {
         const int grid = static_cast<int>(std::min<uint64_t>(seqs->nseq, m->sm_count));
-        rc = sv_generic_launch(m->gen, seqs->dev, d_out, d_best, d_best_state, m->d_counter, grid,
-                               st);
+        m->last_seqs_per_cta = 1;
+        rc = sv_generic_launch(m->gen, seqs->dev, d_out, d_best, d_best_state, counter, grid, st);
     }
     m->last_launches = 1;
     if (rc != 0) return sv_fail(SV_ERR_CUDA, cudaGetErrorString(static_cast<cudaError_t>(rc)));
     return SV_OK;
+    SV_API_END
 }
 
 namespace {
@@ -695,6 +967,7 @@ template <typename SrcT>
 int viterbi_batch_impl(sv_model* m, const SrcT* symbols, const uint64_t* offsets, uint64_t nseq,
                        float* out, float* best, int32_t* best_state) {
     if (m == nullptr) return sv_fail(SV_ERR_ARG, "sv_viterbi_batch: NULL model");
+    std::lock_guard<std::mutex> lock(*static_cast<std::mutex*>(m->ws_mutex)); // one workspace per model
     int rc = sv_ws_upload(m, symbols, offsets, nseq);
     if (rc != SV_OK) return rc;
     float *d_out, *d_best;
@@ -709,16 +982,22 @@ int viterbi_batch_impl(sv_model* m, const SrcT* symbols, const uint64_t* offsets
 
 extern "C" int sv_viterbi_batch(sv_model* m, const uint64_t* symbols, const uint64_t* offsets,
                                 uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    SV_API_BEGIN
     return viterbi_batch_impl(m, symbols, offsets, nseq, out, best, best_state);
+    SV_API_END
 }
 
 extern "C" int sv_viterbi_batch_u8(sv_model* m, const uint8_t* symbols, const uint64_t* offsets,
                                    uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    SV_API_BEGIN
     return viterbi_batch_impl(m, symbols, offsets, nseq, out, best, best_state);
+    SV_API_END
 }
 
 extern "C" int sv_viterbi(sv_model* m, const uint64_t* seq, uint64_t len, float* out) {
+    SV_API_BEGIN
     if (seq == nullptr || out == nullptr) return sv_fail(SV_ERR_ARG, "sv_viterbi: NULL");
     const uint64_t offsets[2] = {0, len};
     return sv_viterbi_batch(m, seq, offsets, 1, out, nullptr, nullptr);
+    SV_API_END
 }

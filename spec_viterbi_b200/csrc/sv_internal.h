@@ -7,12 +7,25 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <exception>
+#include <new>
 #include <string>
 #include <vector>
 
 // ---------------------------------------------------------------- errors ----
 void sv_set_error(const std::string& msg);
 int sv_fail(int code, const std::string& msg);
+
+// Every int-returning extern "C" entry point wraps its body in these: no C++ exception (std::bad_alloc /
+// std::length_error from the std::vector-based planners and readers) may cross the C ABI.
+#define SV_API_BEGIN try {
+#define SV_API_END                                                                               \
+    }                                                                                            \
+    catch (const std::bad_alloc&) { return sv_fail(SV_ERR_MEMORY, "out of host memory"); }      \
+    catch (const std::exception& sv_ex_) {                                                       \
+        return sv_fail(SV_ERR_MEMORY, std::string("internal error: ") + sv_ex_.what());         \
+    }                                                                                            \
+    catch (...) { return sv_fail(SV_ERR_MEMORY, "internal error: unknown C++ exception"); }
 
 #define SV_CUDA(call)                                                                            \
     do {                                                                                         \
@@ -21,6 +34,12 @@ int sv_fail(int code, const std::string& msg);
             return sv_fail(SV_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(sv_e_)); \
         }                                                                                        \
     } while (0)
+
+struct SvHostCsr {
+    uint64_t n = 0;
+    std::vector<uint32_t> rowptr, col;
+    std::vector<float> w;
+};
 
 // ------------------------------------------------------- generic kernel ----
 // Model view for the generic persistent kernel: CSR of the transposed transition
@@ -116,14 +135,21 @@ int sv_es_prepare(int index, size_t smem); // sets the dynamic smem attribute
 constexpr int SV_LS_RSTRIDE = SV_ES_RMAX; // TMEM columns per symbol (one per rank) of the 5-rank variants
 constexpr int SV_LS_RMAX = 10;            // rank capacity of any lockstep variant
 
+// A variant = a register staircase; each is compiled for 8 (nq4 = 2) and 4 (nq4 = 1) sequences per
+// CTA, and the launch picks nq4 from the batch size (the register images do not depend on it).
 struct SvLsVariant {
-    int threads;                 // threads that share one set of rows (a CTA, or one HALF of a CTA)
-    int nq4;                     // float4 groups of sequences per set: Q = 4 * nq4
+    int threads;                 // threads per CTA
     int shape[SV_LS_RMAX];       // max register slots per rank
     int nh;                      // heavy rows supported
     int hs;                      // register slots per heavy row per thread
-    int ranks;                   // rows per thread (5 or 10)
-    int halves;                  // independent thread sets per CTA (1, or 2 with their own barriers)
+    int ranks;                   // rows per thread
+};
+
+// Knobs of one K0 run for the lockstep kernel.
+struct SvLsPlanOpts {
+    uint64_t sa_iters = 0;               // bank-colouring search length (0 = the full default)
+    const volatile int* cancel = nullptr; // polled by the search: non-zero = give up (plan stays invalid)
+    int threads = 1;                     // host threads for the per-octet slot assignment
 };
 
 struct SvLsPlan {
@@ -135,7 +161,10 @@ struct SvLsPlan {
     int n_pad = 0;    // positions per score buffer (n_lpad + heavy, rounded up to 8)
     int n_heavy = 0, nslots = 0, ranks = 0, tmem_cols = 0;
     bool nonneg = false; // every finite score is >= 0 (or -0): float order == signed-int order
-    uint64_t gather_wavefronts = 0, gather_ideal = 0, smem_bytes = 0, split_states = 0;
+    uint64_t gather_wavefronts = 0, gather_ideal = 0, split_states = 0;
+    uint64_t smem_bytes = 0;  // dynamic shared memory of the 8-sequence launch (nq4 = 2)
+    uint64_t smem_bytes4 = 0; // ... of the 4-sequence launch (nq4 = 1)
+    uint64_t sa_iters = 0;    // length of the colouring search that produced this plan
     uint64_t colour_cost_before = 0, colour_cost_after = 0; // excess bank-group loads (K0 search)
     std::vector<float> edge_w;       // [nslots][threads]
     std::vector<uint32_t> edge_off;  // [nslots][threads] byte offset of v[src] in a buffer: p * 16
@@ -162,17 +191,61 @@ struct SvLsDev {
 
 int sv_ls_num_variants();
 const SvLsVariant& sv_ls_variant(int index);
-int sv_ls_prepare(int index, size_t smem);
-int sv_ls_launch(int index, const SvLsDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+int sv_ls_prepare(int index, int nq4, size_t smem);
+int sv_ls_launch(int index, int nq4, const SvLsDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
                  int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
 
-// ----------------------------------------------------------- host model ----
-struct SvHostCsr {
-    uint64_t n = 0;
-    std::vector<uint32_t> rowptr, col;
-    std::vector<float> w;
+// ------------------------------------------------------------- chain kernel ----
+// Register-resident step for "chain + specials" models -- the structure of every profile HMM the
+// reference ships (chmm_files/silent_hmm_to_chmm.py:118-144): after removing at most two SPECIAL
+// states (N and C: fed by / feeding every match state) the transition graph is a union of simple
+// paths.  A thread owns SV_CHAIN_RPT consecutive chain positions of Q sequences IN REGISTERS; the
+// band edge comes from the neighbouring register (or one shuffle), the hub state (special 0) is a
+// broadcast, and a special row whose chain in-edges all carry one weight u needs only the minimum
+// over the chain, because fl(c + x) is monotone:  min_k fl(fl(E+u) + v[k]) = fl(fl(E+u) + min_k v[k]).
+// No per-relaxation shared-memory gather is left, so the kernel is FP32-issue bound.
+constexpr int SV_CHAIN_RPT = 5;  // chain positions per thread (= TMEM columns per symbol)
+constexpr int SV_CHAIN_NSP = 2;  // special states supported
+
+struct SvChainPlan {
+    bool valid = false;
+    int threads = 0;   // CTA size: 128, 256 or 512
+    int n_chain = 0;   // chain states (positions 0 .. n_chain-1; the rest up to n_pos are padding)
+    int n_pos = 0;     // threads * SV_CHAIN_RPT
+    int nsp = 0;       // special states
+    int tmem_cols = 0;
+    bool nonneg = false;
+    uint32_t special[SV_CHAIN_NSP] = {0, 0};       // original ids
+    float u[SV_CHAIN_NSP];                          // weight of every chain -> special s edge (+inf: none)
+    float ss[SV_CHAIN_NSP][SV_CHAIN_NSP];           // ss[s][s2] = weight of special s2 -> special s
+    float start_s[SV_CHAIN_NSP];
+    std::vector<float> w_pred, w_hub;               // [n_pos] weight of (p-1) -> p and of special 0 -> p
+    std::vector<float> emis_p, start_p;             // [emits][n_pos], [n_pos]
+    std::vector<float> emis_s;                      // [NSP][emits]
+    std::vector<int32_t> orig_of_pos;               // [n_pos] original state, -1 = padding
 };
 
+struct SvChainDev {
+    int n = 0, n_pos = 0, emits = 0, nsp = 0, tmem_cols = 0, nonneg = 0;
+    int special[SV_CHAIN_NSP] = {-1, -1};
+    float u[SV_CHAIN_NSP], ss[SV_CHAIN_NSP][SV_CHAIN_NSP], start_s[SV_CHAIN_NSP];
+    const float* w_pred = nullptr;
+    const float* w_hub = nullptr;
+    const float* emis_p = nullptr;
+    const float* start_p = nullptr;
+    const float* emis_s = nullptr;
+    const int32_t* orig_of_pos = nullptr;
+};
+
+// K0 (sv_chain_plan.cpp): detects the structure; plan.valid = false if the model does not have it.
+void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, const std::vector<float>& start,
+                         uint64_t emits, SvChainPlan* plan);
+// sequences per CTA that are compiled: 8, 4, 2, 1
+int sv_chain_prepare(int threads, int q, size_t* smem_out, int* ctas_per_sm_out);
+int sv_chain_launch(int threads, int q, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+                    int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
+
+// ----------------------------------------------------------- host model ----
 struct sv_seqs;
 // Reusable buffers behind the host-pointer entry points (sv_viterbi*, sv_spec_run*).
 struct SvWorkspace {
@@ -184,18 +257,31 @@ struct SvWorkspace {
     size_t best_cap = 0; // sequences
 };
 
+// Background refinement of the lockstep plan (sv_api.cu): the first batch runs on a short colouring
+// search; the full-length search continues on a host thread and its plan is swapped in (and written
+// to the plan cache) when it is ready.
+struct SvLsRefine;
+
+constexpr int SV_COUNTER_RING = 64; // work-queue counters, one per launch in flight
+
 struct sv_model {
     int device = 0;
     int sm_count = 0;
     size_t smem_optin = 0;
     uint64_t n = 0, emits = 0, nnz = 0, max_deg = 0;
+    uint64_t fingerprint = 0;
     SvHostCsr csr;
     std::vector<float> emis;  // [emits][n]
     std::vector<float> start; // [n]
     // generic kernel device data
     SvGenericDev gen;
     void* d_blob = nullptr; // single allocation backing all device arrays
-    unsigned* d_counter = nullptr;
+    // Persistent kernels pull sequences from a global counter.  Every launch takes the next counter of
+    // a ring, so launches of one model that overlap on different streams never share a queue.
+    unsigned* d_counters = nullptr; // [SV_COUNTER_RING], 64 bytes apart
+    unsigned launch_seq = 0;
+    // K0 plans are built on first use (a level >= 2 spec_with never needs them)
+    int es_state = 0, es1_state = 0, ls_state = 0, chain_state = 0; // 0 = not tried, 1 = ready, -1 = does not fit
     // edge-stationary plan
     SvEsPlan es;
     SvEsDev esdev;
@@ -209,9 +295,17 @@ struct sv_model {
     SvLsPlan ls;
     SvLsDev lsdev;
     void* d_ls_blob = nullptr;
+    std::vector<void*> retired_blobs; // plans replaced by the background refinement (kernels may still read them)
+    SvLsRefine* refine = nullptr;
+    // chain plan (profile HMMs: sv_chain_plan.cpp / sv_plain_chain.cu)
+    SvChainPlan chain;
+    SvChainDev chaindev;
+    void* d_chain_blob = nullptr;
+    size_t chain_smem[4] = {0, 0, 0, 0}; // dynamic shared memory of the Q = 1, 2, 4, 8 instantiations
+    int chain_ctas_per_sm = 1;
     // level-2 pair precompute (sv_spec.cu): dense copies of the heavy rows + CSC, built on first use
     void* d_pair_blob = nullptr;
-    void* d_path_blob = nullptr; // K4i/K4p: flattened two-step paths (sv_spec.cu: path_prepare)
+    void* d_path_blob = nullptr; // K4i: flattened two-step paths (sv_spec.cu: path_prepare)
     int path_state = 0;          // 0 = not built, 1 = ready, -1 = not eligible
     int path_slots = 0, path_heavy_total = 0;
     unsigned path_used_mask = 0; // dense rows that some row has a finite edge from (only those are staged)
@@ -219,11 +313,20 @@ struct sv_model {
     int kernel_pref = SV_KERNEL_AUTO;
     int last_launches = 0;
     int last_kernel = 0;
+    int last_seqs_per_cta = 0;
     uint64_t last_nseq = 0;
-    // scratch for host-buffer entry points
+    double plan_ms = 0; // host time spent in K0 planners so far (reported by sv_model_get_info)
+    // scratch for host-buffer entry points (single flight: the host-buffer calls of one model serialise)
     cudaStream_t stream = nullptr;
     SvWorkspace ws;
+    void* ws_mutex = nullptr; // std::mutex
 };
+
+// Plans are lazy: these build (once) and upload the plan a kernel needs; false = the model does not fit it.
+bool sv_model_ensure_es(sv_model* m);
+bool sv_model_ensure_es1(sv_model* m);
+bool sv_model_ensure_ls(sv_model* m);
+bool sv_model_ensure_chain(sv_model* m);
 
 struct sv_seqs {
     int device = 0;
@@ -253,7 +356,15 @@ void sv_es_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
 // K0 for the lockstep kernel (sv_ls_plan.cpp); plan.valid=false if the model does not fit.
 void sv_ls_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
                       const std::vector<float>& start, uint64_t emits, size_t smem_limit,
-                      SvLsPlan* plan);
+                      SvLsPlan* plan, const SvLsPlanOpts& opts = SvLsPlanOpts());
+uint64_t sv_ls_default_sa_iters(uint64_t states);
+
+// Plan cache (sv_plan_cache.cpp): the finished lockstep plan of a model, keyed by a fingerprint of
+// T', the emissions and the start column, kept on disk across processes.
+uint64_t sv_model_fingerprint(const SvHostCsr& csr, const std::vector<float>& emis,
+                              const std::vector<float>& start, uint64_t emits);
+bool sv_plan_cache_load(uint64_t fingerprint, SvLsPlan* plan);
+void sv_plan_cache_store(uint64_t fingerprint, const SvLsPlan& plan);
 
 // generic kernel launcher (sv_plain_generic.cu)
 int sv_generic_launch(const SvGenericDev& m, const SvSeqsDev& s, float* d_out, float* d_best,

@@ -28,6 +28,7 @@
 #include <limits>
 #include <numeric>
 #include <random>
+#include <thread>
 
 namespace {
 
@@ -272,7 +273,7 @@ void apply_swap_delta(Colouring& c, uint32_t pa, uint32_t pb, const SwapDelta& s
 
 // Simulated annealing over position swaps; keeps every row inside a cell whose trip count
 // covers its in-degree.  Deterministic (fixed seed).
-void anneal(Colouring& c, uint64_t iters, uint64_t seed) {
+void anneal(Colouring& c, uint64_t iters, uint64_t seed, const volatile int* cancel) {
     const LGraph& g = *c.g;
     if (c.cost == 0 || iters == 0) return;
     Rng rng(seed);
@@ -285,7 +286,10 @@ void anneal(Colouring& c, uint64_t iters, uint64_t seed) {
     if (const char* e1 = std::getenv("SV_LS_SA_T1")) t1 = std::atof(e1);
     double temp = t0;
     for (uint64_t it = 0; it < iters && c.cost > 0; ++it) {
-        if ((it & 255u) == 0) temp = t0 * std::pow(t1 / t0, static_cast<double>(it) / static_cast<double>(iters));
+        if ((it & 255u) == 0) {
+            temp = t0 * std::pow(t1 / t0, static_cast<double>(it) / static_cast<double>(iters));
+            if (cancel != nullptr && *cancel != 0) return;
+        }
         // pick a row to move: an end of an edge sitting in an over-full (octet, colour), taken
         // from the explicit list of over-full cells (every iteration is a useful attempt)
         uint32_t pa;
@@ -416,9 +420,9 @@ namespace {
 
 bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
                     const std::vector<float>& start, uint64_t emits, size_t smem_limit, int vindex,
-                    uint64_t sa_iters, SvLsPlan* plan) {
+                    uint64_t sa_iters, const SvLsPlanOpts& opts, SvLsPlan* plan) {
     const SvLsVariant& var = sv_ls_variant(vindex);
-    const int TPG = var.threads, NW = TPG / 32, Q = 4 * var.nq4;
+    const int TPG = var.threads, NW = TPG / 32;
     const size_t n = csr.n;
     const size_t cap = var.shape[0];
     const int R = var.ranks;
@@ -477,8 +481,10 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     // (static layout: every float4 group is sized for the largest model the variant takes)
     const size_t npad_max = static_cast<size_t>(R) * TPG + 8;
     if (static_cast<size_t>(n_pad) > npad_max) return false;
-    const size_t smem = static_cast<size_t>(2) * var.nq4 * var.halves * npad_max * 16 +
-                        static_cast<size_t>(var.nh) * NW * Q * 4;
+    auto smem_for = [&](int nq4) {
+        return static_cast<size_t>(2) * nq4 * npad_max * 16 + static_cast<size_t>(var.nh) * NW * (4 * nq4) * 4;
+    };
+    const size_t smem = smem_for(2);
     if (smem + 1024 > smem_limit) return false;
 
     // ---- placement: degree-sorted light rows -> cells of 32, snake order over warps ----
@@ -548,8 +554,10 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     col.hot_at.assign(col.cnt.size(), -1);
     for (uint32_t e = 0; e < g.edges.size(); ++e) col.apply_edge(e, +1);
     plan->colour_cost_before = static_cast<uint64_t>(col.cost);
-    anneal(col, sa_iters, 0x5eed0000ull + n * 131u + vindex);
+    anneal(col, sa_iters, 0x5eed0000ull + n * 131u + vindex, opts.cancel);
+    if (opts.cancel != nullptr && *opts.cancel != 0) return false;
     plan->colour_cost_after = static_cast<uint64_t>(col.cost);
+    plan->sa_iters = sa_iters;
 
     // ---- slot assignment per octet, register images ----
     int base[SV_LS_RMAX + 1];
@@ -560,11 +568,16 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->edge_w.assign(static_cast<size_t>(NSL) * TPG, kInf);
     plan->edge_off.assign(static_cast<size_t>(NSL) * TPG, 0);
     uint64_t wavefronts = 0, ideal = 0;
-    Rng rng(977u + n);
-    for (int r = 0; r < nranks; ++r) {
-        for (int w = 0; w < NW; ++w) {
-            const int D = deg[static_cast<size_t>(w) * R + r];
-            for (int o = 0; o < 4; ++o) {
+    {
+        // one task per (rank, warp, octet); tasks are independent (each writes its own 8 threads' slots of
+        // its own rank) and seeded by their index, so the result does not depend on the thread count
+        const int ntask = nranks * NW * 4;
+        std::vector<uint32_t> task_wf(ntask, 0), task_ideal(ntask, 0);
+        auto run_tasks = [&](int t0, int t1) {
+            for (int task = t0; task < t1; ++task) {
+                const int r = task / (NW * 4), w = (task / 4) % NW, o = task % 4;
+                const int D = deg[static_cast<size_t>(w) * R + r];
+                Rng rng(977u + n * 4099u + static_cast<uint64_t>(task));
                 const int p0 = r * TPG + w * 32 + o * 8;
                 std::vector<std::vector<OEdge>> rows(8);
                 for (int l = 0; l < 8; ++l) {
@@ -574,8 +587,8 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
                         rows[l].push_back(OEdge{col.pos_of[g.edges[e].src], g.edges[e].w});
                 }
                 int32_t tab[8][8];
-                if (D > 0) wavefronts += static_cast<uint64_t>(assign_octet(rows, D, tab, rng));
-                ideal += static_cast<uint64_t>(D);
+                if (D > 0) task_wf[task] = static_cast<uint32_t>(assign_octet(rows, D, tab, rng));
+                task_ideal[task] = static_cast<uint32_t>(D);
                 for (int s = 0; s < D; ++s) {
                     // padded lanes re-read an address of this slot (broadcast, no extra wavefront)
                     uint32_t filler = static_cast<uint32_t>(p0);
@@ -593,6 +606,20 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
                     }
                 }
             }
+        };
+        const int nthr = std::max(1, std::min(opts.threads, ntask));
+        if (nthr == 1) {
+            run_tasks(0, ntask);
+        } else {
+            std::vector<std::thread> pool;
+            for (int k = 0; k < nthr; ++k)
+                pool.emplace_back(run_tasks, static_cast<int>(static_cast<int64_t>(ntask) * k / nthr),
+                                  static_cast<int>(static_cast<int64_t>(ntask) * (k + 1) / nthr));
+            for (auto& th : pool) th.join();
+        }
+        for (int task = 0; task < ntask; ++task) {
+            wavefronts += task_wf[task];
+            ideal += task_ideal[task];
         }
     }
     // heavy rows: sources sorted by position and dealt round-robin: consecutive lanes read
@@ -668,6 +695,7 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->gather_wavefronts = wavefronts;
     plan->gather_ideal = ideal;
     plan->smem_bytes = smem;
+    plan->smem_bytes4 = smem_for(1);
     plan->split_states = n_int - n;
     plan->deg = deg;
     // Sums of scores that are all >= 0 (or -0) stay >= 0, so their float order is the signed-int
@@ -685,25 +713,25 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
 
 } // namespace
 
+uint64_t sv_ls_default_sa_iters(uint64_t states) {
+    uint64_t sa_iters = std::min<uint64_t>(8000000ull, 3300ull * states);
+    if (const char* env = std::getenv("SV_LS_SA_ITERS")) sa_iters = std::strtoull(env, nullptr, 10);
+    return sa_iters;
+}
+
 void sv_ls_build_plan(const SvHostCsr& csr, const std::vector<float>& emis,
                       const std::vector<float>& start, uint64_t emits, size_t smem_limit,
-                      SvLsPlan* plan) {
+                      SvLsPlan* plan, const SvLsPlanOpts& opts) {
     plan->valid = false;
-    int want_nq4 = 0;
-    if (const char* env = std::getenv("SV_LS_NQ4")) want_nq4 = std::atoi(env);
-    int max_halves = 1; // two-halves variants are opt-in (SV_LS_HALVES=2)
-    if (const char* env = std::getenv("SV_LS_HALVES")) max_halves = std::atoi(env);
-    uint64_t sa_iters = std::min<uint64_t>(8000000ull, 3300ull * csr.n);
-    if (const char* env = std::getenv("SV_LS_SA_ITERS")) sa_iters = std::strtoull(env, nullptr, 10);
+    const uint64_t sa_iters = opts.sa_iters ? opts.sa_iters : sv_ls_default_sa_iters(csr.n);
     // variants are listed in order of preference; the first that fits wins
     for (int v = 0; v < sv_ls_num_variants(); ++v) {
-        if (want_nq4 != 0 && sv_ls_variant(v).nq4 != want_nq4) continue;
-        if (sv_ls_variant(v).halves > max_halves) continue;
         SvLsPlan cand;
-        if (ls_try_variant(csr, emis, start, emits, smem_limit, v, sa_iters, &cand)) {
+        if (ls_try_variant(csr, emis, start, emits, smem_limit, v, sa_iters, opts, &cand)) {
             *plan = std::move(cand);
             return;
         }
+        if (opts.cancel != nullptr && *opts.cancel != 0) return;
     }
 }
 
@@ -719,6 +747,7 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
                                     const float* trans_w, const float* emissions, uint64_t nstart,
                                     const uint64_t* start_cols, const float* start_w,
                                     const uint64_t* seq, uint64_t len, float* out, uint64_t stats[12]) {
+    SV_API_BEGIN
     if (states == 0 || emits == 0 || stats == nullptr) return sv_fail(SV_ERR_ARG, "sv_k0_lockstep_check: bad argument");
     // CSR of T' with FIRST-wins duplicates (same rule as sv_model_create)
     SvHostCsr csr;
@@ -753,13 +782,15 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
         }
     }
     SvLsPlan plan;
-    sv_ls_build_plan(csr, emis, start, emits, 227 * 1024, &plan);
+    SvLsPlanOpts opts;
+    opts.threads = static_cast<int>(std::max(1u, std::min(8u, std::thread::hardware_concurrency())));
+    sv_ls_build_plan(csr, emis, start, emits, 227 * 1024, &plan, opts);
     std::memset(stats, 0, 12 * sizeof(uint64_t));
     stats[0] = plan.valid ? 1 : 0;
     if (!plan.valid) return SV_OK;
     const int TPG = plan.var.threads, NW = TPG / 32;
     stats[1] = TPG;
-    stats[2] = 4 * plan.var.nq4 * plan.var.halves;
+    stats[2] = 8;
     stats[3] = plan.ranks;
     stats[4] = plan.n_heavy;
     stats[5] = plan.split_states;
@@ -811,4 +842,5 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
         out[i] = x;
     }
     return SV_OK;
+    SV_API_END
 }

@@ -1,0 +1,467 @@
+// Chain kernel for sm_100a: the plain (min,+) Viterbi step for "chain + specials" models (every
+// profile HMM the reference ships), with the state vectors of Q sequences held in REGISTERS.
+//
+//   v_t[i] = min_j fl(fl(E[o_t][i] + T'[i][j]) + v_{t-1}[j])          (GraphBLAS_impl.cpp:59,64-73)
+//
+// One persistent CTA walks all time steps of Q = 8 / 4 / 2 / 1 sequences in lockstep:
+//   * a thread owns SV_CHAIN_RPT = 5 consecutive chain positions; v_{t-1} of its positions for all Q
+//     sequences lives in registers and is updated in place from the highest position down, so the
+//     band edge (p-1) -> p is a register read; only rank 0 needs the neighbouring lane (one SHFL per
+//     sequence and step; lane 0 takes the previous warp's last score from shared memory);
+//   * the hub state's score (special 0, the N state) is a broadcast shared-memory read;
+//   * the two dense rows (N and C) need only min_k v[k] over the chain because all their chain
+//     in-edges carry one weight (K0 checks it): fl(c + x) is monotone, so
+//     min_k fl(fl(E+u) + v[k]) == fl(fl(E+u) + min_k v[k]) bit for bit.  Each thread folds its five
+//     new scores into a running minimum, one integer REDUX per sequence reduces it over the warp
+//     (all scores >= 0: float order = signed-int order), warp w < Q finishes sequence w's two
+//     special rows in the NEXT step from the per-warp partials -- one barrier per step;
+//   * the emission table lives in TENSOR MEMORY (lane = thread's lane in its warp quadrant, column =
+//     (warp group, symbol, rank)); E[o][own positions] is one tcgen05.ld.x4 + .x1 with a run-time
+//     column, issued one sequence ahead of its use;
+//   * sequence managers (lane q of the last warp) stream the symbols and publish a control block two
+//     steps ahead, exactly as in the lockstep kernel (sv_plain_ls.cu); finished sequences are
+//     written out with their (best, argmin) and replaced from a global longest-first queue.
+//
+// Per (position, sequence) and step: 4 FADD + 1 FMNMX + 0.4 FMNMX3 for FOUR transitions -- no
+// per-relaxation shared-memory traffic is left, so the kernel is bound by FP32 issue.
+// Tensor cores are not used ((min,+) is not an MMA contraction); only their memory is.
+#include "sv_ls_device.cuh"
+
+namespace {
+
+constexpr int kChainHeStride = 256 * SV_CHAIN_RPT; // special-row emissions indexed by symbol * RPT
+
+template <int TPG, int Q>
+__global__ void __launch_bounds__(TPG, 512 / TPG)
+sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict__ best,
+                int32_t* __restrict__ arg, unsigned* __restrict__ counter) {
+    constexpr int NW = TPG / 32;
+    constexpr int MW = NW - 1; // manager warp (its chain positions are mostly padding)
+    constexpr int R = SV_CHAIN_RPT;
+    constexpr int RS = SV_CHAIN_RPT;
+    constexpr int QS = 8; // stride of the per-sequence shared arrays
+    static_assert(R == 5 && Q <= 8 && NW <= 32, "layout");
+
+    __shared__ LsCtl ctl[4];
+    __shared__ LsMgr mgr[8];
+    __shared__ uint32_t s_taddr;
+    __shared__ __align__(16) float s_red[2][NW][QS]; // [parity][warp][q] chain minimum of the warp
+    __shared__ __align__(16) float s_bnd[2][NW][QS]; // [parity][warp][q] score at the warp's last position
+    __shared__ __align__(16) float s_vs[2][SV_CHAIN_NSP][QS]; // [parity][special][q]
+    __shared__ float s_he[SV_CHAIN_NSP * kChainHeStride];
+    __shared__ float s_bv[NW];
+    __shared__ int s_bi[NW];
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // provably warp-uniform
+    const unsigned long long* __restrict__ sym64 = static_cast<const unsigned long long*>(s.sym);
+    const int n_pos = m.n_pos;
+
+    // ---- one-time: tensor memory <- emission table; registers <- this thread's weights ----
+    if (warp == 0) tmem_alloc(&s_taddr, static_cast<uint32_t>(m.tmem_cols));
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = s_taddr;
+    const uint32_t tE = tbase + (static_cast<uint32_t>(warp & 3) << 21) +
+                        static_cast<uint32_t>(warp >> 2) * static_cast<uint32_t>(m.emits * RS);
+    for (int o = 0; o < m.emits; ++o)
+        for (int r = 0; r < R; ++r)
+            tmem_st1(tE + static_cast<uint32_t>(o * RS + r), m.emis_p[static_cast<size_t>(o) * n_pos + tid * R + r]);
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    for (int i = tid; i < SV_CHAIN_NSP * m.emits; i += TPG) {
+        const int h = i / m.emits, o = i % m.emits;
+        s_he[h * kChainHeStride + o * RS] = m.emis_s[i];
+    }
+    for (int i = tid; i < 2 * NW * QS; i += TPG) {
+        (&s_red[0][0][0])[i] = pos_inf();
+        (&s_bnd[0][0][0])[i] = pos_inf();
+    }
+    if (tid < 2 * SV_CHAIN_NSP * QS) (&s_vs[0][0][0])[tid] = pos_inf();
+
+    float wp[R], wh[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        wp[r] = m.w_pred[tid * R + r];
+        wh[r] = m.w_hub[tid * R + r];
+    }
+    // special rows: lane s of a warp finishes special s
+    // (no run-time indexing into the kernel parameters: that would move the whole struct to local memory)
+    static_assert(SV_CHAIN_NSP == 2, "two specials");
+    const bool sp1 = lane == 1;
+    const float sp_u = sp1 ? m.u[1] : m.u[0], sp_s0 = sp1 ? m.ss[1][0] : m.ss[0][0];
+    const float sp_s1 = sp1 ? m.ss[1][1] : m.ss[0][1], sp_start = sp1 ? m.start_s[1] : m.start_s[0];
+    const bool nonneg = m.nonneg != 0;
+    const float* __restrict__ start_p = m.start_p + tid * R;
+
+    float v[Q][R];
+#pragma unroll
+    for (int q = 0; q < Q; ++q)
+#pragma unroll
+        for (int r = 0; r < R; ++r) v[q][r] = pos_inf();
+
+    // ---- sequence managers: identical protocol to the lockstep kernel (control blocks two steps ahead) ----
+    unsigned long long mg_cur = 0, mg_nxt = 0;
+    const unsigned long long* mg_ptr = sym64;
+    uint32_t mg_pos = 0, mg_t = 0, mg_len = 0;
+    auto next_symbol = [&]() -> uint32_t {
+        const uint32_t sym = static_cast<uint32_t>(mg_cur >> ((mg_pos & 7u) * 8u)) & 0xffu;
+        if ((++mg_pos & 7u) == 0) {
+            mg_cur = mg_nxt;
+            mg_nxt = *mg_ptr++;
+        }
+        return sym;
+    };
+    auto refill = [&](uint32_t mask, LsCtl& d0, LsCtl& d1, bool fresh) {
+        bool started = false, one = false, second = false, two = false;
+        uint32_t col0 = 0, col1 = 0;
+        if (lane < Q && ((mask >> lane) & 1u)) {
+            mg_len = 0;
+            mg_t = 0;
+            uint32_t sid = 0;
+            const unsigned w = atomicAdd(counter, 1u);
+            if (w < static_cast<unsigned>(s.nseq)) {
+                sid = s.order[w];
+                const uint64_t b = s.off[sid];
+                mg_len = static_cast<uint32_t>(s.off[sid + 1] - b);
+                mg_ptr = sym64 + (b >> 3);
+                mg_cur = *mg_ptr++;
+                mg_nxt = *mg_ptr++;
+                mg_pos = static_cast<uint32_t>(b & 7u);
+                col0 = next_symbol() * RS;
+                started = true;
+                one = mg_len == 1;
+                if (mg_len > 1) {
+                    col1 = next_symbol() * RS;
+                    second = true;
+                    two = mg_len == 2;
+                    mg_t = 1;
+                }
+            }
+            mgr[lane].sid = sid;
+        }
+        const uint32_t startm = __ballot_sync(0xffffffffu, started);
+        const uint32_t onem = __ballot_sync(0xffffffffu, one);
+        const uint32_t secm = __ballot_sync(0xffffffffu, second);
+        const uint32_t twom = __ballot_sync(0xffffffffu, two);
+        if (lane < 8 && (fresh || (lane < Q && ((mask >> lane) & 1u)))) {
+            d0.col[lane] = col0;
+            d1.col[lane] = col1;
+        }
+        if (lane == 0) {
+            if (fresh) {
+                d0.init_mask = startm; d0.fin_mask = onem; d0.any_act = startm;
+                d1.init_mask = 0;      d1.fin_mask = twom; d1.any_act = secm;
+            } else {
+                d0.init_mask |= startm; d0.fin_mask |= onem; d0.any_act |= startm;
+                d1.fin_mask |= twom;    d1.any_act |= secm;
+            }
+        }
+        __syncwarp();
+    };
+    if (warp == MW) refill((1u << Q) - 1u, ctl[0], ctl[1], true);
+    __syncthreads();
+
+    // flags and TMEM columns of the coming step, fetched before the barrier that ends the current one
+    uint4 fl, cA, cB;
+    uint32_t eA[5], eB[5]; // E[o_q][own positions], double buffered over q
+    auto prefetch_step = [&](const LsCtl& nc) {
+        fl = *reinterpret_cast<const uint4*>(&nc.init_mask);
+        cA = *reinterpret_cast<const uint4*>(&nc.col[0]);
+        cB = *reinterpret_cast<const uint4*>(&nc.col[4]);
+        tmem_ld5(tE + cA.x, eA);
+    };
+    prefetch_step(ctl[0]);
+
+    uint32_t tau = 0;
+    for (;;) {
+        const uint32_t init_mask = fl.x, fin_mask = fl.y, act = fl.z;
+        if (act == 0) break;
+        const uint32_t bo = tau & 1u, bi = bo ^ 1u; // buffers written / read in this step
+        const uint32_t cols[8] = {cA.x, cA.y, cA.z, cA.w, cB.x, cB.y, cB.z, cB.w};
+
+        // ---- managers: control block of step tau + 2 ----
+        if (warp == MW) {
+            LsCtl& nx = ctl[(tau + 2u) & 3u];
+            bool cont = false, last = false;
+            uint32_t colv = 0;
+            if (lane < Q && mg_t + 1u < mg_len) {
+                cont = true;
+                colv = next_symbol() * RS;
+                last = mg_t + 2u == mg_len;
+                ++mg_t;
+            }
+            const uint32_t contm = __ballot_sync(0xffffffffu, cont);
+            const uint32_t lastm = __ballot_sync(0xffffffffu, last);
+            if (lane < 8) nx.col[lane] = colv;
+            if (lane == 0) {
+                nx.init_mask = 0;
+                nx.fin_mask = lastm;
+                nx.any_act = contm;
+            }
+        }
+
+        // ---- special rows of step tau: warp w finishes sequences w, w + NW, .. from the partial minima
+        //      and special scores of step tau - 1 ----
+#pragma unroll
+        for (int q0 = 0; q0 < Q; q0 += NW) {
+            const int q = q0 + warp;
+            if (q < Q && ((act >> q) & 1u)) {
+                float mm = lane < NW ? s_red[bi][lane][q] : pos_inf();
+                if (nonneg) {
+                    mm = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(mm)));
+                } else {
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) mm = fminf(mm, __shfl_xor_sync(0xffffffffu, mm, d));
+                }
+                if (lane < SV_CHAIN_NSP) {
+                    const float e = s_he[lane * kChainHeStride + ctl[tau & 3u].col[q]];
+                    float x = relax1(e, sp_u, mm);
+                    x = fminf(x, fminf(relax1(e, sp_s0, s_vs[bi][0][q]), relax1(e, sp_s1, s_vs[bi][1][q])));
+                    if ((init_mask >> q) & 1u) x = e + sp_start;
+                    s_vs[bo][lane][q] = x;
+                }
+            }
+        }
+
+        // ---- chain positions ----
+        float redv[Q], bndv[Q];
+        auto seq_step = [&](auto qc) {
+            constexpr int q = decltype(qc)::value;
+            uint32_t(&ec)[5] = (q & 1) ? eB : eA;
+            uint32_t(&en)[5] = (q & 1) ? eA : eB;
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]));
+            if constexpr (q + 1 < Q) tmem_ld5(tE + cols[q + 1 < Q ? q + 1 : 0], en);
+            redv[q] = pos_inf();
+            bndv[q] = pos_inf();
+            if ((act >> q) & 1u) {
+                const float hub = s_vs[bi][0][q];
+                float pv = __shfl_up_sync(0xffffffffu, v[q][R - 1], 1);
+                const float wb = warp > 0 ? s_bnd[bi][warp > 0 ? warp - 1 : 0][q] : pos_inf();
+                if (lane == 0) pv = wb;
+                float e[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) e[r] = __uint_as_float(ec[r]);
+#pragma unroll
+                for (int r = R - 1; r >= 0; --r) {
+                    const float prev = r > 0 ? v[q][r - 1] : pv;
+                    v[q][r] = fminf(relax1(e[r], wp[r], prev), relax1(e[r], wh[r], hub));
+                }
+                float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
+                mq = fminf(mq, fminf(v[q][3], v[q][4]));
+                if (nonneg) {
+                    mq = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(mq)));
+                } else {
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) mq = fminf(mq, __shfl_xor_sync(0xffffffffu, mq, d));
+                }
+                redv[q] = mq;
+                bndv[q] = v[q][R - 1];
+            }
+        };
+        seq_step(std::integral_constant<int, 0>{});
+        if constexpr (Q > 1) seq_step(std::integral_constant<int, 1>{});
+        if constexpr (Q > 2) {
+            seq_step(std::integral_constant<int, 2>{});
+            seq_step(std::integral_constant<int, 3>{});
+        }
+        if constexpr (Q > 4) {
+            seq_step(std::integral_constant<int, 4>{});
+            seq_step(std::integral_constant<int, 5>{});
+            seq_step(std::integral_constant<int, 6>{});
+            seq_step(std::integral_constant<int, 7>{});
+        }
+        // ---- rare: first step of a sequence, v_0 = E[o_0] + start replaces the relaxed scores (a real
+        //      branch around everything, so the hot path carries no predicated loads) ----
+        if (init_mask != 0) {
+            auto init_fix = [&](auto qc) {
+                constexpr int q = decltype(qc)::value;
+                if (!((init_mask >> q) & 1u)) return;
+                const float* __restrict__ em = m.emis_p + static_cast<size_t>(cols[q] / RS) * n_pos + tid * R;
+#pragma unroll
+                for (int r = 0; r < R; ++r) v[q][r] = em[r] + start_p[r];
+                float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
+                mq = fminf(mq, fminf(v[q][3], v[q][4]));
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) mq = fminf(mq, __shfl_xor_sync(0xffffffffu, mq, d));
+                redv[q] = mq;
+                bndv[q] = v[q][R - 1];
+            };
+            init_fix(std::integral_constant<int, 0>{});
+            if constexpr (Q > 1) init_fix(std::integral_constant<int, 1>{});
+            if constexpr (Q > 2) {
+                init_fix(std::integral_constant<int, 2>{});
+                init_fix(std::integral_constant<int, 3>{});
+            }
+            if constexpr (Q > 4) {
+                init_fix(std::integral_constant<int, 4>{});
+                init_fix(std::integral_constant<int, 5>{});
+                init_fix(std::integral_constant<int, 6>{});
+                init_fix(std::integral_constant<int, 7>{});
+            }
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < Q; ++q) s_red[bo][warp][q] = redv[q];
+        }
+        if (lane == 31) {
+#pragma unroll
+            for (int q = 0; q < Q; ++q) s_bnd[bo][warp][q] = bndv[q];
+        }
+
+        // control block of step tau + 1 (published during step tau - 1) and its first emission scores
+        prefetch_step(ctl[(tau + 1u) & 3u]);
+        __syncthreads();
+
+        // ---- rare path: write out finished sequences, hand out new ones ----
+        if (fin_mask != 0) {
+            auto write_out = [&](auto qc) {
+                constexpr int q = decltype(qc)::value;
+                if (!((fin_mask >> q) & 1u)) return;
+                const uint32_t sid = mgr[q].sid;
+                float bv = pos_inf();
+                int bidx = 0x7fffffff;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int o = m.orig_of_pos[tid * R + r];
+                    if (o < 0) continue;
+                    const float x = v[q][r];
+                    if (out != nullptr) out[static_cast<size_t>(sid) * m.n + o] = x;
+                    if (x < bv || (x == bv && o < bidx)) {
+                        bv = x;
+                        bidx = o;
+                    }
+                }
+                if (tid < m.nsp) {
+                    const float x = s_vs[bo][tid][q];
+                    const int o = tid == 1 ? m.special[1] : m.special[0];
+                    if (out != nullptr) out[static_cast<size_t>(sid) * m.n + o] = x;
+                    if (x < bv || (x == bv && o < bidx)) {
+                        bv = x;
+                        bidx = o;
+                    }
+                }
+                if (best != nullptr || arg != nullptr) {
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) {
+                        const float ov = __shfl_xor_sync(0xffffffffu, bv, d);
+                        const int oi = __shfl_xor_sync(0xffffffffu, bidx, d);
+                        if (ov < bv || (ov == bv && oi < bidx)) {
+                            bv = ov;
+                            bidx = oi;
+                        }
+                    }
+                    if (lane == 0) {
+                        s_bv[warp] = bv;
+                        s_bi[warp] = bidx;
+                    }
+                    __syncthreads();
+                    if (warp == 0) {
+                        bv = lane < NW ? s_bv[lane] : pos_inf();
+                        bidx = lane < NW ? s_bi[lane] : 0x7fffffff;
+#pragma unroll
+                        for (int d = 16; d > 0; d >>= 1) {
+                            const float ov = __shfl_xor_sync(0xffffffffu, bv, d);
+                            const int oi = __shfl_xor_sync(0xffffffffu, bidx, d);
+                            if (ov < bv || (ov == bv && oi < bidx)) {
+                                bv = ov;
+                                bidx = oi;
+                            }
+                        }
+                        if (lane == 0) {
+                            if (best != nullptr) best[sid] = bv;
+                            // every score +inf: no best state (same convention as the other kernels)
+                            if (arg != nullptr) arg[sid] = bv == pos_inf() ? -1 : bidx;
+                        }
+                    }
+                    __syncthreads();
+                }
+            };
+            write_out(std::integral_constant<int, 0>{});
+            if constexpr (Q > 1) write_out(std::integral_constant<int, 1>{});
+            if constexpr (Q > 2) {
+                write_out(std::integral_constant<int, 2>{});
+                write_out(std::integral_constant<int, 3>{});
+            }
+            if constexpr (Q > 4) {
+                write_out(std::integral_constant<int, 4>{});
+                write_out(std::integral_constant<int, 5>{});
+                write_out(std::integral_constant<int, 6>{});
+                write_out(std::integral_constant<int, 7>{});
+            }
+            __syncthreads(); // every thread is done with mgr[].sid
+            if (warp == MW) refill(fin_mask, ctl[(tau + 1u) & 3u], ctl[(tau + 2u) & 3u], false);
+            __syncthreads();
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); // retire the stale fetch, then redo it
+            prefetch_step(ctl[(tau + 1u) & 3u]);
+        }
+        ++tau;
+    }
+
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); // the last prefetch is never consumed
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) tmem_free(tbase, static_cast<uint32_t>(m.tmem_cols));
+}
+
+const void* chain_fn(int threads, int q) {
+#define SV_CHAIN_CASE(T)                                            \
+    switch (q) {                                                    \
+    case 8: return (const void*)sv_chain_kernel<T, 8>;              \
+    case 4: return (const void*)sv_chain_kernel<T, 4>;              \
+    case 2: return (const void*)sv_chain_kernel<T, 2>;              \
+    case 1: return (const void*)sv_chain_kernel<T, 1>;              \
+    default: return nullptr;                                        \
+    }
+    if (threads == 512) { SV_CHAIN_CASE(512) }
+    if (threads == 256) { SV_CHAIN_CASE(256) }
+    if (threads == 128) { SV_CHAIN_CASE(128) }
+#undef SV_CHAIN_CASE
+    return nullptr;
+}
+
+} // namespace
+
+// Tensor memory is allocated once per CTA for its lifetime: at most 512 / tmem_cols CTAs may share an
+// SM, otherwise a CTA would spin in tcgen05.alloc until a neighbour exits.  The dynamic shared-memory
+// request is padded so that the hardware never co-schedules more than that.
+int sv_chain_prepare(int threads, int q, size_t* smem_out, int* ctas_per_sm_out) {
+    const void* fn = chain_fn(threads, q);
+    if (fn == nullptr) return cudaErrorInvalidValue;
+    const int want = threads == 512 ? 1 : threads == 256 ? 2 : 4;
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, fn);
+    if (e != cudaSuccess) return e;
+    int dev = 0, smem_sm = 0, smem_optin = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    // grow the dynamic request until the occupancy calculator agrees
+    size_t dyn = 0;
+    int occ = 0;
+    for (;;) {
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dyn));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, threads, dyn);
+        if (e != cudaSuccess) return e;
+        if (occ <= want) break;
+        const size_t next = dyn + 4096;
+        if (fa.sharedSizeBytes + next > static_cast<size_t>(smem_optin)) return cudaErrorLaunchOutOfResources;
+        dyn = next;
+    }
+    (void)smem_sm;
+    if (occ < 1) return cudaErrorLaunchOutOfResources;
+    *smem_out = dyn;
+    *ctas_per_sm_out = occ;
+    return cudaSuccess;
+}
+
+int sv_chain_launch(int threads, int q, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+                    int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st) {
+    const void* fn = chain_fn(threads, q);
+    if (fn == nullptr || s.sym_bytes != 1) return cudaErrorInvalidValue;
+    void* args[] = {(void*)&m, (void*)&s, (void*)&d_out, (void*)&d_best, (void*)&d_arg, (void*)&d_counter};
+    cudaError_t e = cudaLaunchKernel(fn, dim3(grid), dim3(threads), args, smem, st);
+    return e != cudaSuccess ? e : cudaGetLastError();
+}

@@ -436,39 +436,36 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
 } // namespace
 
 // ------------------------------------------------------------- variant table ----
-const void* sv_ls2_variant_fn(int which); // sv_plain_ls2.cu
-
 namespace {
 
 using LsSparseT = LShape<8, 4, 3, 2, 1>; // random sparse models, tight staircase (chmm_gen k = 3)
 using LsSparseM = LShape<8, 5, 4, 3, 2>;
 using LsSparse = LShape<8, 6, 5, 4, 3>;  // random sparse models (in-degree capped at 8)
-using LsProfile = LShape<4, 3, 3, 2, 2>; // profile HMMs: <= 2 in-edges per light row + 2 dense rows
+using LsProfile = LShape<4, 3, 3, 2, 2>; // <= 2 in-edges per light row + 2 dense rows (profile HMMs that do not
+                                         // fit the chain kernel, sv_plain_chain.cu)
 
 // order = order of preference in sv_ls_build_plan: fewer register slots first (the registers a
-// tighter staircase frees hold gathers in flight)
+// tighter staircase frees hold gathers in flight).  Every staircase is compiled for 8 and for 4
+// sequences per CTA; the launch picks one from the batch size.
 const SvLsVariant kLsVariants[] = {
-    // threads, nq4, shape, nh, hs, ranks, halves
-    // two independent halves of 256 threads, 4 sequences and 10 rows per thread each (sv_plain_ls2.cu)
-    {256, 1, {8, 5, 4, 4, 3, 3, 2, 2, 1, 1}, 0, 0, 10, 2},
-    {512, 2, {8, 4, 3, 2, 1}, 0, 0, 5, 1},
-    {512, 2, {8, 5, 4, 3, 2}, 0, 0, 5, 1},
-    {512, 2, {8, 6, 5, 4, 3}, 0, 0, 5, 1},
-    {512, 2, {4, 3, 3, 2, 2}, 2, 5, 5, 1},
-    {512, 1, {8, 6, 5, 4, 3}, 0, 0, 5, 1},
-    {512, 1, {4, 3, 3, 2, 2}, 2, 5, 5, 1},
+    // threads, shape, nh, hs, ranks
+    {512, {8, 4, 3, 2, 1}, 0, 0, 5},
+    {512, {8, 5, 4, 3, 2}, 0, 0, 5},
+    {512, {8, 6, 5, 4, 3}, 0, 0, 5},
+    {512, {4, 3, 3, 2, 2}, 2, 5, 5},
 };
 constexpr int kNumLsVariants = sizeof(kLsVariants) / sizeof(kLsVariants[0]);
 
-const void* ls_variant_fn(int index) {
-    switch (index) {
-    case 0: return sv_ls2_variant_fn(0);
-    case 1: return (const void*)sv_ls_kernel<512, 2, LsSparseT, 0, 0>;
+const void* ls_variant_fn(int index, int nq4) {
+    switch (index * 2 + (nq4 == 1 ? 1 : 0)) {
+    case 0: return (const void*)sv_ls_kernel<512, 2, LsSparseT, 0, 0>;
+    case 1: return (const void*)sv_ls_kernel<512, 1, LsSparseT, 0, 0>;
     case 2: return (const void*)sv_ls_kernel<512, 2, LsSparseM, 0, 0>;
-    case 3: return (const void*)sv_ls_kernel<512, 2, LsSparse, 0, 0>;
-    case 4: return (const void*)sv_ls_kernel<512, 2, LsProfile, 2, 5>;
+    case 3: return (const void*)sv_ls_kernel<512, 1, LsSparseM, 0, 0>;
+    case 4: return (const void*)sv_ls_kernel<512, 2, LsSparse, 0, 0>;
     case 5: return (const void*)sv_ls_kernel<512, 1, LsSparse, 0, 0>;
-    case 6: return (const void*)sv_ls_kernel<512, 1, LsProfile, 2, 5>;
+    case 6: return (const void*)sv_ls_kernel<512, 2, LsProfile, 2, 5>;
+    case 7: return (const void*)sv_ls_kernel<512, 1, LsProfile, 2, 5>;
     default: return nullptr;
     }
 }
@@ -478,18 +475,17 @@ const void* ls_variant_fn(int index) {
 int sv_ls_num_variants() { return kNumLsVariants; }
 const SvLsVariant& sv_ls_variant(int index) { return kLsVariants[index]; }
 
-int sv_ls_prepare(int index, size_t smem) {
-    const void* fn = ls_variant_fn(index);
+int sv_ls_prepare(int index, int nq4, size_t smem) {
+    const void* fn = ls_variant_fn(index, nq4);
     if (fn == nullptr) return cudaErrorInvalidValue;
     return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 }
 
-int sv_ls_launch(int index, const SvLsDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+int sv_ls_launch(int index, int nq4, const SvLsDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
                  int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st) {
-    const void* fn = ls_variant_fn(index);
+    const void* fn = ls_variant_fn(index, nq4);
     if (fn == nullptr || s.sym_bytes != 1) return cudaErrorInvalidValue;
     void* args[] = {(void*)&m, (void*)&s, (void*)&d_out, (void*)&d_best, (void*)&d_arg, (void*)&d_counter};
-    cudaError_t e = cudaLaunchKernel(fn, dim3(grid), dim3(kLsVariants[index].threads * kLsVariants[index].halves), args, smem,
-                                     st);
+    cudaError_t e = cudaLaunchKernel(fn, dim3(grid), dim3(kLsVariants[index].threads), args, smem, st);
     return e != cudaSuccess ? e : cudaGetLastError();
 }

@@ -1,7 +1,34 @@
-// FP32 pipe micro-benchmark: fixes the non-tensor roofline used for the (min,+) kernels.
-// Measures lane-instructions/s of FADD, FMNMX, FMNMX3 and the step kernel's instruction
-// mixes on every SM, plus the SM clock seen during the run (clock64 vs globaltimer).
-#include "sv_internal.h"
+// Micro-benchmarks that fix the rooflines of the (min,+) kernels -- built as a SEPARATE library
+// (libsvprobe_b200.so, include/sv_probe_b200.h); nothing of the product links or loads it.
+//   sv_probe_fp32: lane-instructions/s of FADD, FMNMX, FMNMX3 and the step kernels' instruction mixes
+//                  on every SM, plus the SM clock seen during the run (clock64 vs globaltimer);
+//   sv_probe_tmem: tensor memory as a per-SM lookup table (tcgen05.ld with a run-time column);
+//   sv_probe_smem: the shared-memory pipe under the lockstep kernel's access pattern: conflict-free
+//                  LDS.128 gathers at per-lane register addresses, alone and mixed with STS.128.
+#include "sv_probe_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+
+namespace {
+thread_local std::string g_probe_error;
+int sv_fail(int code, const std::string& msg) {
+    g_probe_error = msg;
+    return code;
+}
+enum { SV_OK = 0, SV_ERR_ARG = 1, SV_ERR_CUDA = 2 };
+#define SV_CUDA(call)                                                                            \
+    do {                                                                                         \
+        cudaError_t sv_e_ = (call);                                                              \
+        if (sv_e_ != cudaSuccess) {                                                              \
+            return sv_fail(SV_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(sv_e_)); \
+        }                                                                                        \
+    } while (0)
+} // namespace
+
+extern "C" const char* sv_probe_last_error(void) { return g_probe_error.c_str(); }
 
 namespace {
 
@@ -50,12 +77,13 @@ sv_probe_kernel(int iters, float seed, float* sink, unsigned long long* clk) {
                 const float y = a[k] + c2;
                 b[k] = min3(b[k], x, y);
                 a[k] = x;
-            } else if (MIX == 4) { // 4 FADD + 1 FMNMX3  (oracle-order relaxation pair)
-                const float u0 = b[k] + c1;
-                const float u1 = b[k] + c2;
+            } else if (MIX == 4) { // 4 FADD + 1 FMNMX3  (oracle-order relaxation pair); b[k] is loop carried
+                const float u0 = b[k] + c1;  // (round 1 had b[k] loop-invariant: u0, u1 were hoisted and the
+                const float u1 = b[k] + c2;  //  row over-counted two adds per iteration)
                 const float x = u0 + a[k];
                 const float y = u1 + a[k];
                 a[k] = min3(a[k], x, y);
+                b[k] = u1;
             } else { // LDS + 2 FADD + FMNMX (the gather-bound inner loop)
                 const float v = sh[(threadIdx.x + k * 32 + it) & (2 * PROBE_THREADS - 1)];
                 const float u = b[k] + c1;
@@ -227,5 +255,139 @@ extern "C" int sv_probe_tmem(int device, int iters, unsigned* errors, double* by
     if (e != cudaSuccess) return sv_fail(SV_ERR_CUDA, std::string("sv_probe_tmem: ") + cudaGetErrorString(e));
     // per iteration each of the 16 warps reads 2 x (32 lanes x 4 columns x 4 B)
     *bytes_per_clk_per_sm = double(iters) * 16.0 * 2.0 * 512.0 / double(clk ? clk : 1);
+    return SV_OK;
+}
+
+// ------------------------------------------------------------------ shared-memory probe ----
+// The lockstep kernel's binding resource is the shared-memory pipe: per relaxation one lane reads 16 B
+// (v[src] of 4 sequences) at a register address that K0 made bank-conflict free (the 8 lanes of an
+// LDS.128 phase hit 8 distinct 16-byte bank groups), and per state update one lane stores 16 B.  This
+// probe issues exactly those instructions, with 16 warps per SM and 8 loads in flight per thread, and
+// reports the bytes per clock and SM the pipe sustains -- the MEASURED ceiling bench.py uses.
+//   mode 0: LDS.128 gathers only            mode 1: 3 LDS.128 : 1 STS.128 (the kernel's ratio, nnz/N = 3)
+//   mode 2: mode 1 plus the relaxations (8 FADD + 2 FMNMX3 per load), i.e. the whole inner loop
+//   mode 3: LDS.32 conflict-free (128 B per warp instruction) for reference
+namespace {
+
+constexpr int SM_THREADS = 512;
+constexpr int SM_POS = 2560;  // float4 positions (40 KB), as in the kernel: 5 ranks x 512 threads
+constexpr int SM_SLOTS = 8;
+
+template <int MODE>
+__global__ void __launch_bounds__(SM_THREADS, 1)
+sv_probe_smem_kernel(int iters, unsigned long long* clk, float* sink) {
+    extern __shared__ __align__(16) unsigned char sm_raw[];
+    float4* vbuf = reinterpret_cast<float4*>(sm_raw);
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int i = tid; i < 2 * SM_POS; i += SM_THREADS) vbuf[i] = make_float4(1.f + i, 2.f, 3.f, 4.f);
+    // per-thread gather addresses: pseudo-random position whose bank group (position mod 8) is
+    // (lane + slot) mod 8 -> the 8 lanes of every LDS.128 phase hit 8 distinct bank groups
+    const uint32_t sbase = static_cast<uint32_t>(__cvta_generic_to_shared(sm_raw));
+    uint32_t addr[SM_SLOTS];
+#pragma unroll
+    for (int k = 0; k < SM_SLOTS; ++k) {
+        uint32_t h = static_cast<uint32_t>(tid) * 2654435761u + static_cast<uint32_t>(k) * 40503u + 12345u;
+        h ^= h >> 15;
+        h *= 2246822519u;
+        h ^= h >> 13;
+        const uint32_t pos = ((h % (SM_POS / 8)) * 8u) + ((static_cast<uint32_t>(lane) + k) & 7u);
+        addr[k] = sbase + (MODE == 3 ? ((h % (SM_POS * 4 / 32)) * 32u + ((lane + k) & 31u)) * 4u : pos * 16u);
+    }
+    const uint32_t own = sbase + static_cast<uint32_t>(tid) * 16u;
+    __syncthreads();
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+    const float w0 = 0.25f + lane, w1 = 0.5f + lane;
+    const unsigned long long c0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+        const uint32_t pofs = (it & 1) ? SM_POS * 16u : 0u; // double buffer parity, as in the kernel
+        if (MODE == 3) {
+#pragma unroll
+            for (int k = 0; k < SM_SLOTS; ++k) {
+                float x;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(addr[k] + pofs) : "memory");
+                acc0 += x;
+            }
+            continue;
+        }
+        float4 g[SM_SLOTS];
+#pragma unroll
+        for (int k = 0; k < SM_SLOTS; ++k)
+            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(g[k].x), "=f"(g[k].y), "=f"(g[k].z), "=f"(g[k].w)
+                         : "r"(addr[k] + pofs)
+                         : "memory");
+        if (MODE == 2) {
+            // the "emission" operands are last iteration's results: loop carried across iterations (nothing
+            // can be hoisted) but independent inside one, like the rows of a step
+            const float p0 = acc0, p1 = acc1, p2 = acc2, p3 = acc3;
+#pragma unroll
+            for (int k = 0; k < SM_SLOTS; k += 2) { // a slot pair: 16 FADD + 4 FMNMX3, as pair4<false>
+                acc0 = fminf(acc0, fminf((p0 + w0) + g[k].x, (p0 + w1) + g[k + 1].x));
+                acc1 = fminf(acc1, fminf((p1 + w0) + g[k].y, (p1 + w1) + g[k + 1].y));
+                acc2 = fminf(acc2, fminf((p2 + w0) + g[k].z, (p2 + w1) + g[k + 1].z));
+                acc3 = fminf(acc3, fminf((p3 + w0) + g[k].w, (p3 + w1) + g[k + 1].w));
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < SM_SLOTS; ++k) {
+                acc0 += g[k].x;
+                acc1 += g[k].y;
+                acc2 += g[k].z;
+                acc3 += g[k].w;
+            }
+        }
+        if (MODE == 1 || MODE == 2) { // 8 loads : 8/3 stores -> 3 stores on two iterations of three, 2 on the third
+            const int ns = (it % 3 == 2) ? 2 : 3;
+            for (int k = 0; k < ns; ++k)
+                asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(own + (pofs ^ (SM_POS * 16u)) + k * SM_THREADS * 16u),
+                             "f"(acc0), "f"(acc1), "f"(acc2), "f"(acc3)
+                             : "memory");
+        }
+    }
+    const unsigned long long c1 = clock64();
+    if (acc0 + acc1 + acc2 + acc3 == 12345.678f) sink[0] = acc0;
+    if (tid == 0) clk[blockIdx.x] = c1 - c0;
+}
+
+} // namespace
+
+extern "C" int sv_probe_smem(int device, int mode, int iters, double* bytes_per_clk_per_sm, double* loads_per_clk_per_sm) {
+    if (mode < 0 || mode > 3 || iters < 3 || bytes_per_clk_per_sm == nullptr)
+        return sv_fail(SV_ERR_ARG, "sv_probe_smem: bad argument");
+    SV_CUDA(cudaSetDevice(device));
+    int sms = 0;
+    SV_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    unsigned long long* d_clk = nullptr;
+    float* d_sink = nullptr;
+    SV_CUDA(cudaMalloc(&d_clk, sms * sizeof(unsigned long long)));
+    SV_CUDA(cudaMalloc(&d_sink, sizeof(float)));
+    const size_t smem = 2 * SM_POS * 16;
+    const void* fn = mode == 0 ? (const void*)sv_probe_smem_kernel<0> : mode == 1 ? (const void*)sv_probe_smem_kernel<1>
+                     : mode == 2 ? (const void*)sv_probe_smem_kernel<2> : (const void*)sv_probe_smem_kernel<3>;
+    SV_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    iters = iters / 3 * 3;
+    cudaError_t e = cudaSuccess;
+    for (int rep = 0; rep < 2 && e == cudaSuccess; ++rep) { // first launch warms up
+        void* args[] = {(void*)&iters, (void*)&d_clk, (void*)&d_sink};
+        e = cudaLaunchKernel(fn, dim3(sms), dim3(SM_THREADS), args, smem, nullptr);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    }
+    std::string err = e == cudaSuccess ? "" : cudaGetErrorString(e);
+    unsigned long long clk = 1;
+    {
+        unsigned long long* h = new unsigned long long[sms];
+        cudaMemcpy(h, d_clk, sms * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        clk = 0;
+        for (int i = 0; i < sms; ++i) clk = h[i] > clk ? h[i] : clk; // slowest SM
+        delete[] h;
+    }
+    cudaFree(d_clk);
+    cudaFree(d_sink);
+    if (e != cudaSuccess) return sv_fail(SV_ERR_CUDA, "sv_probe_smem: " + err);
+    const double loads = double(iters) * SM_SLOTS * SM_THREADS;              // lane loads per SM
+    const double stores = (mode == 1 || mode == 2) ? double(iters) * (8.0 / 3.0) * SM_THREADS : 0.0;
+    const double unit = mode == 3 ? 4.0 : 16.0;
+    *bytes_per_clk_per_sm = (loads + stores) * unit / double(clk ? clk : 1);
+    if (loads_per_clk_per_sm != nullptr) *loads_per_clk_per_sm = loads / double(clk ? clk : 1);
     return SV_OK;
 }

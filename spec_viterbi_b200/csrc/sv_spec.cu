@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <mutex>
 #include <new>
 #include <string>
 #include <type_traits>
@@ -32,7 +33,8 @@ struct sv_spec {
     uint64_t table_first = 0; // tuple index stored at d_table[0]
     bool owns_table = false;
     int method = SV_SPEC_SPARSE_LHS;
-    int run_mode = SV_SPEC_RUN_TABLE; // SV_SPEC_RUN_IMPLICIT: level-2 chunks recomputed from the sparse factors (K4i)
+    int run_mode = SV_SPEC_RUN_AUTO;  // AUTO: K4i (level-2 chunks recomputed from the sparse factors) when eligible, else K4
+    cudaEvent_t ev_done = nullptr;    // end of the last run on this spec: runs share d_v and serialise on it
     // run-phase scratch
     float* d_v[2] = {nullptr, nullptr};
     uint64_t v_capacity = 0;
@@ -678,27 +680,28 @@ __device__ __forceinline__ unsigned load_sym(const RunSeqs& s, uint64_t idx) {
 }
 
 // v0[s][i] = fl(E[o_0][i] + start[i])      (GraphBLAS_spec_impl.cpp:54,153-154)
+// grid: x = sequence (up to 2^31-1 of them), y = tile of states
 __global__ void spec_init_kernel(SvGenericDev m, RunSeqs s, float* __restrict__ v) {
-    const int q = blockIdx.y;
+    const int q = blockIdx.x;
     const unsigned o = load_sym(s, s.off[q]);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m.n; i += gridDim.x * blockDim.x)
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < m.n; i += gridDim.y * blockDim.x)
         v[static_cast<size_t>(q) * m.n + i] = m.emis[static_cast<size_t>(o) * m.n + i] + m.start[i];
 }
 
 // K4: one chunk of `level` symbols: vout[s] = H[key(s, chunk)] (x) vin[s]; sequences whose
-// chunks are exhausted copy vin -> vout.  grid: x = row tile, y = sequence; one warp per row.
+// chunks are exhausted copy vin -> vout.  grid: x = sequence, y = row tile; one warp per row.
 __global__ void __launch_bounds__(256)
 handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
                     const float* __restrict__ table, uint64_t table_first,
                     const float* __restrict__ vin, float* __restrict__ vout, int rows_per_cta, int seq_base) {
     extern __shared__ float sv[];
-    const int q = seq_base + blockIdx.y;
+    const int q = seq_base + blockIdx.x;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
     const uint64_t nchunks = (len - 1) / level;
     const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
     float* __restrict__ vo = vout + static_cast<size_t>(q) * n;
-    const int r0 = blockIdx.x * rows_per_cta;
+    const int r0 = blockIdx.y * rows_per_cta;
     const int r1 = min(n, r0 + rows_per_cta);
     if (chunk >= nchunks) {
         for (int i = r0 + threadIdx.x; i < r1; i += blockDim.x) vo[i] = vi[i];
@@ -892,7 +895,7 @@ __device__ __forceinline__ void implicit_stage(const SvPairDev& pd, const float*
     }
 }
 
-// per-chunk launch: grid x = row tile (then one CTA per heavy row), y = sequence
+// per-chunk launch: grid x = sequence, y = row tile (then one CTA per heavy row)
 template <int R>
 __global__ void __launch_bounds__(kImplicitThreads)
 implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* __restrict__ vin,
@@ -903,20 +906,20 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     __shared__ float s_red[kImplicitThreads / 32 /*max*/];
     const int n = pd.n;
     const int nthr = blockDim.x; // 64 or 128
-    const int q = seq_base + blockIdx.y;
+    const int q = seq_base + blockIdx.x;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
     const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
     float* __restrict__ vo = vout + static_cast<size_t>(q) * n;
-    const bool heavy_cta = static_cast<int>(blockIdx.x) >= ntiles;
-    const int hme = static_cast<int>(blockIdx.x) - ntiles;
+    const bool heavy_cta = static_cast<int>(blockIdx.y) >= ntiles;
+    const int hme = static_cast<int>(blockIdx.y) - ntiles;
     if (chunk >= (len - 1) / 2) {
         if (heavy_cta) {
             if (threadIdx.x == 0) vo[pd.hrow[hme]] = vi[pd.hrow[hme]];
         } else {
 #pragma unroll
             for (int x = 0; x < R; ++x) {
-                const int i = (blockIdx.x * R + x) * nthr + threadIdx.x;
+                const int i = (blockIdx.y * R + x) * nthr + threadIdx.x;
                 if (i < n && pd.hidx[i] < 0) vo[i] = vi[i];
             }
         }
@@ -928,7 +931,7 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     implicit_stage(pd, ea, vi, sv, sr, npad, threadIdx.x, nthr);
     __syncthreads();
     if (!heavy_cta) {
-        const int i0 = blockIdx.x * R * nthr + threadIdx.x;
+        const int i0 = blockIdx.y * R * nthr + threadIdx.x;
         unsigned live = 0;
 #pragma unroll
         for (int x = 0; x < R; ++x) {
@@ -951,79 +954,6 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
         for (int wv = 1; wv < nthr / 32; ++wv) r = fminf(r, s_red[wv]);
         vo[pd.hrow[hme]] = r;
     }
-}
-
-// K4p: the same, persistent: a cluster of kClusterCtas CTAs owns one sequence for ALL its chunks (one launch,
-// no per-chunk kernel boundary).  Every CTA keeps the whole score vector double buffered in shared memory,
-// computes rows [rank * rows_per_cta, ...) and pushes them into the next buffer of all CTAs of the cluster
-// through distributed shared memory; one cluster barrier per chunk.  Independent sequences share an SM, so
-// the barrier and set-up latencies of one overlap the streaming loops of the others.
-constexpr int kClusterCtas = 8;
-
-template <int MAXT>
-__global__ void __cluster_dims__(kClusterCtas, 1, 1) __launch_bounds__(MAXT)
-implicit_pair_persistent_kernel(SvPairDev pd, RunSeqs s, const float* __restrict__ vin,
-                                float* __restrict__ vout, int npad, int rows_per_cta) {
-    extern __shared__ float4 sm4[];
-    float* vb = reinterpret_cast<float*>(sm4); // [2][npad] v, +inf padded
-    float* sr = vb + 2 * npad;                 // [n_heavy][npad] r_h
-    __shared__ float s_red[32];
-    __shared__ float s_part[2][kImplicitMaxHeavy][kClusterCtas]; // [buffer][dense row][rank] partial minima
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = static_cast<int>(cluster.block_rank());
-    const int n = pd.n;
-    const int q = blockIdx.x / kClusterCtas;
-    const int tid = threadIdx.x, nthr = blockDim.x;
-    const uint64_t o0 = s.off[q];
-    const uint64_t nchunks = (s.off[q + 1] - o0 - 1) / 2;
-    const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
-    for (int k = tid; k < npad; k += nthr) {
-        vb[k] = k < n ? vi[k] : pos_inf();
-        vb[npad + k] = pos_inf();
-    }
-    cluster.sync(); // every buffer of the cluster is initialised before anybody pushes into it
-    const int i = rank * rows_per_cta + tid;
-    const bool mine = tid < rows_per_cta && i < n;
-    const bool live = mine && pd.hidx[i] < 0;
-    int cur = 0;
-    for (uint64_t c = 0; c < nchunks; ++c) {
-        const unsigned a = load_sym(s, o0 + 1 + c * 2), b = load_sym(s, o0 + 2 + c * 2);
-        const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
-        const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
-        const float* __restrict__ sv = vb + cur * npad;
-        const int nxt = (cur ^ 1) * npad;
-        implicit_stage(pd, ea, nullptr, nullptr, sr, npad, tid, nthr);
-        __syncthreads();
-        float best[1];
-        implicit_light_rows<1>(pd, ea, eb, i, 0, live ? 1u : 0u, sv, sr, npad, best);
-        if (live) {
-#pragma unroll
-            for (int r = 0; r < kClusterCtas; ++r) cluster.map_shared_rank(vb, r)[nxt + i] = best[0];
-        }
-        // dense rows: their entries are dealt to ALL threads of the cluster (a chain of dependent loads per
-        // entry: the fewer per thread the better); the 8 partial minima meet in every CTA's s_part
-        for (int h = 0; h < pd.n_heavy; ++h) {
-            float hb = warp_min(implicit_heavy_row(pd, ea, eb, h, sv, sr, npad, rank * nthr + tid, kClusterCtas * nthr));
-            __syncthreads(); // s_red free
-            if ((tid & 31) == 0) s_red[tid >> 5] = hb;
-            __syncthreads();
-            if (tid < kClusterCtas) {
-                hb = s_red[0];
-                for (int wv = 1; wv < (nthr >> 5); ++wv) hb = fminf(hb, s_red[wv]);
-                cluster.map_shared_rank(&s_part[0][0][0], tid)[((cur ^ 1) * kImplicitMaxHeavy + h) * kClusterCtas + rank] = hb;
-            }
-        }
-        cluster.sync(); // pushes visible, reads of v and r_h done
-        cur ^= 1;
-        if (tid < pd.n_heavy) {
-            float hb = s_part[cur][tid][0];
-#pragma unroll
-            for (int r = 1; r < kClusterCtas; ++r) hb = fminf(hb, s_part[cur][tid][r]);
-            vb[cur * npad + pd.hrow[tid]] = hb; // published by the __syncthreads of the next chunk / the one below
-        }
-    }
-    __syncthreads();
-    if (mine) vout[static_cast<size_t>(q) * n + i] = vb[cur * npad + i];
 }
 
 // Level-1 tail step number `tail` (0-based) of every sequence that still has one
@@ -1444,6 +1374,7 @@ int build_dense_level2(sv_model* m, uint64_t tb, uint64_t te, float* dst, cudaSt
 
 extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t tuple_begin,
                               uint64_t tuple_end, float* d_table, void* stream, sv_spec** out) {
+    SV_API_BEGIN
     if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_create: out is NULL");
     *out = nullptr;
     if (m == nullptr || level < 1) return sv_fail(SV_ERR_ARG, "sv_spec_create: bad argument");
@@ -1496,6 +1427,7 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
     }
     *out = s;
     return SV_OK;
+    SV_API_END
 }
 
 extern "C" void sv_spec_destroy(sv_spec* s) {
@@ -1507,6 +1439,7 @@ extern "C" void sv_spec_destroy(sv_spec* s) {
         if (s->ev_join[g]) cudaEventDestroy(s->ev_join[g]);
     }
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+    if (s->ev_done) cudaEventDestroy(s->ev_done);
     if (s->d_v[0]) cudaFree(s->d_v[0]);
     if (s->d_v[1]) cudaFree(s->d_v[1]);
     delete s;
@@ -1514,13 +1447,20 @@ extern "C" void sv_spec_destroy(sv_spec* s) {
 
 extern "C" uint64_t sv_spec_level(const sv_spec* s) { return s ? s->level : 0; }
 
-extern "C" int sv_spec_set_range(sv_spec* s, uint64_t tuple_begin, uint64_t tuple_end) {
-    if (s == nullptr || tuple_begin > tuple_end || tuple_end > s->ntuples)
-        return sv_fail(SV_ERR_ARG, "sv_spec_set_range: bad argument");
+extern "C" int sv_spec_set_range(sv_spec* s, float* d_table, uint64_t table_first, uint64_t tuple_begin,
+                                 uint64_t tuple_end) {
+    SV_API_BEGIN
+    if (s == nullptr || tuple_begin > tuple_end || tuple_end > s->ntuples || tuple_begin < table_first)
+        return sv_fail(SV_ERR_ARG, "sv_spec_set_range: bad argument (need table_first <= tuple_begin <= tuple_end <= emits^level)");
+    if (s->level < 2) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: level 1 has no handler table");
     if (s->owns_table) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: table is library-owned");
+    if (d_table == nullptr && tuple_end > tuple_begin) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: NULL table");
+    s->d_table = d_table;
+    s->table_first = table_first;
     s->t_begin = tuple_begin;
     s->t_end = tuple_end;
     return SV_OK;
+    SV_API_END
 }
 
 extern "C" float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_t* tuple_end) {
@@ -1531,6 +1471,7 @@ extern "C" float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_
 }
 
 extern "C" int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float* out) {
+    SV_API_BEGIN
     if (s == nullptr || out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_get_handler: NULL");
     if (s->level < 2 || tuple_index < s->t_begin || tuple_index >= s->t_end)
         return sv_fail(SV_ERR_ARG, "sv_spec_get_handler: tuple not in the table");
@@ -1539,6 +1480,7 @@ extern "C" int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float
     SV_CUDA(cudaMemcpy(out, s->d_table + (tuple_index - s->table_first) * mat, mat * sizeof(float),
                        cudaMemcpyDeviceToHost));
     return SV_OK;
+    SV_API_END
 }
 
 // ---------------------------------------------------------------- persistence ----
@@ -1599,6 +1541,7 @@ struct PinnedPair {
 } // namespace
 
 extern "C" int sv_spec_save(const sv_spec* s, const char* path) {
+    SV_API_BEGIN
     if (s == nullptr || path == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_save: NULL");
     if (s->level < 2) return sv_fail(SV_ERR_ARG, "sv_spec_save: level 1 has no handler table (K2 forms E+T' on the fly)");
     const sv_model* m = s->m;
@@ -1646,9 +1589,11 @@ extern "C" int sv_spec_save(const sv_spec* s, const char* path) {
         return sv_fail(SV_ERR_IO, std::string("sv_spec_save: write failed: ") + path);
     }
     return SV_OK;
+    SV_API_END
 }
 
 extern "C" int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out) {
+    SV_API_BEGIN
     if (out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_load: out is NULL");
     *out = nullptr;
     if (m == nullptr || path == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_load: NULL");
@@ -1712,6 +1657,7 @@ extern "C" int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_sp
     std::fclose(f);
     *out = s;
     return SV_OK;
+    SV_API_END
 }
 
 namespace {
@@ -1754,9 +1700,10 @@ bool implicit_supported(sv_spec* s, SvPairDev* pd) {
 } // namespace
 
 extern "C" int sv_spec_set_run_mode(sv_spec* s, int mode) {
-    if (s == nullptr || (mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT && mode != SV_SPEC_RUN_IMPLICIT_CLUSTER))
+    SV_API_BEGIN
+    if (s == nullptr || (mode != SV_SPEC_RUN_AUTO && mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT))
         return sv_fail(SV_ERR_ARG, "sv_spec_set_run_mode: bad argument");
-    if (mode != SV_SPEC_RUN_TABLE && s->level > 1) {
+    if (mode == SV_SPEC_RUN_IMPLICIT && s->level > 1) {
         SV_CUDA(cudaSetDevice(s->m->device));
         SvPairDev pd;
         if (!implicit_supported(s, &pd)) {
@@ -1766,23 +1713,30 @@ extern "C" int sv_spec_set_run_mode(sv_spec* s, int mode) {
     }
     s->run_mode = mode;
     return SV_OK;
+    SV_API_END
 }
 
 extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out, float* d_best,
                                   int32_t* d_best_state, void* stream) {
+    SV_API_BEGIN
     if (s == nullptr || seqs == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run_device: NULL");
     sv_model* m = s->m;
     if (s->level == 1) return sv_viterbi_device(m, seqs, d_out, d_best, d_best_state, stream);
     if (seqs->device != m->device)
         return sv_fail(SV_ERR_ARG, "sv_spec_run_device: sequences live on another device");
-    const bool implicit = s->run_mode != SV_SPEC_RUN_TABLE;
-    if (!implicit && (s->t_begin != 0 || s->t_end != s->ntuples))
-        return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SV_CUDA(cudaSetDevice(m->device));
     SvPairDev pd;
-    if (implicit && !implicit_supported(s, &pd))
+    // AUTO: the implicit run whenever the model is eligible (identical bits, ~5x faster, no table traffic)
+    bool implicit = s->run_mode != SV_SPEC_RUN_TABLE && implicit_supported(s, &pd);
+    if (s->run_mode == SV_SPEC_RUN_IMPLICIT && !implicit)
         return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_run: implicit run needs level 2 and at most 4 dense rows");
+    if (!implicit) cudaGetLastError();
+    if (!implicit && (s->t_begin != 0 || s->t_end != s->ntuples))
+        return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
+    // runs on one spec share its state vectors: order this run after the previous one, whatever its stream
+    if (s->ev_done == nullptr) SV_CUDA(cudaEventCreateWithFlags(&s->ev_done, cudaEventDisableTiming));
+    else SV_CUDA(cudaStreamWaitEvent(st, s->ev_done, 0));
     const size_t n = m->n;
     const uint64_t nseq = seqs->nseq;
     if (s->v_capacity < nseq) {
@@ -1797,37 +1751,26 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     int launches = 0;
     int cur = 0;
     {
-        dim3 grid(static_cast<unsigned>((n + 255) / 256), static_cast<unsigned>(nseq));
+        dim3 grid(static_cast<unsigned>(nseq), static_cast<unsigned>(std::min<size_t>((n + 255) / 256, 65535)));
         spec_init_kernel<<<grid, 256, 0, st>>>(m->gen, rs, s->d_v[cur]);
+        SV_CUDA(cudaGetLastError()); // a failed first launch must not let the chunk kernels run on garbage
         ++launches;
     }
     uint64_t max_chunks = (seqs->max_len - 1) / s->level;
-    if (implicit && s->run_mode == SV_SPEC_RUN_IMPLICIT_CLUSTER && max_chunks > 0) {
-        // K4p: one persistent launch, a cluster per sequence walks all its chunks
-        const int rows = static_cast<int>((n + kClusterCtas - 1) / kClusterCtas);
-        const int threads = std::max(64, (rows + 31) / 32 * 32);
-        const int npad = static_cast<int>((n + 15) / 16 * 16);
-        size_t smem = implicit_smem(pd) + static_cast<size_t>(npad) * sizeof(float);
-        // clusters are packed onto few SMs when many CTAs fit one SM; a larger shared-memory request per CTA
-        // (SV_K4P_SMEM_KB) caps the CTAs per SM and spreads the clusters over the chip
-        if (const char* e = std::getenv("SV_K4P_SMEM_KB")) smem = std::max(smem, static_cast<size_t>(std::atoi(e)) * 1024);
-        if (threads <= 1024 && smem <= 200 * 1024) {
-            auto kern = threads <= 512 ? implicit_pair_persistent_kernel<512> : implicit_pair_persistent_kernel<1024>;
-            SV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-            kern<<<static_cast<unsigned>(nseq * kClusterCtas), threads, smem, st>>>(pd, rs, s->d_v[cur], s->d_v[cur ^ 1],
-                                                                                     npad, rows);
-            SV_CUDA(cudaGetLastError());
-            ++launches;
-            cur ^= 1;
-            max_chunks = 0; // the chunk loop below is done
-        }
-    }
     // rows per CTA: at least ~6 waves of resident CTAs (8 x 256 threads per SM), so that the last,
     // partial wave costs a few percent instead of the ~20 % it cost with 64 rows at 50 sequences
     int rows_per_cta = 64;
     {
         const uint64_t slots = static_cast<uint64_t>(std::max(1, m->sm_count)) * 8ull;
         while (rows_per_cta > 8 && ((n + rows_per_cta - 1) / rows_per_cta) * nseq < 6ull * slots) rows_per_cta /= 2;
+        while ((n + rows_per_cta - 1) / rows_per_cta > 65535) rows_per_cta *= 2;
+    }
+    // v is staged in dynamic shared memory (n floats): opt in above 48 KB
+    if (n * sizeof(float) > 48 * 1024) {
+        SV_CUDA(cudaFuncSetAttribute(handler_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(n * sizeof(float))));
+        SV_CUDA(cudaFuncSetAttribute(tail_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(n * sizeof(float))));
     }
     // sequence groups on up to kRunStreams streams (group 0 stays on the caller's stream)
     int ngroups = static_cast<int>(std::min<uint64_t>(sv_spec::kRunStreams, nseq));
@@ -1852,14 +1795,14 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
                 const int per_cta = threads * rows;
                 const int ntiles = static_cast<int>((n + per_cta - 1) / per_cta);
                 const int npad = static_cast<int>((n + 15) / 16 * 16);
-                dim3 igrid(static_cast<unsigned>(ntiles + pd.n_heavy), static_cast<unsigned>(q1 - q0));
+                dim3 igrid(static_cast<unsigned>(q1 - q0), static_cast<unsigned>(ntiles + pd.n_heavy));
                 auto kern = rows == 1 ? implicit_pair_step_kernel<1> : rows == 2 ? implicit_pair_step_kernel<2> : implicit_pair_step_kernel<4>;
                 kern<<<igrid, threads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
                     pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles, npad);
                 ++launches;
                 continue;
             }
-            dim3 grid(static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta), static_cast<unsigned>(q1 - q0));
+            dim3 grid(static_cast<unsigned>(q1 - q0), static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta));
             handler_gemv_kernel<<<grid, 256, n * sizeof(float), g == 0 ? st : s->aux[g - 1]>>>(
                 static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c,
                 s->d_table, s->table_first, s->d_v[cur], s->d_v[cur ^ 1], rows_per_cta, static_cast<int>(q0));
@@ -1887,8 +1830,10 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         ++launches;
     }
     SV_CUDA(cudaGetLastError());
+    SV_CUDA(cudaEventRecord(s->ev_done, st));
     m->last_launches = launches;
     return SV_OK;
+    SV_API_END
 }
 
 namespace {
@@ -1897,6 +1842,7 @@ int spec_run_batch_impl(sv_spec* s, const SrcT* symbols, const uint64_t* offsets
                         float* out, float* best, int32_t* best_state) {
     if (s == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run_batch: NULL spec");
     sv_model* m = s->m;
+    std::lock_guard<std::mutex> lock(*static_cast<std::mutex*>(m->ws_mutex)); // one workspace per model
     int rc = sv_ws_upload(m, symbols, offsets, nseq);
     if (rc != SV_OK) return rc;
     float *d_out, *d_best;
@@ -1911,16 +1857,22 @@ int spec_run_batch_impl(sv_spec* s, const SrcT* symbols, const uint64_t* offsets
 
 extern "C" int sv_spec_run_batch(sv_spec* s, const uint64_t* symbols, const uint64_t* offsets,
                                  uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    SV_API_BEGIN
     return spec_run_batch_impl(s, symbols, offsets, nseq, out, best, best_state);
+    SV_API_END
 }
 
 extern "C" int sv_spec_run_batch_u8(sv_spec* s, const uint8_t* symbols, const uint64_t* offsets,
                                     uint64_t nseq, float* out, float* best, int32_t* best_state) {
+    SV_API_BEGIN
     return spec_run_batch_impl(s, symbols, offsets, nseq, out, best, best_state);
+    SV_API_END
 }
 
 extern "C" int sv_spec_run(sv_spec* s, const uint64_t* seq, uint64_t len, float* out) {
+    SV_API_BEGIN
     if (seq == nullptr || out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_run: NULL");
     const uint64_t offsets[2] = {0, len};
     return sv_spec_run_batch(s, seq, offsets, 1, out, nullptr, nullptr);
+    SV_API_END
 }

@@ -181,6 +181,18 @@ bool write_HMM_packed(const HMM& hmm, const std::string& file_name) {
     return ok;
 }
 
+namespace {
+// bytes left in the file from the current position (packed readers check every size field against it
+// before allocating: a corrupt header must not turn into a huge allocation or an out-of-bounds read)
+std::uint64_t bytes_left(std::FILE* f) {
+    const long at = std::ftell(f);
+    if (at < 0 || std::fseek(f, 0, SEEK_END) != 0) return 0;
+    const long end = std::ftell(f);
+    std::fseek(f, at, SEEK_SET);
+    return end > at ? static_cast<std::uint64_t>(end - at) : 0;
+}
+} // namespace
+
 HMM read_HMM_packed(const std::string& file_name) {
     std::FILE* f = std::fopen(file_name.c_str(), "rb");
     if (f == nullptr) {
@@ -191,6 +203,14 @@ HMM read_HMM_packed(const std::string& file_name) {
     std::uint64_t hdr[4];
     HMM hmm;
     bool ok = get(f, magic, 8) && std::memcmp(magic, CHMMB_MAGIC, 8) == 0 && get(f, hdr, 4);
+    if (ok) {
+        // start: 8 B per entry; emissions: 4 B x emits x states; transitions: 12 B per entry
+        const std::uint64_t left = bytes_left(f);
+        const unsigned __int128 need = static_cast<unsigned __int128>(hdr[3]) * 8 +
+                                       static_cast<unsigned __int128>(hdr[0]) * hdr[1] * 4 +
+                                       static_cast<unsigned __int128>(hdr[2]) * 12;
+        ok = hdr[0] > 0 && hdr[1] > 0 && need == left;
+    }
     if (ok) {
         hmm.states_num = hdr[0];
         hmm.emit_num = hdr[1];
@@ -211,6 +231,12 @@ HMM read_HMM_packed(const std::string& file_name) {
         hmm.trans_cols.assign(u32.begin(), u32.end());
         hmm.trans_probs.resize(hmm.trans_num);
         ok = ok && get(f, hmm.trans_probs.data(), hmm.trans_num);
+        for (std::size_t i = 0; ok && i < hmm.trans_num; ++i) {
+            ok = hmm.trans_rows[i] < hmm.states_num && hmm.trans_cols[i] < hmm.states_num;
+        }
+        for (std::size_t i = 0; ok && i < hmm.non_zero_start_probs; ++i) {
+            ok = hmm.start_probabilities_cols[i] < hmm.states_num;
+        }
     }
     std::fclose(f);
     return ok ? hmm : HMM{};
@@ -253,10 +279,25 @@ HMM::Emit_seq_vec_t read_emit_seq_packed(const std::string& file_name) {
     HMM::Emit_seq_vec_t seqs;
     bool ok = get(f, magic, 8) && std::memcmp(magic, ESSB_MAGIC, 8) == 0 && get(f, hdr, 3);
     if (ok) {
+        // hdr = {sequences, total symbols, bytes per symbol}: everything is checked against the file size
+        // before anything is allocated, the width before it is used as a memcpy length
+        const std::uint64_t left = bytes_left(f);
+        const unsigned __int128 need = (static_cast<unsigned __int128>(hdr[0]) + 1) * 8 +
+                                       static_cast<unsigned __int128>(hdr[1]) * hdr[2];
+        ok = (hdr[2] == 1 || hdr[2] == 2 || hdr[2] == 4) && need == left;
+    }
+    if (ok) {
         std::vector<std::uint64_t> offs(hdr[0] + 1);
         ok = get(f, offs.data(), offs.size());
-        std::vector<unsigned char> raw(hdr[1] * hdr[2]);
-        ok = ok && get(f, raw.data(), raw.size());
+        ok = ok && offs[0] == 0 && offs.back() == hdr[1];
+        for (std::size_t i = 0; ok && i < hdr[0]; ++i) {
+            ok = offs[i] <= offs[i + 1];
+        }
+        std::vector<unsigned char> raw;
+        if (ok) {
+            raw.resize(hdr[1] * hdr[2]);
+            ok = get(f, raw.data(), raw.size());
+        }
         if (ok) {
             seqs.resize(hdr[0]);
             for (std::size_t i = 0; i < hdr[0]; ++i) {

@@ -11,8 +11,10 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("i", range(4))
 @pytest.mark.parametrize("level", [1, 2, 3])
-def test_reference_known_answers(i, level, api, load_model, load_seqs, golden):
-    impl = api.B200_spec_impl(level)
+@pytest.mark.parametrize("mode", ["auto", "table"])
+def test_reference_known_answers(i, level, mode, api, load_model, load_seqs, golden):
+    from spec_viterbi_b200 import _lib
+    impl = api.B200_spec_impl(level, run_mode=_lib.SPEC_RUN_AUTO if mode == "auto" else _lib.SPEC_RUN_TABLE)
     impl.spec_with(load_model(f"{i}_test_chmm"))
     v = impl.run_Viterbi_spec(load_seqs(f"{i}_test_seq")[0])
     assert impl.get_level() == level
@@ -24,7 +26,8 @@ def test_reference_known_answers(i, level, api, load_model, load_seqs, golden):
 def test_level2_reference_fixture(name, method, api, load_model, load_seqs, golden):
     from spec_viterbi_b200 import _lib
     impl = api.B200_spec_impl(2, method={"dense": _lib.SPEC_DENSE_GEMM, "sparse": _lib.SPEC_SPARSE_LHS,
-                                         "pair": _lib.SPEC_PAIR_ROWS, "auto": _lib.SPEC_AUTO}[method])
+                                         "pair": _lib.SPEC_PAIR_ROWS, "auto": _lib.SPEC_AUTO}[method],
+                              run_mode=_lib.SPEC_RUN_TABLE)  # the precomputed handlers are what is under test
     impl.spec_with(load_model(name))
     out = impl.run_Viterbi_spec_batch(load_seqs("emit_3_3500_20"))
     for k in range(3):
@@ -46,6 +49,40 @@ def test_handlers_bit_exact(name, api, oracle, load_model):
         assert same_bits(sparse.handler(t), exp), t
         assert same_bits(dense.handler(t), exp), t
         assert same_bits(pair.handler(t), exp), t
+
+
+def test_config3_reference_fixture(api, load_model, load_seqs, golden):
+    """BASELINE.json configs[2] for real: 2405.chmm x emit_50_3500_20 at level 2 (400 handlers, 9.27 GB),
+    through the precomputed table + K4 AND through the implicit run (K4i), against vectors produced by the
+    reference's own GraphBLAS_spec_impl (GraphBLAS_spec_impl.cpp:50-97; tools/make_fixtures.py --config3)."""
+    from spec_viterbi_b200 import _lib
+    hmm = load_model("2405")
+    seqs = load_seqs("emit_50_3500_20")
+    syms, offs = api.pack_sequences([seqs[0], seqs[49]])
+    m = api.Model(hmm)
+    sp = api.Spec(m, 2)
+    for mode in (_lib.SPEC_RUN_TABLE, _lib.SPEC_RUN_IMPLICIT):
+        sp.set_run_mode(mode)
+        out, best, arg = sp.run_batch(syms, offs)
+        for j, k in enumerate((0, 49)):
+            exp = golden[f"2405_emit50_3500_seq{k}_spec2"]
+            assert same_bits(out[j], exp), (mode, k)
+            assert best[j] == exp.min() and arg[j] == exp.argmin()
+    sp.close()
+    m.close()
+
+
+def test_config3_pair_handlers_vs_oracle(api, oracle, load_model):
+    """K3'' (the default level-2 precompute) on 2405.chmm against the ORACLE's M_b (x) M_a, element-wise."""
+    from spec_viterbi_b200 import _lib
+    hmm = load_model("2405")
+    m = api.Model(hmm)
+    osp = oracle.spec(hmm, 2)
+    for t in (0, 211, 399):
+        sp = api.Spec(m, 2, _lib.SPEC_PAIR_ROWS, t, t + 1)
+        assert same_bits(sp.handler(t), osp.handler(t)), t
+        sp.close()
+    m.close()
 
 
 def test_pair_rows_equals_sparse_lhs_on_large_models(api, load_model):
@@ -73,7 +110,7 @@ def test_random_model_levels(api, oracle):
     seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 50, 301)]
     for level, method in ((1, _lib.SPEC_AUTO), (2, _lib.SPEC_SPARSE_LHS), (2, _lib.SPEC_DENSE_GEMM),
                           (2, _lib.SPEC_PAIR_ROWS)):
-        impl = api.B200_spec_impl(level, method=method)
+        impl = api.B200_spec_impl(level, method=method, run_mode=_lib.SPEC_RUN_TABLE)
         impl.spec_with(hmm)
         out = impl.run_Viterbi_spec_batch(seqs)
         osp = oracle.spec(hmm, level)
@@ -120,6 +157,7 @@ def test_handler_table_save_load(api, oracle, tmp_path):
     syms, offs = api.pack_sequences(seqs)
     m = api.Model(hmm)
     built = api.Spec(m, 2)
+    built.set_run_mode(_lib.SPEC_RUN_TABLE)  # the table is what is under test
     exp, _, _ = built.run_batch(syms, offs)
     osp = oracle.spec(hmm, 2)
     assert same_bits(exp[4], osp.run(seqs[4]))
@@ -129,6 +167,7 @@ def test_handler_table_save_load(api, oracle, tmp_path):
     loaded = api.Spec.load(m, path)
     assert loaded.level == 2 and loaded.table()[1:] == (0, 400)
     assert same_bits(loaded.handler(123), built.handler(123))
+    loaded.set_run_mode(_lib.SPEC_RUN_TABLE)
     got, _, _ = loaded.run_batch(syms, offs)
     assert same_bits(got, exp)
     # a shard of the tuple range
@@ -148,17 +187,17 @@ def test_handler_table_save_load(api, oracle, tmp_path):
         api.Spec(m, 1).save(tmp_path / "l1")
 
 
-IMPLICIT_MODES = ["step", "cluster"]
+IMPLICIT_MODES = ["step", "auto"]
 
 
 def _implicit(mode):
     from spec_viterbi_b200 import _lib
-    return {"step": _lib.SPEC_RUN_IMPLICIT, "cluster": _lib.SPEC_RUN_IMPLICIT_CLUSTER}[mode]
+    return {"step": _lib.SPEC_RUN_IMPLICIT, "auto": _lib.SPEC_RUN_AUTO}[mode]
 
 
 @pytest.mark.parametrize("mode", IMPLICIT_MODES)
 def test_implicit_run_reference_fixture(mode, api, load_model, load_seqs, golden):
-    """K4p / K4i (level-2 chunks recomputed from the sparse factors, no table) gives the reference's bits:
+    """K4i (level-2 chunks recomputed from the sparse factors, no table) gives the reference's bits:
     profile HMMs (two dense rows, one dense column) against the fixtures generated from
     GraphBLAS_spec_impl (level 2), with an EMPTY handler table."""
     from spec_viterbi_b200 import _lib
@@ -201,6 +240,7 @@ def test_implicit_run_equals_table_run(mode, api, oracle, load_model, load_seqs)
         seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 50, 301, 1000)]
         syms, offs = api.pack_sequences(seqs)
         table = api.Spec(m, 2)
+        table.set_run_mode(_lib.SPEC_RUN_TABLE)
         exp, ebest, earg = table.run_batch(syms, offs)
         table.set_run_mode(_implicit(mode))
         got, best, arg = table.run_batch(syms, offs)
@@ -214,10 +254,81 @@ def test_implicit_run_equals_table_run(mode, api, oracle, load_model, load_seqs)
     m = api.Model(hmm)
     syms, offs = api.pack_sequences(load_seqs("covid-19"))
     table = api.Spec(m, 2)
+    table.set_run_mode(_lib.SPEC_RUN_TABLE)
     exp, _, _ = table.run_batch(syms, offs)
     table.set_run_mode(_implicit(mode))
     got, _, _ = table.run_batch(syms, offs)
     assert same_bits(got, exp)
+
+
+def test_tuple_shards_gathered_into_one_table(api, oracle):
+    """The multi-GPU precompute flow on one device (two 'ranks'): each builds its tuple shard into its slice
+    of ONE caller-owned full-size table, then sv_spec_set_range(full base, 0, 0, ntuples) publishes the whole
+    table (what follows the all-gather).  The run must give the bits of a locally built table; ranges that
+    start below the table's first tuple are rejected."""
+    import torch
+    from spec_viterbi_b200 import generators, _lib
+    hmm = generators.random_hmm(states_num=120, trans_per_state=3, seed=21)
+    n, E = 120, 20
+    seqs = [np.random.default_rng(k).integers(0, E, L).astype(np.uint64) for k, L in enumerate((2, 3, 9, 64, 301))]
+    syms, offs = api.pack_sequences(seqs)
+    m = api.Model(hmm)
+    ref = api.Spec(m, 2)
+    ref.set_run_mode(_lib.SPEC_RUN_TABLE)
+    exp, _, _ = ref.run_batch(syms, offs)
+    table = torch.full((E * E, n, n), float("nan"), dtype=torch.float32, device="cuda")
+    half = 137  # a ragged cut
+    a = api.Spec(m, 2, tuple_begin=0, tuple_end=half, d_table=table[0:half].data_ptr())
+    b = api.Spec(m, 2, tuple_begin=half, tuple_end=E * E, d_table=table[half:].data_ptr())
+    torch.cuda.synchronize()
+    assert not torch.isnan(table).any()
+    for sp in (a, b):
+        sp.set_run_mode(_lib.SPEC_RUN_TABLE)
+        with pytest.raises(_lib.SvError):  # a shard alone cannot run
+            sp.run_batch(syms, offs)
+    with pytest.raises(_lib.SvError):      # b's table starts at tuple `half`: tuple 0 is not in it
+        b.set_range(table[half:].data_ptr(), half, 0, E * E)
+    b.set_range(table.data_ptr(), 0, 0, E * E)
+    got, _, _ = b.run_batch(syms, offs)
+    assert same_bits(got, exp)
+    assert same_bits(b.handler(3), ref.handler(3)) and same_bits(b.handler(399), ref.handler(399))
+    assert same_bits(got[4], oracle.spec(hmm, 2).run(seqs[4]))
+
+
+def test_concurrent_streams_on_one_model(api, oracle):
+    """Two launches of ONE model overlapping on two streams (each takes its own work-queue counter) and two
+    back-to-back runs of one spec on two streams (ordered on the device): all results are the oracle's."""
+    import torch
+    from spec_viterbi_b200 import generators
+    hmm = generators.random_hmm(states_num=300, seed=4)
+    m = api.Model(hmm)
+    batches = [generators.random_sequences(600, 400, seed=70 + k, dtype=np.uint8) for k in range(2)]
+    seqs = [m.upload(sy, of) for sy, of in batches]
+    reps = 3
+    outs = [[torch.full((600, 300), float("nan"), dtype=torch.float32, device="cuda") for _ in range(2)] for _ in range(reps)]
+    streams = [torch.cuda.Stream() for _ in range(2)]
+    torch.cuda.synchronize()
+    for rep in range(reps):
+        for k in range(2):
+            m.viterbi_device(seqs[k], outs[rep][k].data_ptr(), 0, 0, streams[k].cuda_stream)
+    torch.cuda.synchronize()
+    for k in range(2):
+        sy, of = batches[k]
+        exp = oracle.plain_batch(hmm, sy[: int(of[8])].astype(np.uint64), of[:9], threads=4)
+        for rep in range(reps):
+            got = outs[rep][k].cpu().numpy()
+            assert same_bits(got[:8], exp)
+            assert not np.isnan(got).any()  # every sequence was processed in every launch: no row left unwritten
+            assert same_bits(got, outs[0][k].cpu().numpy())
+    outs = outs[0]
+    sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)
+    for k in range(2):
+        sp.run_device(seqs[k], outs[k].data_ptr(), 0, 0, streams[k].cuda_stream)
+    torch.cuda.synchronize()
+    osp = oracle.spec(hmm, 2)
+    for k in range(2):
+        sy, of = batches[k]
+        assert same_bits(outs[k][5].cpu().numpy(), osp.run(sy[int(of[5]):int(of[6])].astype(np.uint64)))
 
 
 def test_implicit_run_unsupported(api):

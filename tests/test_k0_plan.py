@@ -42,3 +42,106 @@ def test_high_in_degree_is_split(api, oracle):
     stats, out = api.k0_lockstep_check(hmm, seq)
     assert stats["valid"] == 1 and stats["split_states"] > 0
     assert same_bits(out, oracle.plain(hmm, seq))
+
+
+# ---------------------------------------------------------------- chain kernel K0 ----
+@pytest.mark.parametrize("name", ["100", "300", "1200", "2405"])
+def test_chain_plan_profile_models(name, api, oracle, load_model, load_seqs):
+    """Every shipped profile HMM has the chain + specials structure; the kernel's algebra (band edge from
+    the neighbouring position, hub broadcast, dense rows through the chain minimum) replayed on the host
+    gives the oracle's bits."""
+    hmm = load_model(name)
+    n = hmm.states_num
+    for seq in (load_seqs("covid-19")[2], load_seqs("covid-19")[0][:1], load_seqs("emit_3_3500_20")[1][:500]):
+        stats, out = api.k0_chain_check(hmm, seq)
+        assert stats["valid"] == 1 and stats["specials"] == 2 and stats["chain_states"] == n - 2
+        assert {stats["special0"], stats["special1"]} == {0, n - 1} and stats["special0"] == 0  # hub = N state
+        assert stats["threads"] * 5 >= n - 2 and stats["nonneg"] == 1
+        assert same_bits(out, oracle.plain(hmm, seq))
+
+
+def test_chain_plan_rejects_other_structures(api):
+    from spec_viterbi_b200 import generators
+    # random sparse graph: no specials
+    st, _ = api.k0_chain_check(generators.random_hmm(states_num=150, seed=7))
+    assert st["valid"] == 0
+    # profile HMM with one dense-row weight changed: the chain-minimum identity no longer applies
+    import copy
+    from conftest import GOLDEN
+    hmm = api.read_HMM(str(GOLDEN / "models" / "100.chmmb"))
+    bad = copy.deepcopy(hmm)
+    k = int(np.flatnonzero((bad.trans_cols == 0) & (bad.trans_rows == 5))[0])  # M_5 -> N
+    bad.trans_probs = bad.trans_probs.copy()
+    bad.trans_probs[k] = np.float32(2.5)
+    assert api.k0_chain_check(bad)[0]["valid"] == 0
+    # an extra skip edge M_3 -> M_7 breaks the simple-path property
+    skip = api.HMM(hmm.states_num, hmm.emit_num, hmm.trans_num + 1,
+                   np.append(hmm.trans_rows, np.uint64(3)), np.append(hmm.trans_cols, np.uint64(7)),
+                   np.append(hmm.trans_probs, np.float32(1.5)), hmm.emissions, hmm.non_zero_start_probs,
+                   hmm.start_probabilities_cols, hmm.start_probabilities)
+    assert api.k0_chain_check(skip)[0]["valid"] == 0
+
+
+def test_chain_plan_variants(api, oracle):
+    """Shuffled state numbering, a broken chain (two paths), +inf weights, one special only, unreachable states."""
+    rng = np.random.default_rng(3)
+    L = 37
+    n = L + 2
+    perm = rng.permutation(n)          # state k of the canonical model is called perm[k]
+    N, C = 0, L + 1
+    src, dst, w = [], [], []
+    src += [N]; dst += [N]; w += [0.3]
+    src += [C]; dst += [C]; w += [0.2]
+    for k in range(1, L + 1):
+        src += [N]; dst += [k]; w += [float(rng.uniform(1, 9))]      # hub -> chain, different weights
+        src += [k]; dst += [N]; w += [1.0]                            # chain -> N, uniform
+        src += [k]; dst += [C]; w += [1.25]                           # chain -> C, uniform
+        if k < L and k != 17:                                          # band, broken after state 17
+            src += [k]; dst += [k + 1]; w += [float(rng.uniform(0.1, 3)) if k != 9 else np.inf]
+    src = perm[np.array(src)].astype(np.uint64)
+    dst = perm[np.array(dst)].astype(np.uint64)
+    em = rng.uniform(0.5, 7, (6, n)).astype(np.float32)
+    hmm = api.HMM(n, 6, src.size, src, dst, np.array(w, np.float32), em, 2,
+                  np.array([perm[N], perm[4]], np.uint64), np.array([0.0, 2.0], np.float32))
+    for T in (1, 2, 3, 50):
+        seq = rng.integers(0, 6, T).astype(np.uint64)
+        st, out = api.k0_chain_check(hmm, seq)
+        assert st["valid"] == 1 and st["chain_states"] == L and st["special0"] == perm[N]
+        assert same_bits(out, oracle.plain(hmm, seq))
+    # no start state at all: everything stays +inf
+    dead = api.HMM(n, 6, src.size, src, dst, np.array(w, np.float32), em, 0, np.zeros(0, np.uint64), np.zeros(0, np.float32))
+    st, out = api.k0_chain_check(dead, np.array([1, 2, 3], np.uint64))
+    assert st["valid"] == 1 and np.all(np.isposinf(out))
+
+
+# ---------------------------------------------------------------- lazy / cached plans ----
+def test_quick_plan_is_fast_and_exact(api, oracle, monkeypatch):
+    """The first batch runs on a short colouring search (the full one continues in the background on a GPU
+    box): the quick plan must still replay to the oracle's bits and stay within 1.35x of the ideal wavefronts."""
+    import time
+    from spec_viterbi_b200 import generators
+    hmm = generators.random_hmm(states_num=2405, seed=2405)
+    seq = np.random.default_rng(1).integers(0, 20, 60).astype(np.uint64)
+    monkeypatch.setenv("SV_LS_SA_ITERS", str(60 * 2405))
+    t0 = time.perf_counter()
+    stats, out = api.k0_lockstep_check(hmm, seq)
+    dt = time.perf_counter() - t0
+    assert stats["valid"] == 1 and same_bits(out, oracle.plain(hmm, seq))
+    assert stats["wavefronts"] <= 1.35 * stats["ideal_wavefronts"]
+    assert dt < 2.0  # ~0.15 s on 8 cores; the bound only catches a return to multi-second planning
+
+
+def test_multi_split(api):
+    """sv_multi_viterbi_batch* deals contiguous ranges of about equal symbol counts."""
+    offs = np.arange(0, 4097, dtype=np.uint64) * np.uint64(7000)
+    for parts in (1, 2, 4, 8):
+        cut = api.multi_split(offs, parts)
+        assert cut[0] == 0 and cut[-1] == 4096 and np.all(np.diff(cut.astype(np.int64)) == 4096 // parts)
+    lens = np.random.default_rng(0).integers(1, 8000, 300)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64) + np.uint64(123)  # non-zero base
+    for parts in (2, 3, 8):
+        cut = api.multi_split(offs, parts).astype(np.int64)
+        assert cut[0] == 0 and cut[-1] == 300 and np.all(np.diff(cut) >= 0)
+        loads = np.array([int(offs[cut[k + 1]] - offs[cut[k]]) for k in range(parts)])
+        assert loads.max() - loads.min() <= 2 * lens.max()
+    assert list(api.multi_split(np.array([0, 5, 9], np.uint64), 8)[[0, -1]]) == [0, 2]  # more devices than sequences

@@ -65,6 +65,14 @@ def test_spec2_matches_reference_fixture(name, oracle, load_model, load_seqs, go
         assert same_bits(sp.run(load_seqs("emit_3_3500_20")[k]), golden[f"{name}_emit3_3500_seq{k}_spec2"])
 
 
+def test_config3_matches_reference_fixture(oracle, load_model, load_seqs, golden):
+    """BASELINE.json configs[2] (2405.chmm x emit_50_3500_20, level 2): the fixture was produced by the
+    reference's GraphBLAS_spec_impl itself (tools/make_fixtures.py --config3); handlers are built lazily
+    here, ~35 s."""
+    sp = oracle.spec(load_model("2405"), 2)
+    assert same_bits(sp.run(load_seqs("emit_50_3500_20")[49]), golden["2405_emit50_3500_seq49_spec2"])
+
+
 def test_spec1_is_bitwise_plain(oracle, load_model, load_seqs):
     hmm = load_model("300")
     seq = load_seqs("emit_3_3500_20")[1]

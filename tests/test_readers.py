@@ -86,3 +86,47 @@ def test_readers_match_reference_reader(api):
             for f in ("trans_rows", "trans_cols", "trans_probs", "emissions", "start_probabilities",
                       "start_probabilities_cols"):
                 assert np.array_equal(getattr(h, f), r[f]), (name, f)
+
+
+def test_corrupt_packed_files_are_rejected(api, tmp_path):
+    """Packed caches are validated against the file size before anything is allocated or copied: a bad symbol
+    width, non-monotonic offsets, oversized counts and out-of-range indices give an error, never a crash."""
+    import struct
+    from spec_viterbi_b200 import _lib
+    good = (GOLDEN / "seqs" / "0_test_seq.essb").read_bytes()
+    nseq, total, width = struct.unpack_from("<3Q", good, 8)
+    assert width == 1
+
+    def essb(nseq_, total_, width_, offs, payload):
+        return good[:8] + struct.pack("<3Q", nseq_, total_, width_) + struct.pack(f"<{len(offs)}Q", *offs) + payload
+
+    offs = list(struct.unpack_from(f"<{nseq + 1}Q", good, 32))
+    payload = good[32 + 8 * (nseq + 1):]
+    cases = {
+        "width8": essb(nseq, total, 8, offs, payload * 8),
+        "width3": essb(nseq, total, 3, offs, payload * 3),
+        "huge": essb(1 << 60, total, 1, offs, payload),
+        "nonmono": essb(nseq, total, 1, [0] + [total + 7] * (nseq - 1) + [total], payload),
+        "short": good[:-1],
+        "offs_beyond": essb(nseq, total, 1, offs[:-1] + [total + 7], payload),
+    }
+    for name, blob in cases.items():
+        p = tmp_path / f"{name}.essb"
+        p.write_bytes(blob)
+        with pytest.raises(_lib.SvError):
+            api.read_emit_seq(str(p))
+    hm = (GOLDEN / "models" / "0_test_chmm.chmmb").read_bytes()
+    states, emits, trans, nstart = struct.unpack_from("<4Q", hm, 8)
+    for name, hdr in {"states": (1 << 50, emits, trans, nstart), "trans": (states, emits, 1 << 61, nstart),
+                      "zero": (0, emits, trans, nstart)}.items():
+        p = tmp_path / f"{name}.chmmb"
+        p.write_bytes(hm[:8] + struct.pack("<4Q", *hdr) + hm[40:])
+        with pytest.raises(_lib.SvError):
+            api.read_HMM(str(p))
+    # a transition index >= states
+    bad = bytearray(hm)
+    at = 40 + nstart * 8 + states * emits * 4
+    struct.pack_into("<I", bad, at, states + 3)
+    (tmp_path / "idx.chmmb").write_bytes(bytes(bad))
+    with pytest.raises(_lib.SvError):
+        api.read_HMM(str(tmp_path / "idx.chmmb"))
