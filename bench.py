@@ -5,16 +5,21 @@
 
 One "step" = one pass of the plain (min,+) Viterbi recursion over one batch of sequences:
 workload `synthetic2405` (BASELINE.json configs[4]) = a seeded chmm_gen-style 2405-state HMM
-(nnz 7215, 20 symbols) x 4096 uniform random sequences of 7000 symbols PER GPU (weak scaling,
-sequences are independent; the HMM is replicated).  Metric = state-updates/s = S*T*N / seconds.
+(nnz 7215, 20 symbols) x ONE set of 4096 uniform random sequences of 7000 symbols, sharded over the
+N GPUs (strong scaling -- how the config is written; `--scaling weak` runs 4096 per GPU instead;
+sequences are independent, the HMM is replicated, the per-sequence (best, argmin) are all-gathered
+with NCCL inside the timed region).  Metric = state-updates/s = S*T*N / seconds.
 
   value     kernel throughput with the model and the packed symbols resident in HBM
   e2e       same metric through the host-buffer C-ABI call sv_viterbi_batch_u8 (pinned host
             symbols -> device, kernel, full final vectors + best scores -> pinned host)
-  roofline  dominant kernel (the persistent batched step) against the shared-memory crossbar
-            (128 B/clk/SM), the lower of its two ceilings; the non-tensor FP32 issue ceiling is
-            reported beside it (`fp32_issue`).  (min,+) is not an MMA contraction and the working
-            set lives in shared memory / registers, so neither HBM nor the tensor pipe bounds it
+  roofline  dominant kernel (the persistent batched step) against the non-tensor FP32 issue
+            ceiling north_star names; the shared-memory pipe -- the lower ceiling of the lockstep
+            kernel -- is reported beside it (`roofline.smem`) against a peak MEASURED live by the
+            micro-benchmark library.  (min,+) is not an MMA contraction and the working set lives
+            on chip, so neither HBM nor the tensor pipe bounds it
+  e2e.cold  model build + first batch with an empty plan cache (the reference's protocol times
+            the model rebuild in every call); e2e.warm_plan_cache: the same with the plan cached
   cpu_baseline  the oracle port (oracle/sv_oracle.c, OpenMP over sequences) on the host cores
 
 `--impl reference` times the reference's own CPU implementation (oracle/_ref = its
@@ -57,11 +62,12 @@ def load_peaks():
 def ncu_traffic(kernel_substr: str, workload: str):
     """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary
     (profiles/*_ncu_summary.txt, written by tools/ncu_summary.py); None if there is none for this workload."""
-    if workload != "synthetic2405":
-        return None, None
     best = None
-    for f in sorted((ROOT / "profiles").glob("*_ls_*ncu_summary.txt")):
-        if "profile2405" in f.name:
+    tag = {"synthetic2405": "_ls_", "profile2405": "_chain_"}.get(workload)
+    if tag is None:
+        return None, None
+    for f in sorted((ROOT / "profiles").glob(f"*{tag}*ncu_summary.txt")):
+        if workload == "synthetic2405" and "profile2405" in f.name:
             continue
         rd = wr = None
         ok = False
@@ -208,8 +214,8 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.workload, hmm, offs, 1),
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, hmm, offs.size - 1, T, args.gpus, args.scaling),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -217,16 +223,46 @@ def run_reference(args):
     emit_line(line)
 
 
-def workload_config(name, hmm, offs, n_gpus):
-    nseq = offs.size - 1
-    T = int(offs[1] - offs[0])
+def workload_config(name, hmm, nseq_total, T, n_gpus, scaling):
+    per = nseq_total // n_gpus if scaling == "strong" else nseq_total
     return {"workload": name, "states": int(hmm.states_num), "transitions": int(hmm.trans_num),
-            "symbols": int(hmm.emit_num), "sequences_per_gpu": int(nseq), "sequence_length": T,
-            "path": "plain (min,+) step, batched sequences", "parallelism": f"sequence-sharded x{n_gpus}",
+            "symbols": int(hmm.emit_num), "sequences_total": int(nseq_total if scaling == "strong" else nseq_total * n_gpus),
+            "sequences_per_gpu": int(per), "sequence_length": T,
+            "path": "plain (min,+) step, batched sequences",
+            "parallelism": (f"ONE {nseq_total}-sequence set sharded over {n_gpus} GPU(s) (sequence-sharded, HMM replicated), "
+                            "NCCL all-gather of (best, argmin) inside the timed region" if scaling == "strong" else
+                            f"{nseq_total} sequences per GPU x{n_gpus} (weak), HMM replicated"),
             "l2": "flushed between timed steps (256 MiB write)"}
 
 
+KERNEL_NAMES = {1: "sv_plain_generic_kernel", 2: "sv_es_kernel", 3: "sv_ls_kernel", 4: "sv_chain_kernel"}
+
+
+def run_probes(device_index):
+    """Measured ceilings of the step kernels, taken live with the micro-benchmark library (libsvprobe_b200.so)."""
+    import ctypes as C
+    from spec_viterbi_b200 import _lib
+    try:
+        pl = _lib.probe_lib()
+    except Exception as e:  # the probes are evidence, not the product: report and carry on
+        return {"error": str(e)}
+    out = {}
+    v, w = C.c_double(), C.c_double()
+    names = {0: "lds128_gather", 1: "lds128_3to1_sts128", 2: "ls_inner_loop", 3: "lds32"}
+    for mode, nm in names.items():
+        if pl.sv_probe_smem(device_index, mode, 6000, C.byref(v), C.byref(w)) == 0:
+            out[nm] = {"bytes_per_clk_per_sm": v.value, "lane_loads_per_clk_per_sm": w.value}
+    mixes = {0: "fadd", 1: "fmnmx", 2: "fmnmx3", 3: "2fadd_fmnmx3", 4: "4fadd_fmnmx3"}
+    fp = {}
+    for mix, nm in mixes.items():
+        if pl.sv_probe_fp32(device_index, mix, 4000, C.byref(v), C.byref(w)) == 0:
+            fp[nm] = {"lane_instr_per_s": v.value, "sm_clock_mhz": w.value}
+    out["fp32"] = fp
+    return out
+
+
 def run_b200(args):
+    import tempfile
     import torch
     import torch.distributed as dist
 
@@ -239,17 +275,65 @@ def run_b200(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    # a private, EMPTY plan cache: the first model creation below is the cold case on every box
+    cache_dir = tempfile.mkdtemp(prefix=f"svplan_r{rank}_")
+    os.environ["SV_PLAN_CACHE_DIR"] = cache_dir
 
-    from spec_viterbi_b200 import api, _lib
-    hmm, syms, offs = make_workload(args.workload, rank)
-    n, nseq, T = int(hmm.states_num), offs.size - 1, int(offs[1] - offs[0])
+    from spec_viterbi_b200 import api, _lib, sharding
+    strong = args.scaling == "strong"
+    # strong (default, BASELINE.json configs[4]): ONE set, every rank generates it from the same seed and takes its
+    # shard; weak: a different set of the same size per rank
+    hmm, syms_all, offs_all = make_workload(args.workload, 0 if strong else rank)
+    n, T = int(hmm.states_num), int(offs_all[1] - offs_all[0])
+    nseq_total = offs_all.size - 1
+    if strong:
+        parts = sharding.shard_sequences(np.diff(offs_all.astype(np.int64)), world)
+        mine = parts[rank]
+        syms, offs = sharding.take_sequences(syms_all, offs_all, mine) if world > 1 else (syms_all, offs_all)
+    else:
+        parts = [np.arange(nseq_total)]
+        mine = parts[0]
+        syms, offs = syms_all, offs_all
+    nseq = offs.size - 1
+
+    # ---- cold start: model build + first batch through the C ABI, K0 inside (the reference protocol times the
+    #      model rebuild in every call: bench_Viterbi.h:51-57, GraphBLAS_impl.cpp:24-45) ----
+    h_syms = torch.from_numpy(syms).pin_memory()
+    h_out = torch.empty((nseq, n), dtype=torch.float32).pin_memory()
+    h_best = torch.empty(nseq, dtype=torch.float32).pin_memory()
+    h_arg = torch.empty(nseq, dtype=torch.int32).pin_memory()
+    np_syms, np_out, np_best, np_arg = h_syms.numpy(), h_out.numpy(), h_best.numpy(), h_arg.numpy()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
     model = api.Model(hmm, device=local_rank)
-    if args.kernel == "generic":
-        model.set_kernel(_lib.KERNEL_GENERIC)
-    elif args.kernel == "es":
-        model.set_kernel(_lib.KERNEL_ES)
-    elif args.kernel == "ls":
-        model.set_kernel(_lib.KERNEL_LS)
+    t1 = time.perf_counter()
+    if args.kernel != "auto":
+        model.set_kernel({"generic": _lib.KERNEL_GENERIC, "es": _lib.KERNEL_ES, "ls": _lib.KERNEL_LS,
+                          "chain": _lib.KERNEL_CHAIN}[args.kernel])
+    model.viterbi_batch(np_syms, offs, out=np_out, best=np_best, arg=np_arg)
+    t2 = time.perf_counter()
+    cold = {"model_create_ms": (t1 - t0) * 1e3, "first_batch_ms": (t2 - t1) * 1e3,
+            "k0_plan_ms_inside_first_batch": float(model.info().plan_ms),
+            "value": float(nseq) * T * n * world / (t2 - t0), "unit": UNIT,
+            "what": "sv_model_create + first sv_viterbi_batch_u8 on a fresh process-level state with an EMPTY plan cache "
+                    "(lazy K0 plan of the chosen kernel, CUDA module load, workspace allocation, H2D/D2H all inside)"}
+    # the full colouring search (background thread) finishes and is stored in the plan cache; every timed number
+    # below runs on the final schedule
+    tp0 = time.perf_counter()
+    model.prepare()
+    cold["background_refine_wait_ms"] = (time.perf_counter() - tp0) * 1e3
+    # warm plan cache: a second fresh model (what every later process on this box pays)
+    t0 = time.perf_counter()
+    model2 = api.Model(hmm, device=local_rank)
+    t1 = time.perf_counter()
+    model2.viterbi_batch(np_syms, offs, out=np_out, best=np_best, arg=np_arg)
+    t2 = time.perf_counter()
+    warm = {"model_create_ms": (t1 - t0) * 1e3, "first_batch_ms": (t2 - t1) * 1e3,
+            "k0_plan_ms_inside_first_batch": float(model2.info().plan_ms),
+            "value": float(nseq) * T * n * world / (t2 - t0), "unit": UNIT,
+            "what": "the same with the finished plan in the on-disk plan cache"}
+    model2.close()
+
     info = model.info()
     seqs = model.upload(syms, offs)
     d_out = torch.empty((nseq, n), dtype=torch.float32, device=dev)
@@ -257,9 +341,12 @@ def run_b200(args):
     d_arg = torch.empty(nseq, dtype=torch.int32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
+    gather = sharding.BestGather(parts, nseq_total, dev) if strong else None
 
     def step():
         model.viterbi_device(seqs, d_out.data_ptr(), d_best.data_ptr(), d_arg.data_ptr(), stream.cuda_stream)
+        if gather is not None and world > 1:
+            gather.run(d_best, d_arg)  # NCCL all-gather of (best, argmin): 8 B per sequence, part of the step
 
     def barrier():
         if world > 1:
@@ -269,28 +356,29 @@ def run_b200(args):
     for _ in range(max(3, args.warmup)):
         step()
     barrier()
+    info = model.info()
 
     # ---- timed region: K steps, CUDA events around each step on the launching stream ----
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kevs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     with ClockSampler(physical_index(local_rank)) as clocks:
         barrier()
-        for a, b in evs:
+        for (a, b), (ka, kb) in zip(evs, kevs):
             flush.fill_(1)  # L2 flush, outside the event pair
             a.record(stream)
-            step()
+            ka.record(stream)
+            model.viterbi_device(seqs, d_out.data_ptr(), d_best.data_ptr(), d_arg.data_ptr(), stream.cuda_stream)
+            kb.record(stream)
+            if gather is not None and world > 1:
+                gather.run(d_best, d_arg)
             b.record(stream)
         barrier()
     step_ms = [a.elapsed_time(b) for a, b in evs]
+    kern_ms = [a.elapsed_time(b) for a, b in kevs]
     total_ms = float(sum(step_ms))
     launches = model.last_launches() * args.steps
 
     # ---- e2e: host buffers through the C ABI (pinned symbols in, vectors + best out) ----
-    h_syms = torch.from_numpy(syms).pin_memory()
-    h_out = torch.empty((nseq, n), dtype=torch.float32).pin_memory()
-    h_best = torch.empty(nseq, dtype=torch.float32).pin_memory()
-    h_arg = torch.empty(nseq, dtype=torch.int32).pin_memory()
-    np_syms, np_out, np_best, np_arg = h_syms.numpy(), h_out.numpy(), h_best.numpy(), h_arg.numpy()
-
     def e2e_step():
         model.viterbi_batch(np_syms, offs, out=np_out, best=np_best, arg=np_arg)
 
@@ -304,6 +392,16 @@ def run_b200(args):
     e2e_s = (time.perf_counter() - t0) / e2e_steps
     h2d = int(syms.nbytes + offs.nbytes + 4 * nseq)
     d2h = int(np_out.nbytes + np_best.nbytes + np_arg.nbytes)
+    # the reference boundary hands over std::vector<size_t>: the same through the uint64 entry point
+    h_syms64 = torch.from_numpy(syms.astype(np.uint64).view(np.int64)).pin_memory()
+    np_syms64 = h_syms64.numpy().view(np.uint64)
+    model.viterbi_batch(np_syms64, offs, out=np_out, best=np_best, arg=np_arg)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(2):
+        model.viterbi_batch(np_syms64, offs, out=np_out, best=np_best, arg=np_arg)
+    barrier()
+    e2e64_s = (time.perf_counter() - t0) / 2
 
     # parity spot check of what was timed (not part of the timing): rank 0, a few sequences
     if rank == 0:
@@ -314,21 +412,25 @@ def run_b200(args):
         got = d_out[:k].cpu().numpy()
         if not (np.array_equal(exp, got) and np.array_equal(exp, np_out[:k])):
             raise SystemExit("bench.py: GPU results differ from the oracle -- number is invalid")
+        if gather is not None and world > 1:  # the gathered (best, argmin) of MY shard sit at their original indices
+            gb, ga = gather.best.cpu().numpy(), gather.arg.cpu().numpy()
+            if not (np.array_equal(gb[mine], d_best.cpu().numpy()) and np.array_equal(ga[mine], d_arg.cpu().numpy())
+                    and np.isfinite(gb).all()):
+                raise SystemExit("bench.py: gathered best/argmin inconsistent -- number is invalid")
 
     # ---- second headline figure: spec precompute ms (level 2: emits^2 pair handlers), tuple-sharded
     #      over the ranks into one caller-owned table, completed by an all-gather of the shards ----
-    from spec_viterbi_b200 import sharding
     E = int(hmm.emit_num)
     ntup = E * E
     table = torch.empty((ntup, n, n), dtype=torch.float32, device=dev)
-    def timed_build(tb, te, gather):
+    def timed_build(tb, te, gather_shards):
         best_b, best_g = 1e30, 1e30
         for _ in range(3):
             barrier()
             t0 = time.perf_counter()
             sp = api.Spec(model, 2, _lib.SPEC_AUTO, tb, te, d_table=table[tb:te].data_ptr())  # synchronous
             t1 = time.perf_counter()
-            if gather:
+            if gather_shards:
                 sharding.all_gather_table(table, ntup)
             barrier()
             t2 = time.perf_counter()
@@ -339,19 +441,31 @@ def run_b200(args):
     rep_build_s, _ = timed_build(0, ntup, False)
     tb, te = sharding.shard_tuples(ntup, world, rank)
     spec_build_s, spec_gather_s = timed_build(tb, te, True) if world > 1 else (rep_build_s, 0.0)
+    # spec_with through the reference interface = fresh model + sv_spec_create (no K0 plan is built for it)
+    spec_with_s = 1e30
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        m3 = api.Model(hmm, device=local_rank)
+        sp = api.Spec(m3, 2, _lib.SPEC_AUTO, 0, ntup, d_table=table.data_ptr())
+        spec_with_s = min(spec_with_s, time.perf_counter() - t0)
+        sp.close()
+        m3.close()
     del table
 
     # ---- max over ranks ----
-    t = torch.tensor([total_ms, e2e_s, spec_build_s, spec_gather_s, rep_build_s], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e_s, spec_build_s, spec_gather_s, rep_build_s, e2e64_s, float(np.mean(kern_ms)),
+                      cold["model_create_ms"] + cold["first_batch_ms"], warm["model_create_ms"] + warm["first_batch_ms"],
+                      spec_with_s],
+                     dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        # gather of final scores (north star: NCCL only to gather results)
-        gathered = [torch.empty_like(d_best) for _ in range(world)]
-        dist.all_gather(gathered, d_best)
-    total_ms, e2e_s, spec_build_s, spec_gather_s, rep_build_s = (float(x) for x in t)
-    updates_per_step = float(nseq) * T * n * world
+    total_ms, e2e_s, spec_build_s, spec_gather_s, rep_build_s, e2e64_s, kernel_ms, cold_ms, warm_ms, spec_with_s = (float(x) for x in t)
+    updates_per_step = float(nseq_total) * T * n * (1 if strong else world)
     value = updates_per_step * args.steps / (total_ms * 1e-3)
     e2e_value = updates_per_step / e2e_s
+    cold["value"] = updates_per_step / (cold_ms * 1e-3)
+    warm["value"] = updates_per_step / (warm_ms * 1e-3)
 
     if rank == 0:
         peaks, peak_kind = load_peaks()
@@ -359,52 +473,64 @@ def run_b200(args):
         sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
         mhz = clk["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)
         relax = float(nseq) * (T - 1) * int(info.nnz)          # relaxations per launch (per GPU)
-        kernel_s = float(np.mean(step_ms)) * 1e-3
-        # algorithmic ops: one add + one min per stored transition; peak = FP32 issue
-        # bound of a (min,+) MAC = 1 FADD + 1/2 FMNMX3 = 1.5 slots on 128 lanes/SM at the SM clock
-        # measured during the run
+        kernel_s = kernel_ms * 1e-3
+        probes = run_probes(local_rank)
+        # K2's ceilings.  Top level = the one north_star names: non-tensor FP32 issue.  algorithmic ops =
+        # 2 per relaxation (one add + one min per stored transition); peak = 2 ops per (min,+) MAC, a MAC costing
+        # 1 FADD + 1/2 FMNMX3 = 1.5 issue slots of the 128 lanes/SM at the SM clock measured during the run.
         achieved = 2.0 * relax / kernel_s / 1e12
         peak = 2.0 * sm_count * 128 * mhz * 1e6 / 1.5 / 1e12
-        traffic, traffic_src = ncu_traffic("sv_ls_kernel", args.workload) if info.kernel == _lib.KERNEL_LS else (None, None)
+        kname = KERNEL_NAMES.get(int(info.kernel), "?")
+        traffic, traffic_src = ncu_traffic(kname, args.workload)
         xbar_bytes = 4.0 * relax + 4.0 * nseq * T * n   # 4 B gathered per relaxation + 4 B stored per state update
-        xbar_peak = sm_count * 128 * mhz * 1e6          # shared-memory crossbar: 128 B/clk/SM at the measured SM clock
-        # K2 has two ceilings: FP32 issue and the shared-memory crossbar.  The crossbar is the
-        # LOWER one (9.3e12 vs 2.5e13 relaxations/s) and the one ncu shows saturating, so it is the roofline
-        # reported at the top level; the FP32-issue figure sits beside it.  Neither "hbm" nor "tensor"
-        # bounds this kernel: its HBM traffic is the symbol stream in and the final vectors out.
-        roofline = {"bound": "smem", "achieved": xbar_bytes / kernel_s / 1e9, "peak": xbar_peak / 1e9, "unit": "GB/s",
-                    "frac": xbar_bytes / kernel_s / xbar_peak, "traffic": traffic, "traffic_source": traffic_src,
-                    "kernel": {_lib.KERNEL_ES: "sv_es_kernel", _lib.KERNEL_LS: "sv_ls_kernel"}.get(info.kernel, "sv_plain_generic_kernel"),
-                    "relaxations_per_launch": relax, "relax_per_clk_per_sm": relax / kernel_s / (sm_count * mhz * 1e6),
-                    "peak_source": f"shared-memory crossbar, {sm_count} SMs x 128 B/clk x {mhz:.0f} MHz (NVML median during the "
-                                   f"run); algorithmic bytes = 4 B gathered per relaxation + 4 B stored per state update; "
-                                   f"MEASURED_PEAKS.json ({peak_kind}) holds only HBM/bf16 peaks, neither of which bounds this kernel",
-                    "fp32_issue": {"achieved_TFLOPs": achieved, "peak_TFLOPs": peak, "frac": achieved / peak,
-                                   "peak_source": "128 lanes/SM at the same clock / 1.5 issue slots per (min,+) MAC "
-                                                  "(1 FADD + 1/2 FMNMX3); algorithmic ops = 2 per relaxation"},
+        smem_probe = probes.get("lds128_3to1_sts128", {}).get("bytes_per_clk_per_sm")
+        xbar_peak = sm_count * (smem_probe or 128.0) * mhz * 1e6
+        roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": traffic, "traffic_source": traffic_src, "kernel": kname,
+                    "kernel_ms": kernel_ms, "relaxations_per_launch": relax,
+                    "relax_per_clk_per_sm": relax / kernel_s / (sm_count * mhz * 1e6),
+                    "peak_source": f"non-tensor FP32 issue: {sm_count} SMs x 128 lanes x {mhz:.0f} MHz (NVML median during the "
+                                   "run) x 2 ops / 1.5 issue slots per (min,+) MAC (1 FADD + 1/2 FMNMX3); algorithmic ops = 2 per "
+                                   "relaxation.  The oracle's association needs 2 FADD per relaxation (2.5 slots), so 0.6 is the "
+                                   f"highest fraction any bit-exact kernel can reach.  MEASURED_PEAKS.json ({peak_kind}) holds "
+                                   "HBM/bf16 peaks only; neither bounds this kernel (bound is not 'hbm'/'tensor': the working set "
+                                   "lives on chip and (min,+) is not an MMA contraction)",
+                    "smem": {"achieved_GBs": xbar_bytes / kernel_s / 1e9, "peak_GBs": xbar_peak / 1e9,
+                             "frac": xbar_bytes / kernel_s / xbar_peak,
+                             "peak_source": ("MEASURED live: sv_probe_smem mode 1 (conflict-free LDS.128 gathers : STS.128 = 3 : 1, "
+                                             "16 warps/SM) x SMs x SM clock" if smem_probe else
+                                             "theoretical 128 B/clk/SM (probe library unavailable)"),
+                             "algorithmic_bytes": "4 B gathered per relaxation + 4 B stored per state update (lockstep kernel "
+                                                  "only; the chain kernel gathers nothing)"},
                     "hbm_algorithmic_gbs": (syms.nbytes + d_out.numel() * 4) / kernel_s / 1e9,
-                    "hbm_peak_gbs": peaks.get("hbm_gbs")}
+                    "hbm_peak_gbs": peaks.get("hbm_gbs"), "probes": probes}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.workload, hmm, offs, world),
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.workload, hmm, nseq_total, T, world, args.scaling),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "sv_viterbi_batch_u8 (host u8 symbols -> final vectors + best score/state)"},
+                    "api": "sv_viterbi_batch_u8 (host u8 symbols -> final vectors + best score/state), per rank on its shard",
+                    "u64_entry": {"value": updates_per_step / e2e64_s, "h2d_bytes_per_step": int(np_syms64.nbytes),
+                                  "api": "sv_viterbi_batch (the reference's vector<size_t> symbols: packed to u8 on the host, then copied)"},
+                    "cold": cold, "warm_plan_cache": warm},
+            "model_create_ms": cold["model_create_ms"],
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
-            "kernel": {"name": roofline["kernel"], "es_threads": int(info.es_threads),
-                       "es_seqs_per_cta": int(info.es_seqs_per_cta), "es_smem_bytes": int(info.es_smem_bytes),
-                       "ls_seqs_per_cta": int(info.ls_seqs_per_cta), "ls_smem_bytes": int(info.ls_smem_bytes),
-                       "ls_tmem_cols": int(info.ls_tmem_cols),
+            "kernel": {"name": kname, "seqs_per_cta": int(info.ls_seqs_per_cta if info.kernel == _lib.KERNEL_LS else
+                                                        info.chain_seqs_per_cta if info.kernel == _lib.KERNEL_CHAIN else
+                                                        info.es_seqs_per_cta),
+                       "ls_smem_bytes": int(info.ls_smem_bytes), "ls_tmem_cols": int(info.ls_tmem_cols),
                        "ls_gather_wavefronts": int(info.ls_gather_wavefronts),
-                       "ls_gather_ideal": int(info.ls_gather_ideal),
-                       "step_ms": step_ms},
+                       "ls_gather_ideal": int(info.ls_gather_ideal), "ls_sa_iters": int(info.ls_sa_iters),
+                       "chain_threads": int(info.chain_threads), "plan_ms": float(info.plan_ms),
+                       "step_ms": step_ms, "kernel_only_ms": kern_ms},
         }
         table_gb = ntup * n * n * 4 / 1e9
         sharded_ms = (spec_build_s + spec_gather_s) * 1e3
         line["spec_precompute"] = {
             "level": 2, "handlers": ntup, "table_GB": table_gb,
             "precompute_ms": min(rep_build_s * 1e3, sharded_ms) if world > 1 else rep_build_s * 1e3,
+            "spec_with_ms": spec_with_s * 1e3,
             "strategy": "replicated" if world == 1 or rep_build_s * 1e3 <= sharded_ms else "tuple-sharded + all-gather",
             "replicated_build_ms": rep_build_s * 1e3,
             "sharded_build_ms": spec_build_s * 1e3 if world > 1 else None,
@@ -413,13 +539,17 @@ def run_b200(args):
             "write_GBs_per_gpu": table_gb / rep_build_s,
             "frac_of_hbm": table_gb / rep_build_s / peaks.get("hbm_gbs", 6546.2),
             "timing": "wall clock around the synchronous sv_spec_create into a caller-owned table (every GPU holds "
-                      "the whole table afterwards), min of 3, max over ranks"}
-        if not args.no_cpu:
+                      "the whole table afterwards), min of 3, max over ranks; spec_with_ms = fresh sv_model_create + "
+                      "sv_spec_create (what Viterbi_spec_impl::spec_with costs through the reference interface)"}
+        if not args.no_cpu and world == 1:  # rank 0 at N = 1 only (the contract)
             line["cpu_baseline"] = cpu_port_baseline(hmm, syms, offs)
         emit_line(line)
+    model.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    import shutil
+    shutil.rmtree(cache_dir, ignore_errors=True)
 
 
 _JSON_OUT = None
@@ -447,7 +577,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="synthetic2405", choices=sorted(WORKLOADS))
-    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "es", "ls"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "es", "ls", "chain"])
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default): ONE 4096-sequence set sharded over the GPUs, as BASELINE.json configs[4] is "
+                         "written; weak: 4096 sequences per GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

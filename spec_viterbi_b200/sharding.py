@@ -76,6 +76,45 @@ def gather_best(local_best, local_arg, idx: np.ndarray, nseq_total: int, group=N
     return best, arg
 
 
+class BestGather:
+    """Device-side all-gather of (best score, best state) with NO host synchronisation: every rank knows the
+    deal (shard_sequences is deterministic), so only the payload travels -- 8 bytes per sequence.  Buffers are
+    allocated once; `run` may sit inside a timed region / be enqueued behind the step kernel."""
+
+    def __init__(self, parts, nseq_total: int, device, group=None):
+        import torch
+        self.group = group
+        self.world = len(parts)
+        self.cap = max(int(p.size) for p in parts)
+        self.recv_best = torch.empty((self.world, self.cap), dtype=torch.float32, device=device)
+        self.recv_arg = torch.empty((self.world, self.cap), dtype=torch.int32, device=device)
+        self.send_best = torch.full((self.cap,), float("inf"), dtype=torch.float32, device=device)
+        self.send_arg = torch.full((self.cap,), -1, dtype=torch.int32, device=device)
+        # scatter map: position (rank, k) of the receive buffer -> original sequence index
+        src = np.concatenate([r * self.cap + np.arange(p.size) for r, p in enumerate(parts)])
+        dst = np.concatenate(parts)
+        self.src = torch.as_tensor(src, dtype=torch.int64, device=device)
+        self.dst = torch.as_tensor(dst, dtype=torch.int64, device=device)
+        self.best = torch.empty(nseq_total, dtype=torch.float32, device=device)
+        self.arg = torch.empty(nseq_total, dtype=torch.int32, device=device)
+
+    def run(self, local_best, local_arg):
+        """local_*: this rank's results in the order of its shard.  Returns (best, arg) in original order."""
+        import torch.distributed as dist
+        k = local_best.numel()
+        self.send_best[:k].copy_(local_best)
+        self.send_arg[:k].copy_(local_arg)
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.recv_best.view(-1), self.send_best, group=self.group)
+            dist.all_gather_into_tensor(self.recv_arg.view(-1), self.send_arg, group=self.group)
+        else:
+            self.recv_best[0].copy_(self.send_best)
+            self.recv_arg[0].copy_(self.send_arg)
+        self.best.index_copy_(0, self.dst, self.recv_best.view(-1).index_select(0, self.src))
+        self.arg.index_copy_(0, self.dst, self.recv_arg.view(-1).index_select(0, self.src))
+        return self.best, self.arg
+
+
 def all_gather_table(table, ntuples: int, group=None) -> None:
     """In-place all-gather of a [ntuples, n, n] handler table whose rank-r slice
     [shard_tuples(ntuples, world, r)] has been computed locally."""

@@ -24,7 +24,7 @@ def run(cfg, model, seqfile, kernel=None):
     lens = np.diff(offs.astype(np.int64))
     n = hmm.states_num
     print(json.dumps({"config": cfg, "model": model, "states": int(n), "nnz": int(m.info().nnz), "sequences": len(seqs),
-                      "longest": int(lens.max()), "total_symbols": int(lens.sum()), "kernel": int(m.info().kernel),
+                      "longest": int(lens.max()), "total_symbols": int(lens.sum()), "kernel": int(m.info().kernel), "seqs_per_cta": int(m.info().chain_seqs_per_cta or m.info().es_seqs_per_cta),
                       "ms_per_call_host_to_host": ms, "us_per_step_critical_path": ms * 1e3 / float(lens.max()),
                       "state_updates_per_s": float(lens.sum()) * n / (ms * 1e-3)}), flush=True)
     m.close()
@@ -32,5 +32,7 @@ def run(cfg, model, seqfile, kernel=None):
 if __name__ == "__main__":
     run("configs[1]: 1200.chmm x emit_3_3500_20, plain", "1200", "emit_3_3500_20")
     run("configs[3]: 2405.chmm x covid-19 (16 ragged sequences, longest 7096), plain", "2405", "covid-19")
+    run("configs[1] on the edge-stationary kernel (round-1 choice)", "1200", "emit_3_3500_20", _lib.KERNEL_ES)
+    run("configs[3] on the edge-stationary kernel (round-1 choice)", "2405", "covid-19", _lib.KERNEL_ES)
     run("configs[1] on the generic kernel", "1200", "emit_3_3500_20", _lib.KERNEL_GENERIC)
     run("configs[3] on the lockstep kernel", "2405", "covid-19", _lib.KERNEL_LS)
