@@ -17,7 +17,8 @@ const char* sv_probe_last_error(void);
 /* FP32 pipe probe used to fix the non-tensor roofline: runs `iters` dependent-chain iterations of the
  * chosen instruction mix on every SM and returns lane-instructions/s.
  * mix: 0 = FADD, 1 = FMNMX (2-input min), 2 = FMNMX3 (3-input min), 3 = 2 FADD + 1 FMNMX3,
- *      4 = 4 FADD + 1 FMNMX3 (the oracle-order relaxation pair), 5 = LDS.32 conflict-free + 2 FADD + FMNMX */
+ *      4 = 4 FADD + 1 FMNMX3 (the oracle-order relaxation pair), 5 = LDS.32 conflict-free + 2 FADD + FMNMX,
+ *      6 = FADD2 (packed add.rn.f32x2, counted as two adds), 7 = 2 FADD2 + 1 FMNMX3 (the same pair, packed) */
 int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_per_s, double* sm_clock_mhz);
 
 /* Tensor-memory probe: fills all 512 TMEM columns of every SM through tcgen05.st, reads them back with

@@ -405,7 +405,7 @@ bool sv_model_ensure_chain(sv_model* m) {
     for (const int q : {8, 4, 2, 1}) {
         size_t smem = 0;
         int per_sm = 0;
-        if (sv_chain_prepare(m->chain.threads, q, &smem, &per_sm) != 0) {
+        if (sv_chain_prepare(m->chain.threads, q, m->chain.nonneg, &smem, &per_sm) != 0) {
             cudaGetLastError();
             m->chain.valid = false;
             return false;

@@ -165,7 +165,7 @@ void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, c
         for (const float x : csr.w) nn &= ok(x);
         for (const float x : emis) nn &= ok(x);
         for (const float x : start) nn &= ok(x);
-        p.nonneg = nn;
+        p.nonneg = nn; // selects the kernel instantiation whose REDUX needs no order-preserving key
     }
     p.valid = true;
 }

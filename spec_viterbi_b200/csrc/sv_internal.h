@@ -241,7 +241,7 @@ struct SvChainDev {
 void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, const std::vector<float>& start,
                          uint64_t emits, SvChainPlan* plan);
 // sequences per CTA that are compiled: 8, 4, 2, 1
-int sv_chain_prepare(int threads, int q, size_t* smem_out, int* ctas_per_sm_out);
+int sv_chain_prepare(int threads, int q, bool nonneg, size_t* smem_out, int* ctas_per_sm_out);
 int sv_chain_launch(int threads, int q, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
                     int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
 

@@ -5,15 +5,15 @@
 //
 // One persistent CTA walks all time steps of Q = 8 / 4 / 2 / 1 sequences in lockstep:
 //   * a thread owns SV_CHAIN_RPT = 5 consecutive chain positions; v_{t-1} of its positions for all Q
-//     sequences lives in registers and is updated in place from the highest position down, so the
-//     band edge (p-1) -> p is a register read; only rank 0 needs the neighbouring lane (one SHFL per
-//     sequence and step; lane 0 takes the previous warp's last score from shared memory);
+//     sequences lives in registers and is updated in place, so the band edge (p-1) -> p is a register
+//     read; only position 0 of a thread needs its neighbour's last score, which every thread publishes
+//     as one 16-byte shared-memory vector per 4 sequences and step (read back the same way);
 //   * the hub state's score (special 0, the N state) is a broadcast shared-memory read;
 //   * the two dense rows (N and C) need only min_k v[k] over the chain because all their chain
 //     in-edges carry one weight (K0 checks it): fl(c + x) is monotone, so
 //     min_k fl(fl(E+u) + v[k]) == fl(fl(E+u) + min_k v[k]) bit for bit.  Each thread folds its five
 //     new scores into a running minimum, one integer REDUX per sequence reduces it over the warp
-//     (all scores >= 0: float order = signed-int order), warp w < Q finishes sequence w's two
+//     (scores >= 0: float order = signed-int order; else through an order-preserving key), warp w < Q finishes sequence w's two
 //     special rows in the NEXT step from the per-warp partials -- one barrier per step;
 //   * the emission table lives in TENSOR MEMORY (lane = thread's lane in its warp quadrant, column =
 //     (warp group, symbol, rank)); E[o][own positions] is one tcgen05.ld.x4 + .x1 with a run-time
@@ -22,16 +22,67 @@
 //     steps ahead, exactly as in the lockstep kernel (sv_plain_ls.cu); finished sequences are
 //     written out with their (best, argmin) and replaced from a global longest-first queue.
 //
-// Per (position, sequence) and step: 4 FADD + 1 FMNMX + 0.4 FMNMX3 for FOUR transitions -- no
-// per-relaxation shared-memory traffic is left, so the kernel is bound by FP32 issue.
+// Per (position, sequence) and step: 4 IEEE adds (16 of 20 per sequence as packed FADD2) + 1 FMNMX + 0.4
+// FMNMX3 for FOUR transitions -- no per-relaxation shared-memory traffic is left, so the kernel is bound by
+// FP32 issue.
 // Tensor cores are not used ((min,+) is not an MMA contraction); only their memory is.
 #include "sv_ls_device.cuh"
+
+#include <cstdlib>
 
 namespace {
 
 constexpr int kChainHeStride = 256 * SV_CHAIN_RPT; // special-row emissions indexed by symbol * RPT
 
-template <int TPG, int Q>
+// N consecutive floats of shared memory as ONE load / store (N = 1, 2, 4; p aligned to 4 N bytes)
+template <int N> __device__ __forceinline__ void lds_vec(const float* p, float (&x)[N]) {
+    if constexpr (N == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        x[0] = t.x; x[1] = t.y; x[2] = t.z; x[3] = t.w;
+    } else if constexpr (N == 2) {
+        const float2 t = *reinterpret_cast<const float2*>(p);
+        x[0] = t.x; x[1] = t.y;
+    } else {
+        x[0] = *p;
+    }
+}
+template <int N> __device__ __forceinline__ void sts_vec(float* p, const float (&x)[N]) {
+    if constexpr (N == 4) *reinterpret_cast<float4*>(p) = make_float4(x[0], x[1], x[2], x[3]);
+    else if constexpr (N == 2) *reinterpret_cast<float2*>(p) = make_float2(x[0], x[1]);
+    else *p = x[0];
+}
+
+// Warp-wide minimum on the integer REDUX unit.  NN (every score >= 0 or -0 / +inf, checked by K0): the signed-int
+// order of the bit patterns IS the float order.  Otherwise (two of the reference's shipped models, 200.chmm and
+// 400.chmm, carry one transition with "probability" > 1, i.e. a negative weight) the bits are first mapped to an
+// order-preserving key -- flip the low 31 bits of negative values -- and mapped back (the map is an involution).
+template <bool NN> __device__ __forceinline__ float warp_min_redux(float x) {
+    int i = __float_as_int(x);
+    if constexpr (!NN) i ^= (i >> 31) & 0x7fffffff;
+    i = __reduce_min_sync(0xffffffffu, i);
+    if constexpr (!NN) i ^= (i >> 31) & 0x7fffffff;
+    return __int_as_float(i);
+}
+
+// Packed IEEE adds (sm_100+: add.rn.f32x2 -> FADD2): two independent round-to-nearest fp32 adds in ONE
+// instruction on a 64-bit register pair.  Each half is an ordinary IEEE add, so the bits are the oracle's; 16 of
+// the 20 adds per sequence pair up (positions 1,2 and 3,4 of a thread with their band predecessors 0,1 and 2,3).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 p, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(p));
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+template <int TPG, int Q, bool NN, bool PK>
 __global__ void __launch_bounds__(TPG, 512 / TPG)
 sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict__ best,
                 int32_t* __restrict__ arg, unsigned* __restrict__ counter) {
@@ -45,8 +96,12 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     __shared__ LsCtl ctl[4];
     __shared__ LsMgr mgr[8];
     __shared__ uint32_t s_taddr;
+    constexpr int QV = Q >= 4 ? 4 : Q; // sequences per shared-memory vector (float4 / float2 / float)
+    constexpr int NG = Q / QV;         // vectors per thread and step
     __shared__ __align__(16) float s_red[2][NW][QS]; // [parity][warp][q] chain minimum of the warp
-    __shared__ __align__(16) float s_bnd[2][NW][QS]; // [parity][warp][q] score at the warp's last position
+    // s_top[parity][group][1 + tid] = score of thread tid's LAST position for the QV sequences of the group: the
+    // band edge into the next thread's first position.  Entry 0 (the predecessor of position 0) stays +inf.
+    __shared__ __align__(16) float s_top[2][NG][(TPG + 1) * QV];
     __shared__ __align__(16) float s_vs[2][SV_CHAIN_NSP][QS]; // [parity][special][q]
     __shared__ float s_he[SV_CHAIN_NSP * kChainHeStride];
     __shared__ float s_bv[NW];
@@ -65,18 +120,19 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     const uint32_t tbase = s_taddr;
     const uint32_t tE = tbase + (static_cast<uint32_t>(warp & 3) << 21) +
                         static_cast<uint32_t>(warp >> 2) * static_cast<uint32_t>(m.emits * RS);
+    // column order of a symbol's five scores: positions 0..4, or (packed adds) 1,2,3,4,0 so that the x4 load
+    // delivers the pairs (1,2) and (3,4) in aligned register pairs
     for (int o = 0; o < m.emits; ++o)
         for (int r = 0; r < R; ++r)
-            tmem_st1(tE + static_cast<uint32_t>(o * RS + r), m.emis_p[static_cast<size_t>(o) * n_pos + tid * R + r]);
+            tmem_st1(tE + static_cast<uint32_t>(o * RS + (PK ? (r == 0 ? R - 1 : r - 1) : r)),
+                     m.emis_p[static_cast<size_t>(o) * n_pos + tid * R + r]);
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     for (int i = tid; i < SV_CHAIN_NSP * m.emits; i += TPG) {
         const int h = i / m.emits, o = i % m.emits;
         s_he[h * kChainHeStride + o * RS] = m.emis_s[i];
     }
-    for (int i = tid; i < 2 * NW * QS; i += TPG) {
-        (&s_red[0][0][0])[i] = pos_inf();
-        (&s_bnd[0][0][0])[i] = pos_inf();
-    }
+    for (int i = tid; i < 2 * NW * QS; i += TPG) (&s_red[0][0][0])[i] = pos_inf();
+    for (int i = tid; i < 2 * NG * (TPG + 1) * QV; i += TPG) (&s_top[0][0][0])[i] = pos_inf();
     if (tid < 2 * SV_CHAIN_NSP * QS) (&s_vs[0][0][0])[tid] = pos_inf();
 
     float wp[R], wh[R];
@@ -85,13 +141,14 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
         wp[r] = m.w_pred[tid * R + r];
         wh[r] = m.w_hub[tid * R + r];
     }
+    [[maybe_unused]] const f32x2 wp12 = pack2(wp[1], wp[2]), wp34 = pack2(wp[3], wp[4]);
+    [[maybe_unused]] const f32x2 wh12 = pack2(wh[1], wh[2]), wh34 = pack2(wh[3], wh[4]);
     // special rows: lane s of a warp finishes special s
     // (no run-time indexing into the kernel parameters: that would move the whole struct to local memory)
     static_assert(SV_CHAIN_NSP == 2, "two specials");
     const bool sp1 = lane == 1;
     const float sp_u = sp1 ? m.u[1] : m.u[0], sp_s0 = sp1 ? m.ss[1][0] : m.ss[0][0];
     const float sp_s1 = sp1 ? m.ss[1][1] : m.ss[0][1], sp_start = sp1 ? m.start_s[1] : m.start_s[0];
-    const bool nonneg = m.nonneg != 0;
     const float* __restrict__ start_p = m.start_p + tid * R;
 
     float v[Q][R];
@@ -175,8 +232,8 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
 
     uint32_t tau = 0;
     for (;;) {
-        const uint32_t init_mask = fl.x, fin_mask = fl.y, act = fl.z;
-        if (act == 0) break;
+        const uint32_t init_mask = fl.x, fin_mask = fl.y;
+        if (fl.z == 0) break; // no sequence takes part in this step: the CTA is done
         const uint32_t bo = tau & 1u, bi = bo ^ 1u; // buffers written / read in this step
         const uint32_t cols[8] = {cA.x, cA.y, cA.z, cA.w, cB.x, cB.y, cB.z, cB.w};
 
@@ -206,14 +263,9 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
 #pragma unroll
         for (int q0 = 0; q0 < Q; q0 += NW) {
             const int q = q0 + warp;
-            if (q < Q && ((act >> q) & 1u)) {
+            if (q < Q) {
                 float mm = lane < NW ? s_red[bi][lane][q] : pos_inf();
-                if (nonneg) {
-                    mm = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(mm)));
-                } else {
-#pragma unroll
-                    for (int d = 16; d > 0; d >>= 1) mm = fminf(mm, __shfl_xor_sync(0xffffffffu, mm, d));
-                }
+                mm = warp_min_redux<NN>(mm);
                 if (lane < SV_CHAIN_NSP) {
                     const float e = s_he[lane * kChainHeStride + ctl[tau & 3u].col[q]];
                     float x = relax1(e, sp_u, mm);
@@ -224,22 +276,39 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             }
         }
 
-        // ---- chain positions ----
-        float redv[Q], bndv[Q];
-        auto seq_step = [&](auto qc) {
+        // ---- chain positions, one group of QV sequences at a time.  Idle sequence slots are relaxed like the
+        //      others (their scores are never read: cheaper than a branch per sequence); everything a sequence
+        //      needs from other threads arrives as ONE vector load per group: the hub score and the band
+        //      predecessor of this thread's first position ----
+        auto seq_step = [&](auto qc, float hub, float pv, float& red) {
             constexpr int q = decltype(qc)::value;
             uint32_t(&ec)[5] = (q & 1) ? eB : eA;
             uint32_t(&en)[5] = (q & 1) ? eA : eB;
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]));
             if constexpr (q + 1 < Q) tmem_ld5(tE + cols[q + 1 < Q ? q + 1 : 0], en);
-            redv[q] = pos_inf();
-            bndv[q] = pos_inf();
-            if ((act >> q) & 1u) {
-                const float hub = s_vs[bi][0][q];
-                float pv = __shfl_up_sync(0xffffffffu, v[q][R - 1], 1);
-                const float wb = warp > 0 ? s_bnd[bi][warp > 0 ? warp - 1 : 0][q] : pos_inf();
-                if (lane == 0) pv = wb;
+            if constexpr (PK) {
+                // ec = E of positions 1,2,3,4,0.  Band predecessors of (1,2) are (0,1), of (3,4) are (2,3).
+                const f32x2 e12 = pack2(__uint_as_float(ec[0]), __uint_as_float(ec[1]));
+                const f32x2 e34 = pack2(__uint_as_float(ec[2]), __uint_as_float(ec[3]));
+                const float e0 = __uint_as_float(ec[4]);
+                const f32x2 hh = pack2(hub, hub);
+                const f32x2 a12 = add2(add2(e12, wp12), pack2(v[q][0], v[q][1]));
+                const f32x2 a34 = add2(add2(e34, wp34), pack2(v[q][2], v[q][3]));
+                const f32x2 b12 = add2(add2(e12, wh12), hh);
+                const f32x2 b34 = add2(add2(e34, wh34), hh);
+                const float a0 = relax1(e0, wp[0], pv), b0 = relax1(e0, wh[0], hub);
+                float a1, a2, a3, a4, b1, b2, b3, b4;
+                unpack2(a12, a1, a2);
+                unpack2(a34, a3, a4);
+                unpack2(b12, b1, b2);
+                unpack2(b34, b3, b4);
+                v[q][0] = fminf(a0, b0);
+                v[q][1] = fminf(a1, b1);
+                v[q][2] = fminf(a2, b2);
+                v[q][3] = fminf(a3, b3);
+                v[q][4] = fminf(a4, b4);
+            } else {
                 float e[R];
 #pragma unroll
                 for (int r = 0; r < R; ++r) e[r] = __uint_as_float(ec[r]);
@@ -248,30 +317,29 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
                     const float prev = r > 0 ? v[q][r - 1] : pv;
                     v[q][r] = fminf(relax1(e[r], wp[r], prev), relax1(e[r], wh[r], hub));
                 }
-                float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
-                mq = fminf(mq, fminf(v[q][3], v[q][4]));
-                if (nonneg) {
-                    mq = __int_as_float(__reduce_min_sync(0xffffffffu, __float_as_int(mq)));
-                } else {
-#pragma unroll
-                    for (int d = 16; d > 0; d >>= 1) mq = fminf(mq, __shfl_xor_sync(0xffffffffu, mq, d));
-                }
-                redv[q] = mq;
-                bndv[q] = v[q][R - 1];
             }
+            float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
+            mq = fminf(mq, fminf(v[q][3], v[q][4]));
+            red = warp_min_redux<NN>(mq);
         };
-        seq_step(std::integral_constant<int, 0>{});
-        if constexpr (Q > 1) seq_step(std::integral_constant<int, 1>{});
-        if constexpr (Q > 2) {
-            seq_step(std::integral_constant<int, 2>{});
-            seq_step(std::integral_constant<int, 3>{});
-        }
-        if constexpr (Q > 4) {
-            seq_step(std::integral_constant<int, 4>{});
-            seq_step(std::integral_constant<int, 5>{});
-            seq_step(std::integral_constant<int, 6>{});
-            seq_step(std::integral_constant<int, 7>{});
-        }
+        auto group_step = [&](auto gc) {
+            constexpr int g = decltype(gc)::value;
+            float hub[QV], pv[QV], red[QV], top[QV];
+            lds_vec<QV>(&s_vs[bi][0][g * QV], hub);
+            lds_vec<QV>(&s_top[bi][g][tid * QV], pv);
+            seq_step(std::integral_constant<int, g * QV>{}, hub[0], pv[0], red[0]);
+            if constexpr (QV > 1) seq_step(std::integral_constant<int, g * QV + (QV > 1 ? 1 : 0)>{}, hub[QV > 1 ? 1 : 0], pv[QV > 1 ? 1 : 0], red[QV > 1 ? 1 : 0]);
+            if constexpr (QV > 2) {
+                seq_step(std::integral_constant<int, g * QV + (QV > 2 ? 2 : 0)>{}, hub[QV > 2 ? 2 : 0], pv[QV > 2 ? 2 : 0], red[QV > 2 ? 2 : 0]);
+                seq_step(std::integral_constant<int, g * QV + (QV > 2 ? 3 : 0)>{}, hub[QV > 2 ? 3 : 0], pv[QV > 2 ? 3 : 0], red[QV > 2 ? 3 : 0]);
+            }
+#pragma unroll
+            for (int j = 0; j < QV; ++j) top[j] = v[g * QV + j][R - 1];
+            sts_vec<QV>(&s_top[bo][g][(tid + 1) * QV], top);
+            if (lane == 0) sts_vec<QV>(&s_red[bo][warp][g * QV], red);
+        };
+        group_step(std::integral_constant<int, 0>{});
+        if constexpr (NG > 1) group_step(std::integral_constant<int, (NG > 1 ? 1 : 0)>{});
         // ---- rare: first step of a sequence, v_0 = E[o_0] + start replaces the relaxed scores (a real
         //      branch around everything, so the hot path carries no predicated loads) ----
         if (init_mask != 0) {
@@ -283,10 +351,9 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
                 for (int r = 0; r < R; ++r) v[q][r] = em[r] + start_p[r];
                 float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
                 mq = fminf(mq, fminf(v[q][3], v[q][4]));
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) mq = fminf(mq, __shfl_xor_sync(0xffffffffu, mq, d));
-                redv[q] = mq;
-                bndv[q] = v[q][R - 1];
+                mq = warp_min_redux<NN>(mq);
+                s_top[bo][q / QV][(tid + 1) * QV + q % QV] = v[q][R - 1];
+                if (lane == 0) s_red[bo][warp][q] = mq;
             };
             init_fix(std::integral_constant<int, 0>{});
             if constexpr (Q > 1) init_fix(std::integral_constant<int, 1>{});
@@ -300,14 +367,6 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
                 init_fix(std::integral_constant<int, 6>{});
                 init_fix(std::integral_constant<int, 7>{});
             }
-        }
-        if (lane == 0) {
-#pragma unroll
-            for (int q = 0; q < Q; ++q) s_red[bo][warp][q] = redv[q];
-        }
-        if (lane == 31) {
-#pragma unroll
-            for (int q = 0; q < Q; ++q) s_bnd[bo][warp][q] = bndv[q];
         }
 
         // control block of step tau + 1 (published during step tau - 1) and its first emission scores
@@ -405,19 +464,33 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     if (warp == 0) tmem_free(tbase, static_cast<uint32_t>(m.tmem_cols));
 }
 
-const void* chain_fn(int threads, int q) {
-#define SV_CHAIN_CASE(T)                                            \
-    switch (q) {                                                    \
-    case 8: return (const void*)sv_chain_kernel<T, 8>;              \
-    case 4: return (const void*)sv_chain_kernel<T, 4>;              \
-    case 2: return (const void*)sv_chain_kernel<T, 2>;              \
-    case 1: return (const void*)sv_chain_kernel<T, 1>;              \
-    default: return nullptr;                                        \
+// SV_CHAIN_PACKED=0 selects the scalar-add instantiations (A/B runs); packed adds are the default.
+bool chain_packed() {
+    static const bool pk = [] {
+        const char* e = std::getenv("SV_CHAIN_PACKED");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    return pk;
+}
+
+template <int T, int QQ> const void* chain_fn_tq(bool nn, bool pk) {
+    if (nn) return pk ? (const void*)sv_chain_kernel<T, QQ, true, true> : (const void*)sv_chain_kernel<T, QQ, true, false>;
+    return pk ? (const void*)sv_chain_kernel<T, QQ, false, true> : (const void*)sv_chain_kernel<T, QQ, false, false>;
+}
+template <int T> const void* chain_fn_t(int q, bool nn, bool pk) {
+    switch (q) {
+    case 8: return chain_fn_tq<T, 8>(nn, pk);
+    case 4: return chain_fn_tq<T, 4>(nn, pk);
+    case 2: return chain_fn_tq<T, 2>(nn, pk);
+    case 1: return chain_fn_tq<T, 1>(nn, pk);
+    default: return nullptr;
     }
-    if (threads == 512) { SV_CHAIN_CASE(512) }
-    if (threads == 256) { SV_CHAIN_CASE(256) }
-    if (threads == 128) { SV_CHAIN_CASE(128) }
-#undef SV_CHAIN_CASE
+}
+const void* chain_fn(int threads, int q, bool nn) {
+    const bool pk = chain_packed();
+    if (threads == 512) return chain_fn_t<512>(q, nn, pk);
+    if (threads == 256) return chain_fn_t<256>(q, nn, pk);
+    if (threads == 128) return chain_fn_t<128>(q, nn, pk);
     return nullptr;
 }
 
@@ -426,8 +499,8 @@ const void* chain_fn(int threads, int q) {
 // Tensor memory is allocated once per CTA for its lifetime: at most 512 / tmem_cols CTAs may share an
 // SM, otherwise a CTA would spin in tcgen05.alloc until a neighbour exits.  The dynamic shared-memory
 // request is padded so that the hardware never co-schedules more than that.
-int sv_chain_prepare(int threads, int q, size_t* smem_out, int* ctas_per_sm_out) {
-    const void* fn = chain_fn(threads, q);
+int sv_chain_prepare(int threads, int q, bool nonneg, size_t* smem_out, int* ctas_per_sm_out) {
+    const void* fn = chain_fn(threads, q, nonneg);
     if (fn == nullptr) return cudaErrorInvalidValue;
     const int want = threads == 512 ? 1 : threads == 256 ? 2 : 4;
     cudaFuncAttributes fa;
@@ -459,7 +532,7 @@ int sv_chain_prepare(int threads, int q, size_t* smem_out, int* ctas_per_sm_out)
 
 int sv_chain_launch(int threads, int q, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
                     int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st) {
-    const void* fn = chain_fn(threads, q);
+    const void* fn = chain_fn(threads, q, m.nonneg != 0);
     if (fn == nullptr || s.sym_bytes != 1) return cudaErrorInvalidValue;
     void* args[] = {(void*)&m, (void*)&s, (void*)&d_out, (void*)&d_best, (void*)&d_arg, (void*)&d_counter};
     cudaError_t e = cudaLaunchKernel(fn, dim3(grid), dim3(threads), args, smem, st);

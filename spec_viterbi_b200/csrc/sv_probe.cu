@@ -84,6 +84,24 @@ sv_probe_kernel(int iters, float seed, float* sink, unsigned long long* clk) {
                 const float y = u1 + a[k];
                 a[k] = min3(a[k], x, y);
                 b[k] = u1;
+            } else if (MIX == 6) { // 2 FADD2 (packed add.rn.f32x2: two IEEE adds per instruction, sm_100+)
+                unsigned long long pa, pb, pc;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(pa) : "f"(a[k]), "f"(b[k]));
+                asm("mov.b64 %0, {%1, %2};" : "=l"(pc) : "f"(c1), "f"(c2));
+                asm("add.rn.f32x2 %0, %1, %2;" : "=l"(pb) : "l"(pa), "l"(pc));
+                asm("add.rn.f32x2 %0, %1, %2;" : "=l"(pa) : "l"(pb), "l"(pc));
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(a[k]), "=f"(b[k]) : "l"(pa));
+            } else if (MIX == 7) { // 2 FADD2 + 1 FMNMX3: the oracle-order relaxation pair with packed adds
+                unsigned long long pa, pb, pc;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(pa) : "f"(b[k]), "f"(b[k]));
+                asm("mov.b64 %0, {%1, %2};" : "=l"(pc) : "f"(c1), "f"(c2));
+                asm("add.rn.f32x2 %0, %1, %2;" : "=l"(pb) : "l"(pa), "l"(pc));
+                asm("mov.b64 %0, {%1, %2};" : "=l"(pc) : "f"(a[k]), "f"(a[k]));
+                asm("add.rn.f32x2 %0, %1, %2;" : "=l"(pa) : "l"(pb), "l"(pc));
+                float x, y;
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(pa));
+                a[k] = min3(a[k], x, y);
+                b[k] = y;
             } else { // LDS + 2 FADD + FMNMX (the gather-bound inner loop)
                 const float v = sh[(threadIdx.x + k * 32 + it) & (2 * PROBE_THREADS - 1)];
                 const float u = b[k] + c1;
@@ -126,7 +144,7 @@ int run_probe(int grid, int iters, float* d_sink, unsigned long long* d_clk, flo
 
 extern "C" int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_per_s,
                              double* sm_clock_mhz) {
-    if (mix < 0 || mix > 5 || iters < 1 || lane_instr_per_s == nullptr)
+    if (mix < 0 || mix > 7 || iters < 1 || lane_instr_per_s == nullptr)
         return sv_fail(SV_ERR_ARG, "sv_probe_fp32: bad argument");
     SV_CUDA(cudaSetDevice(device));
     int sms = 0;
@@ -138,13 +156,16 @@ extern "C" int sv_probe_fp32(int device, int mix, int iters, double* lane_instr_
     const int grid = sms * 4;
     float ms = 0.f;
     int rc = 0;
-    static const int per_iter[6] = {2, 2, 2, 3, 5, 4}; // instructions per ILP lane per iteration
+    // arithmetic operations per ILP lane per iteration (a packed FADD2 counts as its two adds)
+    static const int per_iter[8] = {2, 2, 2, 3, 5, 4, 4, 5};
     switch (mix) {
     case 0: rc = run_probe<0>(grid, iters, d_sink, d_clk, &ms); break;
     case 1: rc = run_probe<1>(grid, iters, d_sink, d_clk, &ms); break;
     case 2: rc = run_probe<2>(grid, iters, d_sink, d_clk, &ms); break;
     case 3: rc = run_probe<3>(grid, iters, d_sink, d_clk, &ms); break;
     case 4: rc = run_probe<4>(grid, iters, d_sink, d_clk, &ms); break;
+    case 6: rc = run_probe<6>(grid, iters, d_sink, d_clk, &ms); break;
+    case 7: rc = run_probe<7>(grid, iters, d_sink, d_clk, &ms); break;
     default: rc = run_probe<5>(grid, iters, d_sink, d_clk, &ms); break;
     }
     unsigned long long clk[2] = {0, 1};
@@ -344,6 +365,7 @@ sv_probe_smem_kernel(int iters, unsigned long long* clk, float* sink) {
                              : "memory");
         }
     }
+    __syncthreads(); // the CTA's time, not warp 0's: without a barrier the warps drift apart (oldest-first issue)
     const unsigned long long c1 = clock64();
     if (acc0 + acc1 + acc2 + acc3 == 12345.678f) sink[0] = acc0;
     if (tid == 0) clk[blockIdx.x] = c1 - c0;

@@ -8,23 +8,30 @@ from conftest import PROFILE_MODELS, best_state, same_bits
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = ["generic", "es", "ls"]
+KERNELS = ["generic", "es", "ls", "chain", "auto"]
 
 
-def _model(api, hmm, kernel):
+def _model(api, hmm, kernel, must_fit=False):
+    """Model with the kernel forced (K0 plans are lazy: set_kernel builds the plan and fails with
+    SV_ERR_UNSUPPORTED when the model does not fit that kernel -> skip, unless the case says it must)."""
     from spec_viterbi_b200 import _lib
     m = api.Model(hmm)
-    if kernel == "generic":
-        m.set_kernel(_lib.KERNEL_GENERIC)
-    elif kernel == "es":
-        if m.info().es_threads == 0:
-            pytest.skip("model does not fit the edge-stationary kernel")
-        m.set_kernel(_lib.KERNEL_ES)
-    elif kernel == "ls":
-        if m.info().ls_threads == 0:
-            pytest.skip("model does not fit the lockstep kernel")
-        m.set_kernel(_lib.KERNEL_LS)
+    want = {"generic": _lib.KERNEL_GENERIC, "es": _lib.KERNEL_ES, "ls": _lib.KERNEL_LS, "chain": _lib.KERNEL_CHAIN,
+            "auto": _lib.KERNEL_AUTO}[kernel]
+    try:
+        m.set_kernel(want)
+    except _lib.SvError as e:
+        if must_fit or e.code != 5:
+            raise
+        pytest.skip(f"model does not fit the {kernel} kernel")
     return m
+
+
+def _ran(m, kernel):
+    """The kernel that was asked for is the one the last launch used."""
+    from spec_viterbi_b200 import _lib
+    want = {"generic": _lib.KERNEL_GENERIC, "es": _lib.KERNEL_ES, "ls": _lib.KERNEL_LS, "chain": _lib.KERNEL_CHAIN}
+    return kernel == "auto" or m.info().kernel == want[kernel]
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
@@ -43,9 +50,10 @@ def test_semantic_equality_all_models(name, kernel, api, oracle, load_model, loa
     """24 shipped models x the 3 sequences of emit_3_3500_20, one batched call."""
     hmm = load_model(name)
     seqs = load_seqs("emit_3_3500_20")
-    m = _model(api, hmm, kernel)
+    m = _model(api, hmm, kernel, must_fit=True)  # every shipped profile HMM fits all four kernels
     syms, offs = api.pack_sequences(seqs)
     out, best, arg = m.viterbi_batch(syms, offs)
+    assert _ran(m, kernel)
     assert same_bits(out[0], golden[f"{name}_emit3_3500_seq0_plain"])
     for k in range(3):
         exp = oracle.plain(hmm, seqs[k])
@@ -89,26 +97,86 @@ def test_random_models(n, seed, kernel, api, oracle):
         assert (best[k] == bv or (np.isposinf(bv) and np.isposinf(best[k]))) and arg[k] == bi
 
 
-@pytest.mark.parametrize("n,seed", [(150, 7), (2405, 2405)])
-def test_two_halves_lockstep_variant(n, seed, api, oracle, monkeypatch):
-    """Opt-in variant of K2 (sv_plain_ls2.cu): two independent 256-thread halves per CTA, 10 rows per
-    thread; same bits as the oracle, including the refill path (more sequences than slots)."""
-    from spec_viterbi_b200 import generators, _lib
-    monkeypatch.setenv("SV_LS_HALVES", "2")
-    hmm = generators.random_hmm(states_num=n, trans_per_state=3, num_non_zero_start_probs=2, seed=seed)
-    rng = np.random.default_rng(seed)
-    lens = [1, 2, 3, 17, 64, 200, 5, 1, 129] + [int(x) for x in rng.integers(1, 120, 1400)]
+@pytest.mark.parametrize("nseq", [300, 590, 1400])
+def test_lockstep_sequences_per_cta(nseq, api, oracle):
+    """K2 runs 4 sequences per CTA when 8 per CTA would leave SMs idle (batch <= 4 x SMs: the strong-scaling
+    shards of config 5) and 8 otherwise; same bits either way, including the refill path."""
+    from spec_viterbi_b200 import generators
+    hmm = generators.random_hmm(states_num=700, trans_per_state=3, num_non_zero_start_probs=2, seed=3)
+    rng = np.random.default_rng(nseq)
+    lens = [1, 2, 3, 17, 64, 200, 5, 1, 129] + [int(x) for x in rng.integers(1, 120, nseq - 9)]
     seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in lens]
-    m = _model(api, hmm, "ls")
-    info = m.info()
-    assert info.ls_threads == 256 and info.ls_smem_bytes == 164352  # 2 halves x 2 buffers x 2568 x 16 B
+    m = _model(api, hmm, "ls", must_fit=True)
     syms, offs = api.pack_sequences(seqs)
     out, best, arg = m.viterbi_batch(syms, offs)
+    info = m.info()
+    assert _ran(m, "ls") and info.ls_seqs_per_cta == (4 if nseq <= 4 * 148 else 8)
     exp = oracle.plain_batch(hmm, syms, offs, threads=8)
     assert same_bits(out, exp)
     for k in range(0, len(seqs), 37):
         bv, bi = best_state(exp[k])
         assert (best[k] == bv or (np.isposinf(bv) and np.isposinf(best[k]))) and arg[k] == bi
+
+
+@pytest.mark.parametrize("name,nseq", [("100", 5), ("100", 700), ("100", 6000), ("300", 150), ("300", 300), ("1200", 40),
+                                       ("2405", 2), ("2405", 149), ("2405", 600), ("2405", 1300)])
+def test_chain_kernel_batches(name, nseq, api, oracle, load_model):
+    """Chain kernel on profile HMMs at batch sizes that select 1, 2, 4 and 8 sequences per CTA and all three CTA
+    sizes, ragged lengths with length-1 and length-2 sequences, more sequences than resident slots (refill)."""
+    hmm = load_model(name)
+    rng = np.random.default_rng(nseq)
+    lens = ([1, 2, 3, 17, 64, 200, 5, 1, 129] + [int(x) for x in rng.integers(1, 90, max(0, nseq - 9))])[:nseq]
+    seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in lens]
+    m = _model(api, hmm, "chain", must_fit=True)
+    syms, offs = api.pack_sequences(seqs)
+    out, best, arg = m.viterbi_batch(syms, offs)
+    assert _ran(m, "chain") and m.info().chain_seqs_per_cta in (1, 2, 4, 8)
+    exp = oracle.plain_batch(hmm, syms, offs, threads=8)
+    assert same_bits(out, exp)
+    for k in range(0, len(seqs), 7):
+        bv, bi = best_state(exp[k])
+        assert best[k] == bv and arg[k] == bi
+    # vectors only / best only
+    out2, _, _ = m.viterbi_batch(syms, offs, want_best=False)
+    _, best2, arg2 = m.viterbi_batch(syms, offs, want_vectors=False)
+    assert same_bits(out2, exp) and np.array_equal(best2, best) and np.array_equal(arg2, arg)
+
+
+def test_chain_kernel_variants(api, oracle):
+    """Chain structure with shuffled state numbering, a broken chain, +inf band weights, non-uniform hub weights,
+    a second start state in the middle of the chain; and a model with no reachable state (argmin = -1)."""
+    rng = np.random.default_rng(3)
+    L = 1500
+    n = L + 2
+    perm = rng.permutation(n)
+    N, C = 0, L + 1
+    src, dst, w = [N, C], [N, C], [0.3, 0.2]
+    for k in range(1, L + 1):
+        src += [N, k, k]
+        dst += [k, N, C]
+        w += [float(rng.uniform(1, 9)), 1.0, 1.25]
+        if k < L and k % 211 != 0:
+            src += [k]
+            dst += [k + 1]
+            w += [float(rng.uniform(0.1, 3)) if k % 97 else np.inf]
+    src = perm[np.array(src)].astype(np.uint64)
+    dst = perm[np.array(dst)].astype(np.uint64)
+    em = rng.uniform(0.5, 7, (6, n)).astype(np.float32)
+    hmm = api.HMM(n, 6, src.size, src, dst, np.array(w, np.float32), em, 2,
+                  np.array([perm[N], perm[4]], np.uint64), np.array([0.0, 2.0], np.float32))
+    seqs = [rng.integers(0, 6, T).astype(np.uint64) for T in (1, 2, 3, 50, 400, 7, 1, 33, 120, 5, 64, 2)]
+    syms, offs = api.pack_sequences(seqs)
+    m = _model(api, hmm, "chain", must_fit=True)
+    out, best, arg = m.viterbi_batch(syms, offs)
+    exp = oracle.plain_batch(hmm, syms, offs, threads=4)
+    assert _ran(m, "chain") and same_bits(out, exp)
+    for k in range(len(seqs)):
+        bv, bi = best_state(exp[k])
+        assert best[k] == bv and arg[k] == bi
+    dead = api.HMM(n, 6, src.size, src, dst, np.array(w, np.float32), em, 0, np.zeros(0, np.uint64), np.zeros(0, np.float32))
+    md = _model(api, dead, "chain", must_fit=True)
+    out, best, arg = md.viterbi_batch(syms, offs)
+    assert np.all(np.isposinf(out)) and np.all(np.isposinf(best)) and np.all(arg == -1)
 
 
 def test_high_in_degree_and_duplicates(api, oracle):

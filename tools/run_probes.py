@@ -14,7 +14,8 @@ def main():
     pl = _lib.probe_lib()
     v, w = C.c_double(), C.c_double()
     out = {"fp32": {}, "smem": {}}
-    names = ["FADD", "FMNMX", "FMNMX3", "2 FADD + FMNMX3", "4 FADD + FMNMX3 (oracle-order pair)", "LDS.32 + 2 FADD + FMNMX"]
+    names = ["FADD", "FMNMX", "FMNMX3", "2 FADD + FMNMX3", "4 FADD + FMNMX3 (oracle-order pair)", "LDS.32 + 2 FADD + FMNMX",
+             "FADD2 (packed f32x2, 2 adds each)", "2 FADD2 + FMNMX3 (oracle-order pair, packed)"]
     sms = None
     for mix, nm in enumerate(names):
         rc = pl.sv_probe_fp32(0, mix, 20000, C.byref(v), C.byref(w))
