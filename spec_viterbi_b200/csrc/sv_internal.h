@@ -308,6 +308,7 @@ struct sv_model {
     void* d_path_blob = nullptr; // K4i: flattened two-step paths (sv_spec.cu: path_prepare)
     int path_state = 0;          // 0 = not built, 1 = ready, -1 = not eligible
     int path_slots = 0, path_heavy_total = 0;
+    size_t path_rh_offset = 0;   // byte offset of the per-symbol r_h tables inside d_path_blob
     unsigned path_used_mask = 0; // dense rows that some row has a finite edge from (only those are staged)
     int pair_state = 0; // 0 = not built, 1 = ready, -1 = model not eligible (too many heavy rows)
     int kernel_pref = SV_KERNEL_AUTO;

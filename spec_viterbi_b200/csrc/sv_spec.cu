@@ -226,6 +226,10 @@ struct SvPairDev {
     const uint4* hpath = nullptr;     // paths of the dense rows, concatenated
     const uint32_t* hpath_ptr = nullptr; // [heavy + 1]
     int path_slots = 0;
+    // r_h[k] = fl(E[a][dense row h] + T'[h][k]) tabulated per symbol: rh[(a * n_stage + s) * npad + k], +inf padded to
+    // npad (a multiple of 16 floats), so that a CTA stages a row with ONE 1-D bulk copy (TMA) instead of recomputing it
+    const float* rh = nullptr;
+    int npad = 0;
     int n_stage = 0;                 // dense rows that are a SOURCE of some row: only these are staged as r_h
     int stage_h[4] = {0, 0, 0, 0};   // their dense-copy indices
     int stage_row = 0; // light pass: (n + 8) floats of dynamic shared memory hold the row's first dense source
@@ -681,11 +685,12 @@ __device__ __forceinline__ unsigned load_sym(const RunSeqs& s, uint64_t idx) {
 
 // v0[s][i] = fl(E[o_0][i] + start[i])      (GraphBLAS_spec_impl.cpp:54,153-154)
 // grid: x = sequence (up to 2^31-1 of them), y = tile of states
-__global__ void spec_init_kernel(SvGenericDev m, RunSeqs s, float* __restrict__ v) {
+// (rows of v are ld floats apart; columns n .. ld-1 are padding and hold +inf)
+__global__ void spec_init_kernel(SvGenericDev m, RunSeqs s, float* __restrict__ v, int ld) {
     const int q = blockIdx.x;
     const unsigned o = load_sym(s, s.off[q]);
-    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < m.n; i += gridDim.y * blockDim.x)
-        v[static_cast<size_t>(q) * m.n + i] = m.emis[static_cast<size_t>(o) * m.n + i] + m.start[i];
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < ld; i += gridDim.y * blockDim.x)
+        v[static_cast<size_t>(q) * ld + i] = i < m.n ? m.emis[static_cast<size_t>(o) * m.n + i] + m.start[i] : pos_inf();
 }
 
 // K4: one chunk of `level` symbols: vout[s] = H[key(s, chunk)] (x) vin[s]; sequences whose
@@ -693,14 +698,14 @@ __global__ void spec_init_kernel(SvGenericDev m, RunSeqs s, float* __restrict__ 
 __global__ void __launch_bounds__(256)
 handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
                     const float* __restrict__ table, uint64_t table_first,
-                    const float* __restrict__ vin, float* __restrict__ vout, int rows_per_cta, int seq_base) {
+                    const float* __restrict__ vin, float* __restrict__ vout, int ld, int rows_per_cta, int seq_base) {
     extern __shared__ float sv[];
     const int q = seq_base + blockIdx.x;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
     const uint64_t nchunks = (len - 1) / level;
-    const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
-    float* __restrict__ vo = vout + static_cast<size_t>(q) * n;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * ld;
+    float* __restrict__ vo = vout + static_cast<size_t>(q) * ld;
     const int r0 = blockIdx.y * rows_per_cta;
     const int r1 = min(n, r0 + rows_per_cta);
     if (chunk >= nchunks) {
@@ -746,30 +751,59 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     b2 = fminf(b2, (u + (r).z) + (v).z);   \
     b3 = fminf(b3, (u + (r).w) + (v).w);
 
+// Packed IEEE adds (sm_100+: add.rn.f32x2 -> FADD2): two independent round-to-nearest fp32 adds per instruction
+// on a 64-bit register pair; each half is an ordinary IEEE add, so the association and the bits are unchanged.
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t pack2f(float lo, float hi) {
+    f32x2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2f(f32x2_t p, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(p));
+}
+__device__ __forceinline__ f32x2_t add2f(f32x2_t a, f32x2_t b) {
+    f32x2_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// 16 bytes of shared memory as two register pairs (volatile: never hoisted over the barriers that publish v and r_h)
+__device__ __forceinline__ void lds128_pairs(uint32_t addr, f32x2_t& lo, f32x2_t& hi) {
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "r"(addr));
+}
+
 // best[x] = min(best[x], min_k fl(fl(u[x] + r[k]) + v[k])) over all npad columns (npad is a multiple of 16, +inf
 // padded) for R rows at once: a broadcast LDS costs shared-memory wavefronts like any other, so every loaded
-// (r, v) quad is used for R rows.  16 columns per trip = 8 LDS.128 with immediate offsets, 32 R FADD, 8 R FMNMX3.
+// (r, v) quad is used for R rows.  16 columns per trip = 8 LDS.128 with immediate offsets, 16 R FADD2 (two adds each),
+// 8 R FMNMX3: 2 instructions per term where scalar adds need 3.
 template <int R>
 __device__ __forceinline__ void heavy_stream_all(const float (&u)[R], uint32_t r_addr, uint32_t v_addr, int npad,
                                                  float (&best)[R]) {
     float b0[R], b1[R];
+    f32x2_t uu[R];
 #pragma unroll
-    for (int x = 0; x < R; ++x) b0[x] = b1[x] = pos_inf();
+    for (int x = 0; x < R; ++x) {
+        b0[x] = b1[x] = pos_inf();
+        uu[x] = pack2f(u[x], u[x]);
+    }
     const uint32_t r_end = r_addr + static_cast<uint32_t>(npad) * 4u;
 #pragma unroll 1
     for (; r_addr != r_end; r_addr += 64, v_addr += 64) {
-        float4 r[4], v[4];
+        f32x2_t rl[4], rh[4], vl[4], vh[4];
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-            r[g] = lds128(r_addr + 16 * g);
-            v[g] = lds128(v_addr + 16 * g);
+            lds128_pairs(r_addr + 16 * g, rl[g], rh[g]);
+            lds128_pairs(v_addr + 16 * g, vl[g], vh[g]);
         }
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
 #pragma unroll
             for (int x = 0; x < R; ++x) {
-                b0[x] = fminf(fminf(b0[x], (u[x] + r[g].x) + v[g].x), (u[x] + r[g].y) + v[g].y);
-                b1[x] = fminf(fminf(b1[x], (u[x] + r[g].z) + v[g].z), (u[x] + r[g].w) + v[g].w);
+                float t0, t1, t2, t3;
+                unpack2f(add2f(add2f(uu[x], rl[g]), vl[g]), t0, t1); // fl(fl(u + r) + v), columns 4g and 4g+1
+                unpack2f(add2f(add2f(uu[x], rh[g]), vh[g]), t2, t3); // ... 4g+2 and 4g+3
+                b0[x] = fminf(fminf(b0[x], t0), t1);
+                b1[x] = fminf(fminf(b1[x], t2), t3);
             }
         }
     }
@@ -862,55 +896,53 @@ __device__ __forceinline__ float implicit_heavy_row(const SvPairDev& pd, const f
     return best;
 }
 
-// Stages v (when vi != nullptr) and r_h[k] = fl(E[a][hrow[h]] + T'[hrow[h]][k]) of the dense rows, +inf padded.
-// The loads of four strides of all arrays are issued before the first store: a loop that stores after each
-// load serialises ~60 L2 round trips per thread (it was most of the kernel: 29 us per launch in ncu).
-__device__ __forceinline__ void implicit_stage(const SvPairDev& pd, const float* __restrict__ ea,
-                                               const float* __restrict__ vi, float* __restrict__ sv,
-                                               float* __restrict__ sr, int npad, int tid, int nthr) {
-    const int n = pd.n;
-    float e[kImplicitMaxHeavy];
-#pragma unroll
-    for (int h = 0; h < kImplicitMaxHeavy; ++h) e[h] = h < pd.n_stage ? ea[pd.hrow[pd.stage_h[h]]] : 0.0f;
-    for (int k0 = tid; k0 < npad; k0 += 4 * nthr) {
-        float x[4][1 + kImplicitMaxHeavy];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int k = k0 + u * nthr;
-            const bool ok = k < n;
-            x[u][0] = (vi != nullptr && ok) ? vi[k] : pos_inf();
-#pragma unroll
-            for (int h = 0; h < kImplicitMaxHeavy; ++h)
-                x[u][1 + h] = (h < pd.n_stage && ok) ? pd.wd[static_cast<size_t>(pd.stage_h[h]) * n + k] : pos_inf();
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int k = k0 + u * nthr;
-            if (k >= npad) continue;
-            if (vi != nullptr) sv[k] = x[u][0];
-#pragma unroll
-            for (int h = 0; h < kImplicitMaxHeavy; ++h)
-                if (h < pd.n_stage) sr[h * npad + k] = e[h] + x[u][1 + h];
-        }
-    }
+// ---- TMA staging (1-D bulk copies global -> shared, completion on an mbarrier) ----
+// The per-CTA inputs of a chunk -- the sequence's score vector (rows of npad floats in global memory, +inf padded)
+// and the r_h rows of the chunk's first symbol (tabulated once per model, SvPairDev::rh) -- arrive as bulk copies
+// issued by one thread instead of being loaded, recomputed and stored by all of them.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
-
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "SV_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra SV_MBAR_DONE;\n"
+        "bra SV_MBAR_WAIT;\n"
+        "SV_MBAR_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D bulk copy global -> shared (TMA), bytes a multiple of 16, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 // per-chunk launch: grid x = sequence, y = row tile (then one CTA per heavy row)
 template <int R>
 __global__ void __launch_bounds__(kImplicitThreads)
 implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* __restrict__ vin,
-                          float* __restrict__ vout, int seq_base, int ntiles, int npad) {
+                          float* __restrict__ vout, int seq_base, int ntiles) {
     extern __shared__ float4 sm4[];
+    const int n = pd.n, npad = pd.npad; // rows of vin / vout are npad floats apart, columns n.. hold +inf
     float* sv = reinterpret_cast<float*>(sm4);  // [npad] v, +inf padded
-    float* sr = sv + npad;                      // [n_heavy][npad] r_h
+    float* sr = sv + npad;                      // [n_stage][npad] r_h
     __shared__ float s_red[kImplicitThreads / 32 /*max*/];
-    const int n = pd.n;
+    __shared__ __align__(8) uint64_t s_bar;
     const int nthr = blockDim.x; // 64 or 128
     const int q = seq_base + blockIdx.x;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
-    const float* __restrict__ vi = vin + static_cast<size_t>(q) * n;
-    float* __restrict__ vo = vout + static_cast<size_t>(q) * n;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * npad;
+    float* __restrict__ vo = vout + static_cast<size_t>(q) * npad;
     const bool heavy_cta = static_cast<int>(blockIdx.y) >= ntiles;
     const int hme = static_cast<int>(blockIdx.y) - ntiles;
     if (chunk >= (len - 1) / 2) {
@@ -920,7 +952,7 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
 #pragma unroll
             for (int x = 0; x < R; ++x) {
                 const int i = (blockIdx.y * R + x) * nthr + threadIdx.x;
-                if (i < n && pd.hidx[i] < 0) vo[i] = vi[i];
+                if (i < npad && (i >= n || pd.hidx[i] < 0)) vo[i] = vi[i]; // padding included
             }
         }
         return;
@@ -928,8 +960,17 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
     const unsigned a = load_sym(s, o0 + 1 + chunk * 2), b = load_sym(s, o0 + 2 + chunk * 2);
     const float* __restrict__ ea = pd.emis + static_cast<size_t>(a) * n;
     const float* __restrict__ eb = pd.emis + static_cast<size_t>(b) * n;
-    implicit_stage(pd, ea, vi, sv, sr, npad, threadIdx.x, nthr);
-    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        const unsigned row_bytes = static_cast<unsigned>(npad) * 4u;
+        mbar_expect_tx(&s_bar, row_bytes * static_cast<unsigned>(1 + pd.n_stage));
+        bulk_g2s(sv, vi, row_bytes, &s_bar);
+        for (int h = 0; h < pd.n_stage; ++h)
+            bulk_g2s(sr + h * npad, pd.rh + (static_cast<size_t>(a) * pd.n_stage + h) * npad, row_bytes, &s_bar);
+    }
+    __syncthreads(); // the initialised barrier is visible to every waiter
+    mbar_wait(&s_bar, 0);
     if (!heavy_cta) {
         const int i0 = blockIdx.y * R * nthr + threadIdx.x;
         unsigned live = 0;
@@ -941,8 +982,11 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
         float best[R];
         implicit_light_rows<R>(pd, ea, eb, i0, nthr, live, sv, sr, npad, best);
 #pragma unroll
-        for (int x = 0; x < R; ++x)
-            if ((live >> x) & 1u) vo[i0 + x * nthr] = best[x];
+        for (int x = 0; x < R; ++x) {
+            const int i = i0 + x * nthr;
+            if ((live >> x) & 1u) vo[i] = best[x];
+            else if (i >= n && i < npad) vo[i] = pos_inf(); // the padding the next chunk's bulk copy fetches
+        }
         return;
     }
     float best = warp_min(implicit_heavy_row(pd, ea, eb, hme, sv, sr, npad, threadIdx.x, nthr));
@@ -960,15 +1004,15 @@ implicit_pair_step_kernel(SvPairDev pd, RunSeqs s, uint64_t chunk, const float* 
 // (GraphBLAS_spec_impl.cpp:84-89); others copy.  One CTA per sequence.
 __global__ void __launch_bounds__(1024)
 tail_step_kernel(SvGenericDev m, int level, RunSeqs s, int tail, const float* __restrict__ vin,
-                 float* __restrict__ vout) {
+                 float* __restrict__ vout, int ld) {
     extern __shared__ float sv[];
     const int q = blockIdx.x;
     const uint64_t o0 = s.off[q];
     const uint64_t len = s.off[q + 1] - o0;
     const uint64_t nchunks = (len - 1) / level;
     const uint64_t ntail = (len - 1) % level;
-    const float* __restrict__ vi = vin + static_cast<size_t>(q) * m.n;
-    float* __restrict__ vo = vout + static_cast<size_t>(q) * m.n;
+    const float* __restrict__ vi = vin + static_cast<size_t>(q) * ld;
+    float* __restrict__ vo = vout + static_cast<size_t>(q) * ld;
     if (static_cast<uint64_t>(tail) >= ntail) {
         for (int i = threadIdx.x; i < m.n; i += blockDim.x) vo[i] = vi[i];
         return;
@@ -993,12 +1037,12 @@ tail_step_kernel(SvGenericDev m, int level, RunSeqs s, int tail, const float* __
 
 // (min, lowest argmin) of each final vector; optional copy-out is done by the caller.
 __global__ void __launch_bounds__(256)
-best_state_kernel(int n, const float* __restrict__ v, float* __restrict__ best,
+best_state_kernel(int n, int ld, const float* __restrict__ v, float* __restrict__ best,
                   int32_t* __restrict__ arg) {
     __shared__ float s_bv[8];
     __shared__ int s_bi[8];
     const int q = blockIdx.x;
-    const float* __restrict__ x = v + static_cast<size_t>(q) * n;
+    const float* __restrict__ x = v + static_cast<size_t>(q) * ld;
     float bv = pos_inf();
     int bi = 0x7fffffff;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -1266,13 +1310,29 @@ bool path_prepare(sv_model* m, SvPairDev* pd) {
                 }
             }
         }
+        // r_h tables of the staged dense rows (those that are a source of some row), one per symbol
+        const size_t npad = (n + 15) / 16 * 16;
+        std::vector<uint32_t> stage;
+        for (size_t h = 0; h < hrow.size(); ++h)
+            if ((used >> h) & 1u) stage.push_back(static_cast<uint32_t>(h));
+        std::vector<float> rh(std::max<size_t>(m->emits * stage.size() * npad, 1), std::numeric_limits<float>::infinity());
+        for (size_t a = 0; a < m->emits; ++a)
+            for (size_t sidx = 0; sidx < stage.size(); ++sidx) {
+                const uint32_t row = hrow[stage[sidx]];
+                const float e = m->emis[a * n + row];
+                float* dst = &rh[(a * stage.size() + sidx) * npad];
+                for (uint32_t p2 = rp[row]; p2 < rp[row + 1]; ++p2) dst[cl[p2]] = e + cw[p2]; // fl(E + T'), as the kernels form it
+            }
         const size_t o_lp = 0;
         const size_t o_hp = align(o_lp + lpath.size() * 16);
         const size_t o_lc = align(o_hp + hpath.size() * 16);
         const size_t o_wc = align(o_lc + n * 4);
         const size_t o_ptr = align(o_wc + wcol.size() * 4);
-        const size_t bytes = o_ptr + (nh + 1) * 4 + 256;
+        const size_t o_rh = align(o_ptr + (nh + 1) * 4);
+        const size_t bytes = o_rh + rh.size() * 4 + 256;
+        m->path_rh_offset = o_rh;
         std::vector<unsigned char> host(bytes, 0);
+        std::memcpy(host.data() + o_rh, rh.data(), rh.size() * 4);
         std::memcpy(host.data() + o_lp, lpath.data(), lpath.size() * 16);
         std::memcpy(host.data() + o_hp, hpath.data(), hpath.size() * 16);
         std::memcpy(host.data() + o_lc, lcount.data(), n * 4);
@@ -1304,6 +1364,8 @@ bool path_prepare(sv_model* m, SvPairDev* pd) {
     pd->lcount = reinterpret_cast<const uint32_t*>(base + o_lc);
     pd->wcol = reinterpret_cast<const float*>(base + o_wc);
     pd->hpath_ptr = reinterpret_cast<const uint32_t*>(base + o_ptr);
+    pd->rh = reinterpret_cast<const float*>(base + m->path_rh_offset);
+    pd->npad = static_cast<int>((n + 15) / 16 * 16);
     pd->path_slots = m->path_slots;
     pd->n_stage = 0;
     for (int h = 0; h < pd->n_heavy; ++h)
@@ -1738,12 +1800,15 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     if (s->ev_done == nullptr) SV_CUDA(cudaEventCreateWithFlags(&s->ev_done, cudaEventDisableTiming));
     else SV_CUDA(cudaStreamWaitEvent(st, s->ev_done, 0));
     const size_t n = m->n;
+    // row stride of the state vectors: the implicit run fetches rows with bulk copies (64-byte rows, +inf padded)
+    const size_t npad_rows = (n + 15) / 16 * 16;
+    const size_t ld = npad_rows;
     const uint64_t nseq = seqs->nseq;
     if (s->v_capacity < nseq) {
         for (int b = 0; b < 2; ++b) {
             if (s->d_v[b]) cudaFree(s->d_v[b]);
             s->d_v[b] = nullptr;
-            SV_CUDA(cudaMalloc(&s->d_v[b], nseq * n * sizeof(float)));
+            SV_CUDA(cudaMalloc(&s->d_v[b], nseq * npad_rows * sizeof(float)));
         }
         s->v_capacity = nseq;
     }
@@ -1751,8 +1816,8 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     int launches = 0;
     int cur = 0;
     {
-        dim3 grid(static_cast<unsigned>(nseq), static_cast<unsigned>(std::min<size_t>((n + 255) / 256, 65535)));
-        spec_init_kernel<<<grid, 256, 0, st>>>(m->gen, rs, s->d_v[cur]);
+        dim3 grid(static_cast<unsigned>(nseq), static_cast<unsigned>(std::min<size_t>((ld + 255) / 256, 65535)));
+        spec_init_kernel<<<grid, 256, 0, st>>>(m->gen, rs, s->d_v[cur], static_cast<int>(ld));
         SV_CUDA(cudaGetLastError()); // a failed first launch must not let the chunk kernels run on garbage
         ++launches;
     }
@@ -1794,18 +1859,17 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
                 static const int threads = implicit_threads();
                 const int per_cta = threads * rows;
                 const int ntiles = static_cast<int>((n + per_cta - 1) / per_cta);
-                const int npad = static_cast<int>((n + 15) / 16 * 16);
                 dim3 igrid(static_cast<unsigned>(q1 - q0), static_cast<unsigned>(ntiles + pd.n_heavy));
                 auto kern = rows == 1 ? implicit_pair_step_kernel<1> : rows == 2 ? implicit_pair_step_kernel<2> : implicit_pair_step_kernel<4>;
                 kern<<<igrid, threads, implicit_smem(pd), g == 0 ? st : s->aux[g - 1]>>>(
-                    pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles, npad);
+                    pd, rs, c, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(q0), ntiles);
                 ++launches;
                 continue;
             }
             dim3 grid(static_cast<unsigned>(q1 - q0), static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta));
             handler_gemv_kernel<<<grid, 256, n * sizeof(float), g == 0 ? st : s->aux[g - 1]>>>(
                 static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c,
-                s->d_table, s->table_first, s->d_v[cur], s->d_v[cur ^ 1], rows_per_cta, static_cast<int>(q0));
+                s->d_table, s->table_first, s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(ld), rows_per_cta, static_cast<int>(q0));
             ++launches;
         }
         cur ^= 1;
@@ -1818,14 +1882,15 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     }
     for (uint64_t tl = 0; tl + 1 < s->level; ++tl) {
         tail_step_kernel<<<static_cast<unsigned>(nseq), 1024, n * sizeof(float), st>>>(
-            m->gen, static_cast<int>(s->level), rs, static_cast<int>(tl), s->d_v[cur], s->d_v[cur ^ 1]);
+            m->gen, static_cast<int>(s->level), rs, static_cast<int>(tl), s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(ld));
         cur ^= 1;
         ++launches;
     }
     if (d_out != nullptr)
-        SV_CUDA(cudaMemcpyAsync(d_out, s->d_v[cur], nseq * n * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        SV_CUDA(cudaMemcpy2DAsync(d_out, n * sizeof(float), s->d_v[cur], ld * sizeof(float), n * sizeof(float), nseq,
+                                  cudaMemcpyDeviceToDevice, st));
     if (d_best != nullptr || d_best_state != nullptr) {
-        best_state_kernel<<<static_cast<unsigned>(nseq), 256, 0, st>>>(static_cast<int>(n), s->d_v[cur],
+        best_state_kernel<<<static_cast<unsigned>(nseq), 256, 0, st>>>(static_cast<int>(n), static_cast<int>(ld), s->d_v[cur],
                                                                       d_best, d_best_state);
         ++launches;
     }

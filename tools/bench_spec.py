@@ -13,12 +13,15 @@ from spec_viterbi_b200 import api, _lib  # noqa: E402
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "2405"
     hmm = api.read_HMM(str(ROOT / "tests/golden/models" / f"{name}.chmmb"))
-    seqs = api.read_emit_seq(str(ROOT / "tests/golden/seqs/emit_50_3500_20.essb"))
+    seqfile = sys.argv[3] if len(sys.argv) > 3 else "emit_50_3500_20"
+    seqs = api.read_emit_seq(str(ROOT / "tests/golden/seqs" / f"{seqfile}.essb"))
+    if len(sys.argv) > 4:  # replicate the set to get larger batches
+        seqs = seqs * int(sys.argv[4])
     syms, offs = api.pack_sequences(seqs)
     n, E = hmm.states_num, hmm.emit_num
     m = api.Model(hmm)
     nnz = int(m.info().nnz)
-    res = {"model": name, "states": n, "nnz": nnz, "handlers": E * E, "table_GB": E * E * n * n * 4 / 1e9}
+    res = {"model": name, "sequences": len(seqs), "seqfile": seqfile, "states": n, "nnz": nnz, "handlers": E * E, "table_GB": E * E * n * n * 4 / 1e9}
     peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {"hbm_gbs": 6650.0}
     quick = len(sys.argv) > 2 and sys.argv[2] == "quick"  # only the K3' build and the run legs
     for label, method in (("sparse_lhs", _lib.SPEC_SPARSE_LHS), ("pair_rows", _lib.SPEC_PAIR_ROWS),
@@ -44,11 +47,15 @@ def main():
         if label == "dense_gemm":
             npad = (n + 127) // 128 * 128
             res["dense_gemm_mac_per_s"] = E * E * float(npad) ** 3 / (min(tk) * 1e-3)
-            res["dense_gemm_frac_of_fp32_mac_peak"] = res["dense_gemm_mac_per_s"] / (148 * 128 * 1.965e9 / 1.5)
+            import torch
+            prop = torch.cuda.get_device_properties(0)
+            res["dense_gemm_frac_of_fp32_mac_peak"] = res["dense_gemm_mac_per_s"] / (
+                prop.multi_processor_count * 128 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1.5)
         else:
             res[f"{label}_write_GBs"] = res["table_GB"] / (min(tk) * 1e-3)
             res[f"{label}_frac_of_hbm"] = res[f"{label}_write_GBs"] / peaks["hbm_gbs"]
         if label == "sparse_lhs":
+            sp.set_run_mode(_lib.SPEC_RUN_TABLE)
             rt = []
             for _ in range(3):
                 t0 = time.perf_counter()
@@ -60,16 +67,13 @@ def main():
             res["run_frac_of_hbm"] = res["run_handler_read_GBs"] / peaks["hbm_gbs"]
             res["run_state_updates_per_s"] = sum(len(s) for s in seqs) * n / (min(rt) * 1e-3)
             # K4i: the same chunks recomputed from the sparse factors (no table reads), bit-identical
-            for key, mode in (("run_ms_level2_implicit_cluster", _lib.SPEC_RUN_IMPLICIT_CLUSTER),
-                              ("run_ms_level2_implicit", _lib.SPEC_RUN_IMPLICIT)):
-                sp.set_run_mode(mode)
-                it = []
-                for _ in range(3):
-                    t0 = time.perf_counter()
-                    iout, ibest, iarg = sp.run_batch(syms, offs)
-                    it.append((time.perf_counter() - t0) * 1e3)
-                res[key] = min(it)
-                res[key.replace("run_ms", "bits_equal")] = bool(np.array_equal(iout.view(np.uint32), out.view(np.uint32)))
+            sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+            it = []
+            for _ in range(4):
+                t0 = time.perf_counter()
+                iout, ibest, iarg = sp.run_batch(syms, offs)
+                it.append((time.perf_counter() - t0) * 1e3)
+            res["run_ms_level2_implicit"] = min(it)
             sp.set_run_mode(_lib.SPEC_RUN_TABLE)
             it = [res["run_ms_level2_implicit"]]
             res["implicit_bits_equal_table_run"] = bool(np.array_equal(iout.view(np.uint32), out.view(np.uint32)))
@@ -79,7 +83,10 @@ def main():
             paths = int(indeg[np.asarray(hmm.trans_rows, np.int64)].sum())        # sum over edges (j->i) of indeg(j)
             res["implicit_terms_per_chunk"] = paths
             res["implicit_terms_per_s"] = paths * chunks / (min(it) * 1e-3)
-            res["implicit_frac_of_fp32_issue"] = res["implicit_terms_per_s"] * 2.5 / (148 * 128 * 1.965e9)
+            import torch
+            prop = torch.cuda.get_device_properties(0)
+            res["implicit_frac_of_fp32_issue"] = res["implicit_terms_per_s"] * 2.5 / (
+                prop.multi_processor_count * 128 * peaks.get("sm_max_mhz", 1965.0) * 1e6)
             # plain path on the same input for the honest comparison
             pt = []
             for _ in range(3):
