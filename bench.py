@@ -248,7 +248,7 @@ def run_probes(device_index):
         return {"error": str(e)}
     out = {}
     v, w = C.c_double(), C.c_double()
-    names = {0: "lds128_gather", 1: "lds128_3to1_sts128", 2: "ls_inner_loop", 3: "lds32"}
+    names = {1: "lds128_3to1_sts128", 2: "ls_inner_loop"}
     for mode, nm in names.items():
         if pl.sv_probe_smem(device_index, mode, 6000, C.byref(v), C.byref(w)) == 0:
             out[nm] = {"bytes_per_clk_per_sm": v.value, "lane_loads_per_clk_per_sm": w.value}

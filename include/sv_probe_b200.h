@@ -28,8 +28,9 @@ int sv_probe_tmem(int device, int iters, unsigned* errors, double* bytes_per_clk
 
 /* Shared-memory pipe probe under the lockstep kernel's access pattern (16 warps per SM, 8 loads in flight
  * per thread, per-lane register addresses that are bank-conflict free by construction).
- * mode: 0 = LDS.128 gathers, 1 = 3 LDS.128 : 1 STS.128, 2 = mode 1 + the relaxations (whole inner loop),
- *       3 = LDS.32.  Returns bytes (and lane loads) per clock and SM of the slowest SM. */
+ * mode: 1 = 3 LDS.128 : 1 STS.128 (the kernel's ratio), 2 = mode 1 + the relaxations (the whole inner loop).
+ * Returns bytes (and lane loads) per clock and SM of the slowest SM.  Both modes were checked against ncu's
+ * shared-memory wavefront counters (profiles/r02_smem_probe_ncu.csv). */
 int sv_probe_smem(int device, int mode, int iters, double* bytes_per_clk_per_sm, double* loads_per_clk_per_sm);
 
 #ifdef __cplusplus

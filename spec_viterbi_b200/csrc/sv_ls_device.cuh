@@ -72,14 +72,46 @@ struct LsMgr {
 // fl(fl(E + T') + v) -- the two adds are never re-associated (GraphBLAS_impl.cpp:65,69)
 __device__ __forceinline__ float relax1(float e, float w, float v) { return (e + w) + v; }
 
+// Packed IEEE adds (sm_100+: add.rn.f32x2 -> FADD2): two independent round-to-nearest fp32 adds in ONE instruction
+// on a 64-bit register pair.  Each half is an ordinary IEEE add -- fl(fl(E + T') + v) stays exactly the oracle's
+// (GraphBLAS_impl.cpp:65,69) -- but a slot pair of 4 sequences issues 8 FADD2 instead of 16 FADD.
+#ifndef SV_LS_PACKED
+#define SV_LS_PACKED 1
+#endif
+typedef unsigned long long ls_f32x2;
+__device__ __forceinline__ ls_f32x2 ls_pack2(float lo, float hi) {
+    ls_f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void ls_unpack2(ls_f32x2 p, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(p));
+}
+__device__ __forceinline__ ls_f32x2 ls_add2(ls_f32x2 a, ls_f32x2 b) {
+    ls_f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 // One pair of slots for 4 sequences: acc = min(acc, x0, x1) is a single 3-input FMNMX3.
 template <bool FIRST>
 __device__ __forceinline__ void pair4(float w0, float w1, const float4 a, const float4 b, const float* e,
                                       float* acc) {
+#if SV_LS_PACKED
+    const ls_f32x2 e01 = ls_pack2(e[0], e[1]), e23 = ls_pack2(e[2], e[3]);
+    const ls_f32x2 ww0 = ls_pack2(w0, w0), ww1 = ls_pack2(w1, w1);
+    float p0, p1, p2, p3, q0, q1, q2, q3;
+    ls_unpack2(ls_add2(ls_add2(e01, ww0), ls_pack2(a.x, a.y)), p0, p1);
+    ls_unpack2(ls_add2(ls_add2(e23, ww0), ls_pack2(a.z, a.w)), p2, p3);
+    ls_unpack2(ls_add2(ls_add2(e01, ww1), ls_pack2(b.x, b.y)), q0, q1);
+    ls_unpack2(ls_add2(ls_add2(e23, ww1), ls_pack2(b.z, b.w)), q2, q3);
+    const float x0 = fminf(p0, q0), x1 = fminf(p1, q1), x2 = fminf(p2, q2), x3 = fminf(p3, q3);
+#else
     const float x0 = fminf(relax1(e[0], w0, a.x), relax1(e[0], w1, b.x));
     const float x1 = fminf(relax1(e[1], w0, a.y), relax1(e[1], w1, b.y));
     const float x2 = fminf(relax1(e[2], w0, a.z), relax1(e[2], w1, b.z));
     const float x3 = fminf(relax1(e[3], w0, a.w), relax1(e[3], w1, b.w));
+#endif
     if (FIRST) {
         acc[0] = x0; acc[1] = x1; acc[2] = x2; acc[3] = x3;
     } else {
@@ -89,8 +121,15 @@ __device__ __forceinline__ void pair4(float w0, float w1, const float4 a, const 
 }
 template <bool FIRST>
 __device__ __forceinline__ void single4(float w0, const float4 a, const float* e, float* acc) {
+#if SV_LS_PACKED
+    const ls_f32x2 ww0 = ls_pack2(w0, w0);
+    float x0, x1, x2, x3;
+    ls_unpack2(ls_add2(ls_add2(ls_pack2(e[0], e[1]), ww0), ls_pack2(a.x, a.y)), x0, x1);
+    ls_unpack2(ls_add2(ls_add2(ls_pack2(e[2], e[3]), ww0), ls_pack2(a.z, a.w)), x2, x3);
+#else
     const float x0 = relax1(e[0], w0, a.x), x1 = relax1(e[1], w0, a.y);
     const float x2 = relax1(e[2], w0, a.z), x3 = relax1(e[3], w0, a.w);
+#endif
     if (FIRST) {
         acc[0] = x0; acc[1] = x1; acc[2] = x2; acc[3] = x3;
     } else {

@@ -29,8 +29,8 @@ def main():
     err = C.c_uint()
     pl.sv_probe_tmem(0, 20000, C.byref(err), C.byref(v))
     out["tmem"] = {"errors": err.value, "bytes_per_clk_per_sm": v.value}
-    for mode, nm in enumerate(["LDS.128 conflict-free gather", "3 LDS.128 : 1 STS.128 (lockstep kernel's ratio)",
-                               "the lockstep inner loop (gathers + stores + 8 FADD + 2 FMNMX3 per load)", "LDS.32 conflict-free"]):
+    for mode, nm in ((1, "3 LDS.128 : 1 STS.128 (lockstep kernel's ratio)"),
+                     (2, "the lockstep inner loop (gathers + stores + 8 FADD + 2 FMNMX3 per load)")):
         rc = pl.sv_probe_smem(0, mode, 30000, C.byref(v), C.byref(w))
         if rc != 0:
             raise SystemExit(pl.sv_probe_last_error().decode())
