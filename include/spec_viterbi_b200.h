@@ -185,8 +185,14 @@ enum {
     SV_SPEC_AUTO = 0,
     SV_SPEC_DENSE_GEMM = 1, /* K3: register-blocked dense (min,+) GEMM, 2*N^3 ops / handler */
     SV_SPEC_SPARSE_LHS = 2, /* K3': sparse level-1 matrix times dense handler, 2*nnz*N ops */
-    SV_SPEC_PAIR_ROWS = 3   /* K3'': level 2 only, sparse x sparse rows streamed into the dense table;
+    SV_SPEC_PAIR_ROWS = 3,  /* K3'': level 2 only, sparse x sparse rows streamed into the dense table;
                                AUTO picks it for level 2 when the model has few dense rows */
+    SV_SPEC_ONDEMAND = 4    /* level >= 3: precompute only the level-(L-1) table; every chunk of a run builds the
+                               level-L handlers of the tuples the batch actually observes (K3' into a scratch, one per
+                               sequence) and applies them (K4) -- same sums, same association, same bits as the full
+                               table.  Level 3 of a 2405-state model needs 9.3 GB instead of 185 GB.  AUTO picks it
+                               when the full level-L table would not fit the device (tuple range must be the whole
+                               range or empty) */
 };
 
 /* spec_with(hmm): level-1 tables, and for level > 1 the dense handler of every symbol

@@ -35,6 +35,11 @@ struct sv_spec {
     int method = SV_SPEC_SPARSE_LHS;
     int run_mode = SV_SPEC_RUN_AUTO;  // AUTO: K4i (level-2 chunks recomputed from the sparse factors) when eligible, else K4
     cudaEvent_t ev_done = nullptr;    // end of the last run on this spec: runs share d_v and serialise on it
+    // on-demand mode (level >= 3): the complete level-(L-1) table and a scratch of per-sequence level-L handlers
+    bool ondemand = false;
+    float* d_prev = nullptr;       // [emits^(L-1)][n][n]
+    float* d_scratch = nullptr;    // [scratch_cap][n][n]
+    size_t scratch_cap = 0;        // handlers
     // run-phase scratch
     float* d_v[2] = {nullptr, nullptr};
     uint64_t v_capacity = 0;
@@ -95,6 +100,51 @@ sparse_lhs_kernel(SvGenericDev m, const float* __restrict__ prev, uint64_t prev_
     const uint64_t prefix = tuple / emits;
     const float* __restrict__ P = prev + (prefix - prev_first) * static_cast<size_t>(n) * n;
     float* __restrict__ O = out + static_cast<size_t>(blockIdx.z) * n * n + static_cast<size_t>(i) * n;
+    const float e = m.emis[static_cast<size_t>(symb) * n + i];
+    const uint32_t p0 = m.rowptr[i], p1 = m.rowptr[i + 1];
+    for (int k0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4; k0 < n; k0 += gridDim.x * blockDim.x * 4) {
+        float acc[4] = {pos_inf(), pos_inf(), pos_inf(), pos_inf()};
+        for (uint32_t p = p0; p < p1; ++p) {
+            const float a = e + m.w[p]; // level-1 value M_sym[i][j]
+            const float* __restrict__ prow = P + static_cast<size_t>(m.col[p]) * n + k0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (k0 + c < n) acc[c] = fminf(acc[c], a + prow[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (k0 + c < n) O[k0 + c] = acc[c];
+    }
+}
+
+// The same product for ONE tuple per sequence -- the tuple sequence q observes in chunk `chunk` -- into a scratch
+// handler per sequence (on-demand mode of levels >= 3: "recompute on demand per observed tuple").
+// prev = the COMPLETE level-(L-1) table.  grid: x = column tile, y = row i, z = sequence (relative to seq_base).
+struct OnDemandSeqs {
+    int nseq;
+    const void* sym;
+    int sym_bytes;
+    const uint64_t* off;
+};
+__global__ void __launch_bounds__(256)
+ondemand_handler_kernel(SvGenericDev m, const float* __restrict__ prev, float* __restrict__ scratch, OnDemandSeqs s,
+                        uint64_t chunk, int level, int emits, int seq_base) {
+    const int n = m.n;
+    const int i = blockIdx.y;
+    const int q = seq_base + blockIdx.z;
+    const uint64_t o0 = s.off[q];
+    const uint64_t len = s.off[q + 1] - o0;
+    if (chunk >= (len - 1) / level) return; // no chunk left: K4 copies the vector through
+    uint64_t prefix = 0;
+    unsigned symb = 0;
+    for (int j = 0; j < level; ++j) {
+        const uint64_t idx = o0 + 1 + chunk * level + j;
+        const unsigned o = s.sym_bytes == 1 ? static_cast<const uint8_t*>(s.sym)[idx] : static_cast<const uint16_t*>(s.sym)[idx];
+        if (j + 1 < level) prefix = prefix * emits + o;
+        else symb = o; // the last consumed symbol is the left (sparse) factor: H(k1..kL) = M_kL (x) H(k1..k(L-1))
+    }
+    const float* __restrict__ P = prev + prefix * static_cast<size_t>(n) * n;
+    float* __restrict__ O = scratch + static_cast<size_t>(blockIdx.z) * n * n + static_cast<size_t>(i) * n;
     const float e = m.emis[static_cast<size_t>(symb) * n + i];
     const uint32_t p0 = m.rowptr[i], p1 = m.rowptr[i + 1];
     for (int k0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4; k0 < n; k0 += gridDim.x * blockDim.x * 4) {
@@ -715,7 +765,9 @@ handler_gemv_kernel(int n, int emits, int level, RunSeqs s, uint64_t chunk,
     for (int k = threadIdx.x; k < n; k += blockDim.x) sv[k] = vi[k];
     uint64_t tuple = 0;
     for (int j = 0; j < level; ++j) tuple = tuple * emits + load_sym(s, o0 + 1 + chunk * level + j);
-    const float* __restrict__ H = table + (tuple - table_first) * static_cast<size_t>(n) * n;
+    // table_first == ~0: on-demand mode, `table` holds one handler per sequence of this launch
+    const float* __restrict__ H = table_first == ~0ull ? table + static_cast<size_t>(blockIdx.x) * n * n
+                                                       : table + (tuple - table_first) * static_cast<size_t>(n) * n;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int i = r0 + warp; i < r1; i += nw) {
@@ -1449,8 +1501,24 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
         return sv_fail(SV_ERR_UNSUPPORTED, "dense (min,+) GEMM precompute is implemented for level 2");
     SV_CUDA(cudaSetDevice(m->device));
     SvPairDev pairdev;
+    const size_t mat_elems = static_cast<size_t>(m->n) * m->n;
+    if (method == SV_SPEC_AUTO && level >= 3 && d_table == nullptr && tuple_begin == 0 && tuple_end == ntuples) {
+        // the whole level-L table is asked for: on-demand when it cannot fit beside the level-(L-1) table
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+            const double need = static_cast<double>(ntuples) * mat_elems * sizeof(float) * (1.0 + 1.0 / m->emits);
+            if (need > 0.9 * static_cast<double>(free_b)) method = SV_SPEC_ONDEMAND;
+        }
+    }
+    if (method == SV_SPEC_ONDEMAND) {
+        if (level < 3) {
+            method = SV_SPEC_AUTO; // levels 1 and 2 have nothing to defer (level 2 runs implicitly, K4i)
+        } else if (d_table != nullptr || !((tuple_begin == 0 && tuple_end == ntuples) || tuple_begin == tuple_end)) {
+            return sv_fail(SV_ERR_ARG, "sv_spec_create: the on-demand mode has no level-L table (no tuple shards, no caller table)");
+        }
+    }
     if (method == SV_SPEC_AUTO) method = (level == 2 && pair_prepare(m, &pairdev)) ? SV_SPEC_PAIR_ROWS : SV_SPEC_SPARSE_LHS;
-    if (method != SV_SPEC_SPARSE_LHS && method != SV_SPEC_DENSE_GEMM && method != SV_SPEC_PAIR_ROWS)
+    if (method != SV_SPEC_SPARSE_LHS && method != SV_SPEC_DENSE_GEMM && method != SV_SPEC_PAIR_ROWS && method != SV_SPEC_ONDEMAND)
         return sv_fail(SV_ERR_ARG, "sv_spec_create: unknown method");
     if (method == SV_SPEC_PAIR_ROWS && (level != 2 || !pair_prepare(m, &pairdev)))
         return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_create: the pair-rows kernel builds level 2 of models with few dense rows");
@@ -1461,6 +1529,26 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
     s->ntuples = ntuples;
     s->method = method;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (method == SV_SPEC_ONDEMAND) {
+        // the complete level-(L-1) table; level-L handlers are built per chunk by sv_spec_run*
+        const uint64_t nprev = ipow(m->emits, level - 1);
+        s->ondemand = true;
+        s->t_begin = s->t_end = s->table_first = ntuples; // no level-L table
+        if (cudaMalloc(&s->d_prev, nprev * mat_elems * sizeof(float)) != cudaSuccess) {
+            cudaGetLastError();
+            delete s;
+            return sv_fail(SV_ERR_MEMORY, "sv_spec_create: the level-(L-1) table does not fit device memory");
+        }
+        int rc = (level == 3 && pair_prepare(m, &pairdev)) ? build_pair_level2(m, pairdev, 0, nprev, s->d_prev, st)
+                                                          : build_sparse(m, level - 1, 0, nprev, s->d_prev, st);
+        if (rc == SV_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "sv_spec_create: precompute failed");
+        if (rc != SV_OK) {
+            sv_spec_destroy(s);
+            return rc;
+        }
+        *out = s;
+        return SV_OK;
+    }
     if (level > 1) {
         const size_t mat = static_cast<size_t>(m->n) * m->n;
         s->table_first = tuple_begin;
@@ -1502,6 +1590,8 @@ extern "C" void sv_spec_destroy(sv_spec* s) {
     }
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->ev_done) cudaEventDestroy(s->ev_done);
+    if (s->d_prev) cudaFree(s->d_prev);
+    if (s->d_scratch) cudaFree(s->d_scratch);
     if (s->d_v[0]) cudaFree(s->d_v[0]);
     if (s->d_v[1]) cudaFree(s->d_v[1]);
     delete s;
@@ -1790,11 +1880,11 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     SV_CUDA(cudaSetDevice(m->device));
     SvPairDev pd;
     // AUTO: the implicit run whenever the model is eligible (identical bits, ~5x faster, no table traffic)
-    bool implicit = s->run_mode != SV_SPEC_RUN_TABLE && implicit_supported(s, &pd);
+    bool implicit = !s->ondemand && s->run_mode != SV_SPEC_RUN_TABLE && implicit_supported(s, &pd);
     if (s->run_mode == SV_SPEC_RUN_IMPLICIT && !implicit)
         return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_run: implicit run needs level 2 and at most 4 dense rows");
     if (!implicit) cudaGetLastError();
-    if (!implicit && (s->t_begin != 0 || s->t_end != s->ntuples))
+    if (!implicit && !s->ondemand && (s->t_begin != 0 || s->t_end != s->ntuples))
         return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
     // runs on one spec share its state vectors: order this run after the previous one, whatever its stream
     if (s->ev_done == nullptr) SV_CUDA(cudaEventCreateWithFlags(&s->ev_done, cudaEventDisableTiming));
@@ -1850,6 +1940,37 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     if (ngroups > 1 && max_chunks > 0) {
         SV_CUDA(cudaEventRecord(s->ev_fork, st));
         for (int g = 1; g < ngroups; ++g) SV_CUDA(cudaStreamWaitEvent(s->aux[g - 1], s->ev_fork, 0));
+    }
+    if (s->ondemand && max_chunks > 0) {
+        // On-demand levels >= 3: per chunk, K3' builds the handler each sequence needs from the level-(L-1) table into
+        // a scratch (one handler per sequence of the group), then K4 applies it.  Groups bound the scratch to ~8 GB.
+        const size_t mat = n * n;
+        const uint64_t gmax = std::max<uint64_t>(1, std::min<uint64_t>(nseq, (8ull << 30) / (mat * sizeof(float))));
+        if (s->scratch_cap < gmax) {
+            if (s->d_scratch) cudaFree(s->d_scratch);
+            s->d_scratch = nullptr;
+            s->scratch_cap = 0;
+            SV_CUDA(cudaMalloc(&s->d_scratch, gmax * mat * sizeof(float)));
+            s->scratch_cap = gmax;
+        }
+        if (n > 65535) return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_run: on-demand mode supports up to 65535 states");
+        OnDemandSeqs os{static_cast<int>(nseq), seqs->dev.sym, seqs->dev.sym_bytes, seqs->dev.off};
+        for (uint64_t c = 0; c < max_chunks; ++c) {
+            for (uint64_t q0 = 0; q0 < nseq; q0 += gmax) {
+                const uint64_t q1 = std::min(nseq, q0 + gmax);
+                dim3 bgrid(static_cast<unsigned>((n + 1023) / 1024), static_cast<unsigned>(n), static_cast<unsigned>(q1 - q0));
+                ondemand_handler_kernel<<<bgrid, 256, 0, st>>>(m->gen, s->d_prev, s->d_scratch, os, c, static_cast<int>(s->level),
+                                                               static_cast<int>(m->emits), static_cast<int>(q0));
+                dim3 grid(static_cast<unsigned>(q1 - q0), static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta));
+                handler_gemv_kernel<<<grid, 256, n * sizeof(float), st>>>(
+                    static_cast<int>(n), static_cast<int>(m->emits), static_cast<int>(s->level), rs, c, s->d_scratch, ~0ull,
+                    s->d_v[cur], s->d_v[cur ^ 1], static_cast<int>(ld), rows_per_cta, static_cast<int>(q0));
+                launches += 2;
+            }
+            cur ^= 1;
+        }
+        SV_CUDA(cudaGetLastError());
+        max_chunks = 0;
     }
     for (uint64_t c = 0; c < max_chunks; ++c) {
         for (int g = 0; g < ngroups; ++g) {

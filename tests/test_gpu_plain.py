@@ -209,6 +209,36 @@ def test_many_sequences_queue(api, oracle):
         assert same_bits(out, exp), kernel
 
 
+def test_multi_device_entry_point(api, oracle, load_model):
+    """sv_multi_*: the C-level multi-GPU batch call (replicas, contiguous symbol-balanced ranges, one host thread
+    per device).  On a one-GPU box two replicas on device 0 exercise the same code; all devices when there are more."""
+    from spec_viterbi_b200 import generators, _lib
+    ndev = _lib.lib().sv_device_count()
+    devices = list(range(ndev)) if ndev > 1 else [0, 0]
+    rng = np.random.default_rng(8)
+    for hmm in (load_model("300"), generators.random_hmm(states_num=400, seed=6)):
+        lens = [int(x) for x in rng.integers(1, 200, 333)]
+        seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in lens]
+        syms, offs = api.pack_sequences(seqs)
+        mm = api.MultiModel(hmm, devices)
+        assert mm.ndev == len(devices)
+        exp = oracle.plain_batch(hmm, syms, offs, threads=8)
+        for sy in (syms, syms.astype(np.uint8)):
+            out, best, arg = mm.viterbi_batch(sy, offs)
+            assert same_bits(out, exp)
+            for k in range(0, len(seqs), 11):
+                bv, bi = best_state(exp[k])
+                assert (best[k] == bv or (np.isposinf(bv) and np.isposinf(best[k]))) and arg[k] == bi
+        # fewer sequences than devices, and a symbol out of range on the LAST device's share
+        out, _, _ = mm.viterbi_batch(syms[: int(offs[1])], offs[:2])
+        assert same_bits(out[0], exp[0])
+        bad = syms.copy()
+        bad[-1] = 77
+        with pytest.raises(_lib.SvError):
+            mm.viterbi_batch(bad, offs)
+        mm.close()
+
+
 def test_adaptor_mirrors_reference_interface(api, oracle, load_model, load_seqs):
     impl = api.B200_impl()
     hmm = load_model("100")

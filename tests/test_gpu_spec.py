@@ -134,6 +134,47 @@ def test_level3_small_alphabet(api, oracle):
         assert same_bits(impl.run_Viterbi_spec(s), osp.run(s)), L
 
 
+def test_level3_on_demand(api, oracle, load_model):
+    """level 3 WITHOUT the level-3 table.  SV_SPEC_ONDEMAND keeps only the level-2 table and builds,
+    per chunk, the level-3 handler each sequence observes (H(k1,k2,k3) = M_k3 (x) H(k1,k2),
+    GraphBLAS_spec_impl.cpp:15-36) before applying it: the bits of the full-table run and of the oracle."""
+    from spec_viterbi_b200 import generators, _lib
+    rng = np.random.default_rng(13)
+    # (a) against the full level-3 table and the oracle on a model whose 8000 handlers fit easily
+    hmm = generators.random_hmm(states_num=90, seed=4)
+    seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 8, 40, 121)]
+    syms, offs = api.pack_sequences(seqs)
+    m = api.Model(hmm)
+    full = api.Spec(m, 3, _lib.SPEC_SPARSE_LHS)
+    exp, ebest, earg = full.run_batch(syms, offs)
+    full.close()
+    od = api.Spec(m, 3, _lib.SPEC_ONDEMAND)
+    got, best, arg = od.run_batch(syms, offs)
+    assert same_bits(got, exp) and np.array_equal(best, ebest) and np.array_equal(arg, earg)
+    osp = oracle.spec(hmm, 3)
+    for k in (0, 3, 6, 8, 9):
+        assert same_bits(got[k], osp.run(seqs[k])), k
+    with pytest.raises(_lib.SvError):   # there is no level-3 table to read a handler from
+        od.handler(5)
+    od.close()
+    # (b) the case the mode exists for: 2405.chmm at level 3 (full table: 185 GB) on one GPU, against the oracle
+    hmm = load_model("2405")
+    seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (20, 13, 1, 31)]
+    syms, offs = api.pack_sequences(seqs)
+    m = api.Model(hmm)
+    od = api.Spec(m, 3)                 # AUTO: the full table cannot fit -> on demand
+    got, best, arg = od.run_batch(syms, offs)
+    osp = oracle.spec(hmm, 3)
+    for k in range(len(seqs)):
+        exp = osp.run(seqs[k])
+        assert same_bits(got[k], exp), k
+        assert best[k] == exp.min() and arg[k] == exp.argmin()
+    # the reference interface takes it too
+    impl = api.B200_spec_impl(3)
+    impl.spec_with(hmm)
+    assert same_bits(impl.run_Viterbi_spec(seqs[1]), osp.run(seqs[1]))
+
+
 def test_spec_vs_plain_cross_path(api, load_model, load_seqs):
     """Across paths the reference's own criterion holds (abs <= 1.0, HMM.h:43-49); the fp32
     re-association gap is reported, argmin must match."""

@@ -32,6 +32,10 @@ def run(cfg, model, seqfile, kernel=None):
 if __name__ == "__main__":
     run("configs[1]: 1200.chmm x emit_3_3500_20, plain", "1200", "emit_3_3500_20")
     run("configs[3]: 2405.chmm x covid-19 (16 ragged sequences, longest 7096), plain", "2405", "covid-19")
+    # the 1/2/4-way split question: the chain kernel on a quarter / half / the whole of the work per CTA
+    run("600.chmm (128-thread CTA: a quarter of 2405's positions per sequence)", "600", "emit_3_3500_20")
+    run("1200.chmm (256-thread CTA: half)", "1200", "emit_3_3500_20")
+    run("2405.chmm (512-thread CTA)", "2405", "emit_3_3500_20")
     run("configs[1] on the edge-stationary kernel (round-1 choice)", "1200", "emit_3_3500_20", _lib.KERNEL_ES)
     run("configs[3] on the edge-stationary kernel (round-1 choice)", "2405", "covid-19", _lib.KERNEL_ES)
     run("configs[1] on the generic kernel", "1200", "emit_3_3500_20", _lib.KERNEL_GENERIC)
