@@ -176,16 +176,21 @@ def test_level3_on_demand(api, oracle, load_model):
 
 
 def test_spec_vs_plain_cross_path(api, load_model, load_seqs):
-    """Across paths the reference's own criterion holds (abs <= 1.0, HMM.h:43-49); the fp32
-    re-association gap is reported, argmin must match."""
+    """Across paths (spec level 2 vs plain) fp32 re-association differs in every element.  north_star asks for <= 1e-5
+    relative on final scores; SURVEY A.2 measured 9.6e-6 on this input with the reference itself and up to 1.6e-5 on
+    others, so the bound asserted here is 2e-5 (documented in DESIGN.md section 2) plus the reference's own criterion
+    (abs <= 1.0 or both +inf, HMM.h:43-49) and equal argmin.  Positions that are +inf on both sides are masked."""
     hmm = load_model("300")
     seqs = load_seqs("emit_3_3500_20")
     plain = api.B200_impl().run_Viterbi_batch(hmm, seqs)
     impl = api.B200_spec_impl(2)
     impl.spec_with(hmm)
     spec = impl.run_Viterbi_spec_batch(seqs)
-    assert np.all(np.abs(plain - spec) <= 1.0)
-    assert np.max(np.abs(plain - spec) / plain) < 5e-5
+    both_inf = np.isposinf(plain) & np.isposinf(spec)
+    assert np.array_equal(np.isposinf(plain), np.isposinf(spec))
+    fin = ~both_inf
+    assert np.all(np.abs(plain[fin] - spec[fin]) <= 1.0)
+    assert np.max(np.abs(plain[fin] - spec[fin]) / np.abs(plain[fin])) < 2e-5
     assert np.array_equal(plain.argmin(1), spec.argmin(1))
 
 
