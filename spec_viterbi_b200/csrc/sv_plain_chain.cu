@@ -82,6 +82,15 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
     return r;
 }
 
+// E of the thread's five positions for one sequence as ONE tcgen05.ld.x8 (three columns more than needed: they
+// belong to the next symbol, or to the unused tail of the allocation, and are ignored)
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+
 template <int TPG, int Q, bool NN, bool PK>
 __global__ void __launch_bounds__(TPG, 512 / TPG)
 sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict__ best,
@@ -91,6 +100,8 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     constexpr int R = SV_CHAIN_RPT;
     constexpr int RS = SV_CHAIN_RPT;
     constexpr int QS = 8; // stride of the per-sequence shared arrays
+    // one tcgen05.ld.x8 per sequence (5 % off the single-sequence step) where registers allow, else .x4 + .x1
+    constexpr bool X8 = Q <= 2;
     static_assert(R == 5 && Q <= 8 && NW <= 32, "layout");
 
     __shared__ LsCtl ctl[4];
@@ -221,12 +232,13 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
 
     // flags and TMEM columns of the coming step, fetched before the barrier that ends the current one
     uint4 fl, cA, cB;
-    uint32_t eA[5], eB[5]; // E[o_q][own positions], double buffered over q
+    uint32_t eA[8], eB[8]; // E[o_q][own positions] (+3 ignored columns), double buffered over q
     auto prefetch_step = [&](const LsCtl& nc) {
         fl = *reinterpret_cast<const uint4*>(&nc.init_mask);
         cA = *reinterpret_cast<const uint4*>(&nc.col[0]);
         cB = *reinterpret_cast<const uint4*>(&nc.col[4]);
-        tmem_ld5(tE + cA.x, eA);
+        if constexpr (X8) tmem_ld8(tE + cA.x, eA);
+        else tmem_ld5(tE + cA.x, reinterpret_cast<uint32_t(&)[5]>(eA));
     };
     prefetch_step(ctl[0]);
 
@@ -282,11 +294,14 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
         //      predecessor of this thread's first position ----
         auto seq_step = [&](auto qc, float hub, float pv, float& red) {
             constexpr int q = decltype(qc)::value;
-            uint32_t(&ec)[5] = (q & 1) ? eB : eA;
-            uint32_t(&en)[5] = (q & 1) ? eA : eB;
+            uint32_t(&ec)[8] = (q & 1) ? eB : eA;
+            uint32_t(&en)[8] = (q & 1) ? eA : eB;
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]));
-            if constexpr (q + 1 < Q) tmem_ld5(tE + cols[q + 1 < Q ? q + 1 : 0], en);
+            if constexpr (q + 1 < Q) {
+                if constexpr (X8) tmem_ld8(tE + cols[q + 1 < Q ? q + 1 : 0], en);
+                else tmem_ld5(tE + cols[q + 1 < Q ? q + 1 : 0], reinterpret_cast<uint32_t(&)[5]>(en));
+            }
             if constexpr (PK) {
                 // ec = E of positions 1,2,3,4,0.  Band predecessors of (1,2) are (0,1), of (3,4) are (2,3).
                 const f32x2 e12 = pack2(__uint_as_float(ec[0]), __uint_as_float(ec[1]));
