@@ -784,7 +784,15 @@ extern "C" int sv_k0_lockstep_check(uint64_t states, uint64_t emits, uint64_t tr
     SvLsPlan plan;
     SvLsPlanOpts opts;
     opts.threads = static_cast<int>(std::max(1u, std::min(8u, std::thread::hardware_concurrency())));
-    sv_ls_build_plan(csr, emis, start, emits, 227 * 1024, &plan, opts);
+    // SV_K0_CHECK_USE_CACHE=1: go through the on-disk plan cache exactly as sv_model_ensure_ls does (load, else build
+    // and store), so that the cache round trip can be tested without a device
+    const char* use_cache = std::getenv("SV_K0_CHECK_USE_CACHE");
+    const bool cached = use_cache != nullptr && use_cache[0] == '1';
+    const uint64_t fp = cached ? sv_model_fingerprint(csr, emis, start, emits) : 0;
+    if (!cached || !sv_plan_cache_load(fp, &plan)) {
+        sv_ls_build_plan(csr, emis, start, emits, 227 * 1024, &plan, opts);
+        if (cached) sv_plan_cache_store(fp, plan);
+    }
     std::memset(stats, 0, 12 * sizeof(uint64_t));
     stats[0] = plan.valid ? 1 : 0;
     if (!plan.valid) return SV_OK;

@@ -22,7 +22,7 @@
 
 namespace {
 
-constexpr char kMagic[8] = {'S', 'V', 'L', 'S', 'P', 'L', 'N', '2'};
+constexpr char kMagic[8] = {'S', 'V', 'L', 'S', 'P', 'L', 'N', '3'};
 // bump when SvLsPlan's meaning changes (planner, variant table, kernel register layout)
 constexpr uint64_t kPlanVersion = 0x20261105ull;
 
@@ -93,7 +93,21 @@ struct PlanHeader {
     uint64_t version, fingerprint;
     int32_t variant_index, n_int, n_lpad, n_pad, n_heavy, nslots, ranks, tmem_cols, nonneg, pad;
     uint64_t gather_wavefronts, gather_ideal, split_states, smem_bytes, smem_bytes4, sa_iters, cost_before, cost_after;
+    uint64_t payload_hash; // over every vector below: a damaged payload must never become a wrong schedule
 };
+
+uint64_t payload_hash(const SvLsPlan& p) {
+    uint64_t h = 0x5061796c6f616421ull;
+    h = hash_words(h, p.edge_w.data(), p.edge_w.size() * sizeof(float));
+    h = hash_words(h, p.edge_off.data(), p.edge_off.size() * sizeof(uint32_t));
+    h = hash_words(h, p.deg.data(), p.deg.size());
+    h = hash_words(h, p.heavy_slots.data(), p.heavy_slots.size());
+    h = hash_words(h, p.emis_p.data(), p.emis_p.size() * sizeof(float));
+    h = hash_words(h, p.start_p.data(), p.start_p.size() * sizeof(float));
+    h = hash_words(h, p.copy_ptr.data(), p.copy_ptr.size() * sizeof(uint32_t));
+    h = hash_words(h, p.copy_p.data(), p.copy_p.size() * sizeof(uint32_t));
+    return h;
+}
 
 } // namespace
 
@@ -124,7 +138,7 @@ bool sv_plan_cache_load(uint64_t fingerprint, SvLsPlan* plan) {
          get_vec(f, &p.heavy_slots, cap) && get_vec(f, &p.emis_p, cap) && get_vec(f, &p.start_p, cap) &&
          get_vec(f, &p.copy_ptr, cap) && get_vec(f, &p.copy_p, cap);
     std::fclose(f);
-    if (!ok) return false;
+    if (!ok || payload_hash(p) != h.payload_hash) return false;
     p.var = sv_ls_variant(h.variant_index);
     p.variant_index = h.variant_index;
     p.n_int = h.n_int;
@@ -192,6 +206,7 @@ void sv_plan_cache_store(uint64_t fingerprint, const SvLsPlan& p) {
     h.sa_iters = p.sa_iters;
     h.cost_before = p.colour_cost_before;
     h.cost_after = p.colour_cost_after;
+    h.payload_hash = payload_hash(p);
     bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1 && put_vec(f, p.edge_w) && put_vec(f, p.edge_off) &&
               put_vec(f, p.deg) && put_vec(f, p.heavy_slots) && put_vec(f, p.emis_p) && put_vec(f, p.start_p) &&
               put_vec(f, p.copy_ptr) && put_vec(f, p.copy_p);

@@ -145,3 +145,50 @@ def test_multi_split(api):
         loads = np.array([int(offs[cut[k + 1]] - offs[cut[k]]) for k in range(parts)])
         assert loads.max() - loads.min() <= 2 * lens.max()
     assert list(api.multi_split(np.array([0, 5, 9], np.uint64), 8)[[0, -1]]) == [0, 2]  # more devices than sequences
+
+
+def test_plan_cache_round_trip(api, oracle, monkeypatch, tmp_path):
+    """The on-disk plan cache: a stored lockstep plan is loaded by the next process-level use (same statistics, same
+    replayed bits, no search), another model never matches it, and a damaged file is ignored and rebuilt."""
+    import time
+    from spec_viterbi_b200 import generators
+    monkeypatch.setenv("SV_PLAN_CACHE_DIR", str(tmp_path))
+    monkeypatch.setenv("SV_K0_CHECK_USE_CACHE", "1")
+    monkeypatch.setenv("SV_LS_SA_ITERS", "400000")
+    hmm = generators.random_hmm(states_num=900, seed=17)
+    seq = np.random.default_rng(2).integers(0, 20, 80).astype(np.uint64)
+    t0 = time.perf_counter()
+    st1, out1 = api.k0_lockstep_check(hmm, seq)
+    t_build = time.perf_counter() - t0
+    files = list(tmp_path.glob("ls-*.svplan"))
+    assert len(files) == 1 and st1["valid"] == 1
+    t0 = time.perf_counter()
+    st2, out2 = api.k0_lockstep_check(hmm, seq)
+    t_load = time.perf_counter() - t0
+    assert st2 == st1 and same_bits(out2, out1) and same_bits(out1, oracle.plain(hmm, seq))
+    assert t_load < t_build  # no colouring search the second time
+    other = generators.random_hmm(states_num=900, seed=18)
+    api.k0_lockstep_check(other, seq)
+    assert len(list(tmp_path.glob("ls-*.svplan"))) == 2  # keyed by content: a second file, not a false hit
+    # damage the first file: truncated, then garbage of the right length -> ignored, rebuilt, replaced
+    blob = files[0].read_bytes()
+    files[0].write_bytes(blob[: len(blob) // 2])
+    st3, out3 = api.k0_lockstep_check(hmm, seq)
+    assert st3["valid"] == 1 and same_bits(out3, out1)
+    files[0].write_bytes(blob[:200] + bytes(len(blob) - 200))
+    st4, out4 = api.k0_lockstep_check(hmm, seq)
+    assert st4["valid"] == 1 and same_bits(out4, out1)
+    # one flipped payload byte with every size field intact: caught by the payload checksum (a wrong weight in an
+    # accepted plan would be a silently wrong result)
+    good = files[0].read_bytes()
+    bad = bytearray(good)
+    bad[len(bad) // 3] ^= 0x40
+    files[0].write_bytes(bytes(bad))
+    st5, out5 = api.k0_lockstep_check(hmm, seq)
+    assert st5["valid"] == 1 and same_bits(out5, out1)
+    assert files[0].read_bytes() == good  # rebuilt (deterministic search) and stored again
+    monkeypatch.setenv("SV_PLAN_CACHE", "0")   # disabled: nothing is read or written
+    for f in tmp_path.glob("ls-*.svplan"):
+        f.unlink()
+    api.k0_lockstep_check(hmm, seq)
+    assert not list(tmp_path.glob("ls-*.svplan"))
