@@ -920,12 +920,22 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
     const int kernel = chosen_kernel(m, seqs->nseq);
     m->last_nseq = seqs->nseq;
     m->last_kernel = kernel;
+    // 8-sequence CTAs: where the 4-per-CTA tail of the queue begins (see SvSeqsDev::tail_begin)
+    auto with_tail = [&](int grid) {
+        SvSeqsDev d = seqs->dev;
+        const uint64_t wave = 8ull * static_cast<uint64_t>(grid);
+        const uint64_t full = seqs->nseq / wave * wave, rest = seqs->nseq - full;
+        d.tail_begin = (rest > 0 && rest <= 4ull * static_cast<uint64_t>(grid)) ? static_cast<unsigned>(full) : 0xffffffffu;
+        if (const char* env = std::getenv("SV_TAIL_BALANCE"))
+            if (env[0] == '0') d.tail_begin = 0xffffffffu;
+        return d;
+    };
     if (kernel == SV_KERNEL_CHAIN) {
         const int q = chain_q_for(m, seqs->nseq);
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
         const int grid = static_cast<int>(std::min<int64_t>(want, int64_t(m->sm_count) * m->chain_ctas_per_sm));
         m->last_seqs_per_cta = q;
-        rc = sv_chain_launch(m->chain.threads, q, m->chaindev, seqs->dev, d_out, d_best, d_best_state, counter, grid,
+        rc = sv_chain_launch(m->chain.threads, q, m->chaindev, q == 8 ? with_tail(grid) : seqs->dev, d_out, d_best, d_best_state, counter, grid,
                              m->chain_smem[q == 8 ? 3 : q == 4 ? 2 : q == 2 ? 1 : 0], st);
     } else if (kernel == SV_KERNEL_LS) {
         // 8 sequences per CTA when that fills every SM, else 4 (twice the CTAs, about half the step time each)
@@ -935,7 +945,7 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
         const int grid = static_cast<int>(std::min<int64_t>(want, m->sm_count));
         m->last_seqs_per_cta = q;
-        rc = sv_ls_launch(m->ls.variant_index, nq4, m->lsdev, seqs->dev, d_out, d_best, d_best_state, counter, grid,
+        rc = sv_ls_launch(m->ls.variant_index, nq4, m->lsdev, nq4 == 2 ? with_tail(grid) : seqs->dev, d_out, d_best, d_best_state, counter, grid,
                           nq4 == 2 ? m->ls.smem_bytes : m->ls.smem_bytes4, st);
     } else if (kernel == SV_KERNEL_ES) {
         // a batch small enough that every sequence gets its own resident CTA runs one sequence per CTA

@@ -65,6 +65,11 @@ struct SvSeqsDev {
     const void* sym = nullptr;       // packed symbols, sequences concatenated in input order
     const uint64_t* off = nullptr;   // [nseq+1]
     const uint32_t* order = nullptr; // sequence ids, longest first (work-queue order)
+    // Set per launch by sv_viterbi_device (8-sequence CTAs only): queue positions >= tail_begin are handed out 4 per
+    // CTA.  Sequences of equal length finish together, and a queue that gives 8 to every CTA that asks leaves most SMs
+    // idle in the last wave (4096 sequences on 148 SMs: 68 CTAs would take 8, 80 none); when the remainder after the
+    // full waves is at most 4 per CTA, every CTA takes 4 and skips its idle float4 group (about half the step time).
+    unsigned tail_begin = 0xffffffffu;
 };
 
 // ------------------------------------------------ edge-stationary kernel ----

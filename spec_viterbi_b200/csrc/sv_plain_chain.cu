@@ -187,7 +187,10 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             mg_len = 0;
             mg_t = 0;
             uint32_t sid = 0;
-            const unsigned w = atomicAdd(counter, 1u);
+            // tail balance (SvSeqsDev::tail_begin): past that queue position the second float4 group stops fetching
+            bool take = true;
+            if (Q == 8 && lane >= 4) take = *reinterpret_cast<volatile unsigned*>(counter) < s.tail_begin;
+            const unsigned w = take ? atomicAdd(counter, 1u) : 0xffffffffu;
             if (w < static_cast<unsigned>(s.nseq)) {
                 sid = s.order[w];
                 const uint64_t b = s.off[sid];
@@ -354,7 +357,18 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             if (lane == 0) sts_vec<QV>(&s_red[bo][warp][g * QV], red);
         };
         group_step(std::integral_constant<int, 0>{});
-        if constexpr (NG > 1) group_step(std::integral_constant<int, (NG > 1 ? 1 : 0)>{});
+        if constexpr (NG > 1) {
+            // an idle second group (the tail of a batch, see refill) is skipped; the emission fetch issued for its first
+            // sequence is retired so that the next step's fetch into the same registers cannot be overtaken
+            if ((fl.z & 0xf0u) != 0) {
+                group_step(std::integral_constant<int, (NG > 1 ? 1 : 0)>{});
+            } else {
+                // sequence 3 issued the fetch for sequence 4 into eA: wait with eA still allocated (an asynchronous
+                // tcgen05.ld must never land in registers the compiler has handed to something else)
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                asm volatile("" ::"r"(eA[0]), "r"(eA[1]), "r"(eA[2]), "r"(eA[3]), "r"(eA[4]), "r"(eA[5]), "r"(eA[6]), "r"(eA[7]));
+            }
+        }
         // ---- rare: first step of a sequence, v_0 = E[o_0] + start replaces the relaxed scores (a real
         //      branch around everything, so the hot path carries no predicated loads) ----
         if (init_mask != 0) {

@@ -121,7 +121,10 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
             mg_len = 0;
             mg_t = 0;
             uint32_t sid = 0;
-            const unsigned w = atomicAdd(counter, 1u);
+            // tail balance (SvSeqsDev::tail_begin): past that queue position the second float4 group stops fetching
+            bool take = true;
+            if (Q == 8 && lane >= 4) take = *reinterpret_cast<volatile unsigned*>(counter) < s.tail_begin;
+            const unsigned w = take ? atomicAdd(counter, 1u) : 0xffffffffu;
             if (w < static_cast<unsigned>(s.nseq)) {
                 sid = s.order[w];
                 const uint64_t b = s.off[sid];
@@ -357,7 +360,23 @@ sv_ls_kernel(SvLsDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict_
                 }
             }
         }
-        if constexpr (NQ4 == 2) group_step(std::integral_constant<int, 1>{});
+        if constexpr (NQ4 == 2) {
+            // an idle second group -- the tail of a batch, SvSeqsDev::tail_begin -- is skipped (39.7 instead of 42.8 ms for
+            // 4096 equal sequences on 148 SMs).  Its slices would have read the control block of the NEXT step; and the
+            // emission fetch that group 0's last slice issued for it is retired with its destination registers still
+            // allocated (an asynchronous tcgen05.ld must never land in registers the compiler has handed to something
+            // else).  Guarding that fetch with a branch instead was measured: 42.4 ms, it disturbs the hot path.
+            if ((fl.z & 0xf0u) != 0) {
+                group_step(std::integral_constant<int, 1>{});
+            } else {
+                prefetch_ctl(ctl[(tau + 1u) & 3u]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    asm volatile("" ::"r"(et[NQ4 - 1][j][0]), "r"(et[NQ4 - 1][j][1]), "r"(et[NQ4 - 1][j][2]),
+                                 "r"(et[NQ4 - 1][j][3]), "r"(et[NQ4 - 1][j][4]));
+            }
+        }
         if (init_mask != 0) init_fix(0, Q);
 
         // first emission scores of step tau + 1 (control block published during step tau - 1, read in
