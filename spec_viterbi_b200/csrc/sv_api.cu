@@ -426,9 +426,13 @@ int chain_q_for(const sv_model* m, uint64_t nseq) {
     int best_q = 1;
     uint64_t best_cost = ~0ull;
     for (const int q : {8, 4, 2, 1}) {
-        const uint64_t ctas = (nseq + q - 1) / q;
-        const uint64_t waves = (ctas + slots - 1) / slots;
-        const uint64_t cost = waves * static_cast<uint64_t>(2 + q);
+        const uint64_t grid = std::min<uint64_t>((nseq + q - 1) / q, slots);
+        const uint64_t wave = grid * static_cast<uint64_t>(q);
+        const uint64_t full = nseq / wave, rest = nseq - full * wave;
+        // the partial last wave costs a whole step time -- or, for 8-sequence CTAs, a 4-sequence one when it is
+        // handed out 4 per CTA (the tail balance of sv_viterbi_device)
+        const uint64_t tail = rest == 0 ? 0 : (q == 8 && full > 0 && rest <= 4 * grid) ? 2 + 4 : 2 + q;
+        const uint64_t cost = full * static_cast<uint64_t>(2 + q) + tail;
         if (cost < best_cost) {
             best_cost = cost;
             best_q = q;
@@ -788,6 +792,7 @@ int seqs_assign(sv_seqs* s, const sv_model* m, const SrcT* symbols, const uint64
     s->nseq = nseq;
     s->total = total;
     s->max_len = max_len;
+    s->min_len = min_len;
     s->h2d_bytes = total * sym_bytes + (nseq + 1) * sizeof(uint64_t) + nseq * sizeof(uint32_t);
     s->dev.nseq = static_cast<int>(nseq);
     s->dev.sym_bytes = sym_bytes;
@@ -920,23 +925,54 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
     const int kernel = chosen_kernel(m, seqs->nseq);
     m->last_nseq = seqs->nseq;
     m->last_kernel = kernel;
-    // 8-sequence CTAs: where the 4-per-CTA tail of the queue begins (see SvSeqsDev::tail_begin)
-    auto with_tail = [&](int grid) {
-        SvSeqsDev d = seqs->dev;
+    // 8-sequence CTAs and the last, partial wave of a batch (see SvSeqsDev::tail_begin): when what is left after the full
+    // waves is at most 4 sequences per CTA, it is handed out 4 per CTA.  Sequences of ONE length finish together, so
+    // the tail can even be a second launch of the 4-sequence instantiation behind the first (its step is shorter than
+    // an 8-sequence CTA's with one group skipped); ragged batches keep one launch and the in-kernel tail.
+    const bool tail_on = [] {
+        const char* env = std::getenv("SV_TAIL_BALANCE");
+        return !(env != nullptr && env[0] == '0');
+    }();
+    auto tail_of = [&](int grid, uint64_t* full, uint64_t* rest) {
         const uint64_t wave = 8ull * static_cast<uint64_t>(grid);
-        const uint64_t full = seqs->nseq / wave * wave, rest = seqs->nseq - full;
-        d.tail_begin = (rest > 0 && rest <= 4ull * static_cast<uint64_t>(grid)) ? static_cast<unsigned>(full) : 0xffffffffu;
-        if (const char* env = std::getenv("SV_TAIL_BALANCE"))
-            if (env[0] == '0') d.tail_begin = 0xffffffffu;
-        return d;
+        *full = seqs->nseq / wave * wave;
+        *rest = seqs->nseq - *full;
+        return tail_on && *full > 0 && *rest > 0 && *rest <= 4ull * static_cast<uint64_t>(grid);
     };
+    const bool one_length = seqs->min_len == seqs->max_len;
+    auto next_counter = [&](unsigned** c) -> cudaError_t {
+        *c = m->d_counters + static_cast<size_t>(m->launch_seq++ % SV_COUNTER_RING) * 16;
+        return cudaMemsetAsync(*c, 0, sizeof(unsigned), st);
+    };
+    m->last_launches = 1;
     if (kernel == SV_KERNEL_CHAIN) {
         const int q = chain_q_for(m, seqs->nseq);
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
         const int grid = static_cast<int>(std::min<int64_t>(want, int64_t(m->sm_count) * m->chain_ctas_per_sm));
         m->last_seqs_per_cta = q;
-        rc = sv_chain_launch(m->chain.threads, q, m->chaindev, q == 8 ? with_tail(grid) : seqs->dev, d_out, d_best, d_best_state, counter, grid,
-                             m->chain_smem[q == 8 ? 3 : q == 4 ? 2 : q == 2 ? 1 : 0], st);
+        auto smem_of = [&](int qq) { return m->chain_smem[qq == 8 ? 3 : qq == 4 ? 2 : qq == 2 ? 1 : 0]; };
+        uint64_t full = 0, rest = 0;
+        SvSeqsDev d = seqs->dev;
+        if (q == 8 && tail_of(grid, &full, &rest)) {
+            if (one_length) {
+                d.nseq = static_cast<int>(full);
+                SvSeqsDev dt = seqs->dev;
+                dt.order += full;
+                dt.nseq = static_cast<int>(rest);
+                rc = sv_chain_launch(m->chain.threads, 8, m->chaindev, d, d_out, d_best, d_best_state, counter, grid, smem_of(8), st);
+                unsigned* c2 = nullptr;
+                if (rc == 0) rc = next_counter(&c2);
+                if (rc == 0)
+                    rc = sv_chain_launch(m->chain.threads, 4, m->chaindev, dt, d_out, d_best, d_best_state, c2,
+                                         static_cast<int>((rest + 3) / 4), smem_of(4), st);
+                m->last_launches = 2;
+            } else {
+                d.tail_begin = static_cast<unsigned>(full);
+                rc = sv_chain_launch(m->chain.threads, 8, m->chaindev, d, d_out, d_best, d_best_state, counter, grid, smem_of(8), st);
+            }
+        } else {
+            rc = sv_chain_launch(m->chain.threads, q, m->chaindev, d, d_out, d_best, d_best_state, counter, grid, smem_of(q), st);
+        }
     } else if (kernel == SV_KERNEL_LS) {
         // 8 sequences per CTA when that fills every SM, else 4 (twice the CTAs, about half the step time each)
         int nq4 = seqs->nseq <= static_cast<uint64_t>(4) * m->sm_count ? 1 : 2;
@@ -945,8 +981,29 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
         const int64_t want = (static_cast<int64_t>(seqs->nseq) + q - 1) / q;
         const int grid = static_cast<int>(std::min<int64_t>(want, m->sm_count));
         m->last_seqs_per_cta = q;
-        rc = sv_ls_launch(m->ls.variant_index, nq4, m->lsdev, nq4 == 2 ? with_tail(grid) : seqs->dev, d_out, d_best, d_best_state, counter, grid,
-                          nq4 == 2 ? m->ls.smem_bytes : m->ls.smem_bytes4, st);
+        uint64_t full = 0, rest = 0;
+        SvSeqsDev d = seqs->dev;
+        if (nq4 == 2 && tail_of(grid, &full, &rest)) {
+            if (one_length) {
+                d.nseq = static_cast<int>(full);
+                SvSeqsDev dt = seqs->dev;
+                dt.order += full;
+                dt.nseq = static_cast<int>(rest);
+                rc = sv_ls_launch(m->ls.variant_index, 2, m->lsdev, d, d_out, d_best, d_best_state, counter, grid, m->ls.smem_bytes, st);
+                unsigned* c2 = nullptr;
+                if (rc == 0) rc = next_counter(&c2);
+                if (rc == 0)
+                    rc = sv_ls_launch(m->ls.variant_index, 1, m->lsdev, dt, d_out, d_best, d_best_state, c2,
+                                      static_cast<int>(std::min<uint64_t>((rest + 3) / 4, m->sm_count)), m->ls.smem_bytes4, st);
+                m->last_launches = 2;
+            } else {
+                d.tail_begin = static_cast<unsigned>(full);
+                rc = sv_ls_launch(m->ls.variant_index, 2, m->lsdev, d, d_out, d_best, d_best_state, counter, grid, m->ls.smem_bytes, st);
+            }
+        } else {
+            rc = sv_ls_launch(m->ls.variant_index, nq4, m->lsdev, d, d_out, d_best, d_best_state, counter, grid,
+                              nq4 == 2 ? m->ls.smem_bytes : m->ls.smem_bytes4, st);
+        }
     } else if (kernel == SV_KERNEL_ES) {
         // a batch small enough that every sequence gets its own resident CTA runs one sequence per CTA
         // (shorter steps); larger batches advance two sequences per CTA in lockstep
@@ -966,7 +1023,6 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
         m->last_seqs_per_cta = 1;
         rc = sv_generic_launch(m->gen, seqs->dev, d_out, d_best, d_best_state, counter, grid, st);
     }
-    m->last_launches = 1;
     if (rc != 0) return sv_fail(SV_ERR_CUDA, cudaGetErrorString(static_cast<cudaError_t>(rc)));
     return SV_OK;
     SV_API_END

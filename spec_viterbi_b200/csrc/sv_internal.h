@@ -336,7 +336,7 @@ bool sv_model_ensure_chain(sv_model* m);
 
 struct sv_seqs {
     int device = 0;
-    uint64_t nseq = 0, total = 0, max_len = 0;
+    uint64_t nseq = 0, total = 0, max_len = 0, min_len = 0;
     uint64_t h2d_bytes = 0; // bytes the last (re)fill copied to the device
     SvSeqsDev dev;
     void* d_blob = nullptr;

@@ -142,6 +142,28 @@ def test_chain_kernel_batches(name, nseq, api, oracle, load_model):
     assert same_bits(out2, exp) and np.array_equal(best2, best) and np.array_equal(arg2, arg)
 
 
+@pytest.mark.parametrize("kernel", ["ls", "chain"])
+@pytest.mark.parametrize("ragged", [False, True])
+def test_tail_balance(kernel, ragged, api, oracle, load_model):
+    """The last, partial wave of a batch of 8-sequence CTAs is handed out 4 per CTA: as a second launch of the
+    4-sequence kernel when all sequences have one length, inside the kernel (second float4 group idle and skipped) when
+    they are ragged.  Same bits; every sequence processed exactly once."""
+    from spec_viterbi_b200 import generators, _lib
+    sms = 148
+    hmm = load_model("2405") if kernel == "chain" else generators.random_hmm(states_num=500, seed=21)  # one CTA per SM
+    n_seq = 8 * sms + 4 * sms - 37           # one full wave + a tail of at most 4 per CTA
+    rng = np.random.default_rng(5)
+    lens = rng.integers(20, 60, n_seq) if ragged else np.full(n_seq, 41)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    syms = rng.integers(0, 20, int(offs[-1])).astype(np.uint8)
+    m = _model(api, hmm, kernel, must_fit=True)
+    out, best, arg = m.viterbi_batch(syms, offs)
+    assert _ran(m, kernel) and m.last_launches() == (1 if ragged else 2)
+    exp = oracle.plain_batch(hmm, syms.astype(np.uint64), offs, threads=16)
+    assert same_bits(out, exp)
+    assert np.array_equal(best, exp.min(1)) and np.array_equal(arg, exp.argmin(1))
+
+
 def test_chain_kernel_variants(api, oracle):
     """Chain structure with shuffled state numbering, a broken chain, +inf band weights, non-uniform hub weights,
     a second start state in the middle of the chain; and a model with no reachable state (argmin = -1)."""
