@@ -157,7 +157,8 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     // special rows: lane s of a warp finishes special s
     // (no run-time indexing into the kernel parameters: that would move the whole struct to local memory)
     static_assert(SV_CHAIN_NSP == 2, "two specials");
-    const bool sp1 = lane == 1;
+    constexpr int SW = NW >= 2 ? NW - 2 : 0; // the warp that finishes the special rows (not the manager warp)
+    const bool sp1 = lane >= Q;               // lanes 0..Q-1: special 0, lanes Q..2Q-1: special 1
     const float sp_u = sp1 ? m.u[1] : m.u[0], sp_s0 = sp1 ? m.ss[1][0] : m.ss[0][0];
     const float sp_s1 = sp1 ? m.ss[1][1] : m.ss[0][1], sp_start = sp1 ? m.start_s[1] : m.start_s[0];
     const float* __restrict__ start_p = m.start_p + tid * R;
@@ -273,22 +274,20 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             }
         }
 
-        // ---- special rows of step tau: warp w finishes sequences w, w + NW, .. from the partial minima
-        //      and special scores of step tau - 1 ----
+        // ---- special rows of step tau from the partial minima and special scores of step tau - 1: ONE warp, lane
+        //      (s, q) finishes special row s of sequence q (the minimum over the NW warp partials is a short serial
+        //      loop per lane instead of a REDUX per sequence on eight different warps) ----
+        if (warp == SW && lane < SV_CHAIN_NSP * Q) {
+            const int q = lane & (Q - 1);
+            float mm = s_red[bi][0][q];
 #pragma unroll
-        for (int q0 = 0; q0 < Q; q0 += NW) {
-            const int q = q0 + warp;
-            if (q < Q) {
-                float mm = lane < NW ? s_red[bi][lane][q] : pos_inf();
-                mm = warp_min_redux<NN>(mm);
-                if (lane < SV_CHAIN_NSP) {
-                    const float e = s_he[lane * kChainHeStride + ctl[tau & 3u].col[q]];
-                    float x = relax1(e, sp_u, mm);
-                    x = fminf(x, fminf(relax1(e, sp_s0, s_vs[bi][0][q]), relax1(e, sp_s1, s_vs[bi][1][q])));
-                    if ((init_mask >> q) & 1u) x = e + sp_start;
-                    s_vs[bo][lane][q] = x;
-                }
-            }
+            for (int w = 1; w + 1 < NW; w += 2) mm = fminf(mm, fminf(s_red[bi][w][q], s_red[bi][w + 1][q]));
+            if constexpr ((NW & 1) == 0) mm = fminf(mm, s_red[bi][NW - 1][q]);
+            const float e = s_he[(sp1 ? kChainHeStride : 0) + ctl[tau & 3u].col[q]];
+            float x = relax1(e, sp_u, mm);
+            x = fminf(x, fminf(relax1(e, sp_s0, s_vs[bi][0][q]), relax1(e, sp_s1, s_vs[bi][1][q])));
+            if ((init_mask >> q) & 1u) x = e + sp_start;
+            s_vs[bo][sp1 ? 1 : 0][q] = x;
         }
 
         // ---- chain positions, one group of QV sequences at a time.  Idle sequence slots are relaxed like the
