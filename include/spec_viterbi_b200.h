@@ -153,6 +153,22 @@ int sv_viterbi_batch_u8(sv_model* m, const uint8_t* symbols, const uint64_t* off
  * Asynchronous with respect to the host. */
 int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out, float* d_best,
                       int32_t* d_best_state, void* stream);
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results (bit for bit) as sv_viterbi_device, but the call allocates NOTHING: no
+ * cudaMalloc / cudaFree, no lazy K0 plan, no library routine that allocates.  It runs a variant of the generic
+ * kernel whose scratch (the score vectors of every CTA and the work-queue counter) is a fixed file-scope device
+ * array of SV_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   - limit: models with more than SV_STATIC_MAX_STATES states are refused (SV_ERR_ARG);
+ *   - all calls on one device share that array and it keeps the previous call's contents; the call clears the
+ *     one word that must start at zero (the queue counter) on `stream` itself;
+ *   - calls that overlap on the GPU (different streams without an ordering between them) RACE on the array:
+ *     order them (same stream, or an event).  Calls on different devices are independent.
+ * `m` and `seqs` are the ordinary handles (created earlier, where allocation is allowed); d_* as above. */
+#define SV_STATIC_MAX_STATES 4096
+#define SV_STATIC_SCRATCH_BYTES 4849920 /* (64 + 148 CTAs * 2 vectors * 4096 states) floats */
+int sv_viterbi_device_static(const sv_model* m, const sv_seqs* seqs, float* d_out, float* d_best,
+                             int32_t* d_best_state, void* stream);
 /* Kernel launches issued by the last sv_viterbi*_ / sv_spec_run* call on this model. */
 int sv_model_last_launches(const sv_model* m);
 

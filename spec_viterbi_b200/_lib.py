@@ -67,6 +67,7 @@ SIGNATURES = {
     "sv_viterbi_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, f32p, f32p, i32p]),
     "sv_viterbi_batch_u8": (C.c_int, [vp, u8p, u64p, C.c_uint64, f32p, f32p, i32p]),
     "sv_viterbi_device": (C.c_int, [vp, vp, vp, vp, vp, vp]),
+    "sv_viterbi_device_static": (C.c_int, [vp, vp, vp, vp, vp, vp]),
     "sv_spec_create": (C.c_int, [vp, C.c_uint64, C.c_int, C.c_uint64, C.c_uint64, vp, vp,
                                  C.POINTER(vp)]),
     "sv_spec_destroy": (None, [vp]),

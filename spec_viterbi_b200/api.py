@@ -276,6 +276,12 @@ class Model:
         L.check(self._lib.sv_viterbi_device(self._h, seqs.handle, d_out or None, d_best or None,
                                             d_arg or None, stream or None))
 
+    def viterbi_device_static(self, seqs: "Seqs", d_out: int = 0, d_best: int = 0, d_arg: int = 0, stream: int = 0):
+        """sv_viterbi_device_static: same results, allocates nothing (fixed device scratch, <= 4096 states;
+        calls that overlap on one GPU race on the scratch).  No counterpart in the reference."""
+        L.check(self._lib.sv_viterbi_device_static(self._h, seqs.handle, d_out or None, d_best or None,
+                                                   d_arg or None, stream or None))
+
 
 class MultiModel:
     """The HMM replicated on several devices of one box (sv_multi); batches are dealt to them."""

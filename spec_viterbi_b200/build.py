@@ -20,6 +20,7 @@ SOURCES = [
     "csrc/sv_api.cu",
     "csrc/sv_multi.cu",
     "csrc/sv_plain_generic.cu",
+    "csrc/sv_noalloc.cu",
     "csrc/sv_plain_es.cu",
     "csrc/sv_plain_ls.cu",
     "csrc/sv_plain_chain.cu",
