@@ -248,10 +248,16 @@ int sv_spec_load(sv_model* m, const char* path, float* d_table, sv_spec** out);
  * (K4i) -- same sums, same association, same bits, no table traffic; the table may then be empty
  * (sv_spec_create with tuple_begin == tuple_end == emits^level).  Level 2, models with at most 4
  * dense rows; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.
- * SV_SPEC_RUN_AUTO (default) = IMPLICIT whenever the spec is eligible, else TABLE.  Level 1 ignores the mode. */
+ * SV_SPEC_RUN_CHAIN (K4c): level 2 of a model with the chain + specials structure of the reference's profile HMMs
+ * (detected, never assumed): the two-step paths through the dense rows collapse onto the chain minimum because
+ * x -> fl(c + x) is monotone, so a chunk costs O(N) instead of O(N^2) and a whole batch is ONE persistent launch --
+ * still the sums of GraphBLAS_spec_impl.cpp:15-36,69-79 in their association, hence the same bits.  u8 symbols, emission
+ * table must fit shared memory; otherwise SV_ERR_UNSUPPORTED and the mode is unchanged.
+ * SV_SPEC_RUN_AUTO (default) = CHAIN, else IMPLICIT, whenever the spec is eligible, else TABLE.  Level 1 ignores the mode. */
 enum {
     SV_SPEC_RUN_TABLE = 0,
     SV_SPEC_RUN_IMPLICIT = 1, /* K4i */
+    SV_SPEC_RUN_CHAIN = 2,    /* K4c */
     SV_SPEC_RUN_AUTO = 3
 };
 int sv_spec_set_run_mode(sv_spec* s, int mode);

@@ -14,7 +14,7 @@ LIB_PATH = _PKG / "libspecviterbi_b200.so"
 SV_OK = 0
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_ES, KERNEL_LS, KERNEL_CHAIN = 0, 1, 2, 3, 4
 SPEC_AUTO, SPEC_DENSE_GEMM, SPEC_SPARSE_LHS, SPEC_PAIR_ROWS, SPEC_ONDEMAND = 0, 1, 2, 3, 4
-SPEC_RUN_TABLE, SPEC_RUN_IMPLICIT, SPEC_RUN_AUTO = 0, 1, 3
+SPEC_RUN_TABLE, SPEC_RUN_IMPLICIT, SPEC_RUN_CHAIN, SPEC_RUN_AUTO = 0, 1, 2, 3
 
 u64p = C.POINTER(C.c_uint64)
 u8p = C.POINTER(C.c_uint8)

@@ -25,6 +25,7 @@ SOURCES = [
     "csrc/sv_plain_ls.cu",
     "csrc/sv_plain_chain.cu",
     "csrc/sv_spec.cu",
+    "csrc/sv_spec_chain.cu",
     "csrc/sv_es_plan.cpp",
     "csrc/sv_ls_plan.cpp",
     "csrc/sv_chain_plan.cpp",

@@ -250,6 +250,12 @@ int sv_chain_prepare(int threads, int q, bool nonneg, size_t* smem_out, int* cta
 int sv_chain_launch(int threads, int q, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
                     int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
 
+// K4c (sv_spec_chain.cu): the level-2 specialised run of a chain + specials model in one persistent launch
+size_t sv_chain_pair_smem(int threads, int emits);
+int sv_chain_pair_prepare(int threads, bool nonneg, size_t smem, int* ctas_per_sm_out);
+int sv_chain_pair_launch(int threads, bool nonneg, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
+                         int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
+
 // ----------------------------------------------------------- host model ----
 struct sv_seqs;
 // Reusable buffers behind the host-pointer entry points (sv_viterbi*, sv_spec_run*).
@@ -308,6 +314,9 @@ struct sv_model {
     void* d_chain_blob = nullptr;
     size_t chain_smem[4] = {0, 0, 0, 0}; // dynamic shared memory of the Q = 1, 2, 4, 8 instantiations
     int chain_ctas_per_sm = 1;
+    int chain_pair_state = 0;    // K4c: 0 = not tried, 1 = ready, -1 = not eligible (no chain structure / table does not fit)
+    size_t chain_pair_smem = 0;
+    int chain_pair_ctas_per_sm = 1;
     // level-2 pair precompute (sv_spec.cu): dense copies of the heavy rows + CSC, built on first use
     void* d_pair_blob = nullptr;
     void* d_path_blob = nullptr; // K4i: flattened two-step paths (sv_spec.cu: path_prepare)

@@ -338,6 +338,61 @@ void anneal(Colouring& c, uint64_t iters, uint64_t seed, const volatile int* can
     }
 }
 
+// End game of the colouring search ("min-conflicts"): the annealing above proposes random partners, and once few
+// over-full (octet, colour) cells are left almost every proposal is rejected (8 M iterations leave ~40 of 1336,
+// 40 M leave ~11).  Here every move is chosen: take a row at one end of an edge that sits in an over-full cell,
+// evaluate the swap with EVERY degree-compatible position, apply the best one (ties broken at random; sideways
+// moves allowed, uphill moves never).  Only for graphs without heavy sources (swap_delta's precondition).
+void endgame(Colouring& c, uint64_t moves, uint64_t seed, const volatile int* cancel) {
+    const LGraph& g = *c.g;
+    if (c.cost == 0 || moves == 0 || c.n_heavy != 0) return;
+    Rng rng(seed ^ 0xe4d9a3e5ull);
+    SwapDelta sd, best_sd;
+    const uint32_t npos = static_cast<uint32_t>(c.n_lpad);
+    auto degree = [&](int32_t x) { return x < 0 ? size_t(0) : g.in[x].size(); };
+    uint64_t stale = 0;
+    for (uint64_t it = 0; it < moves && c.cost > 0 && !c.hot.empty(); ++it) {
+        if (cancel != nullptr && *cancel != 0) return;
+        const uint32_t cell = c.hot[rng.below(static_cast<uint32_t>(c.hot.size()))];
+        const uint32_t oct = cell >> 3, colr = cell & 7u;
+        uint32_t cand[64];
+        uint32_t nc = 0;
+        for (uint32_t l = 0; l < 8; ++l) {
+            const int32_t row = c.at_pos[oct * 8 + l];
+            if (row < 0) continue;
+            for (const uint32_t e : g.in[row])
+                if ((c.pos_of[g.edges[e].src] & 7u) == colr && nc < 64) cand[nc++] = e;
+        }
+        if (nc == 0) continue;
+        const LEdge& ed = g.edges[cand[rng.below(nc)]];
+        const uint32_t pa = (rng.next() & 1u) ? c.pos_of[ed.src] : c.pos_of[ed.dst];
+        if (pa >= npos) continue;
+        const int32_t a = c.at_pos[pa];
+        int64_t best = 1; // accept only delta <= 0
+        uint32_t best_pb = pa, nbest = 0;
+        for (uint32_t pb = 0; pb < npos; ++pb) {
+            if (pb == pa) continue;
+            const int32_t b = c.at_pos[pb];
+            if (degree(a) > c.cellD[pb >> 5] || degree(b) > c.cellD[pa >> 5]) continue;
+            const int64_t delta = swap_delta(c, pa, pb, sd);
+            if (sd.overflow || delta > 0 || delta > best) continue;
+            if (delta < best) {
+                best = delta;
+                nbest = 0;
+            }
+            // reservoir sampling among the equally good partners
+            if (rng.below(++nbest) == 0) {
+                best_pb = pb;
+                best_sd = sd;
+            }
+        }
+        if (best_pb == pa) continue;
+        apply_swap_delta(c, pa, best_pb, best_sd);
+        stale = best < 0 ? 0 : stale + 1;
+        if (stale > 4000) return; // plateau: sideways moves only for a long while
+    }
+}
+
 // ------------------------------------------------------------- slot assignment ----
 // One octet: rows[l] holds the (source position, weight) pairs of lane l.  Assigns every edge
 // to one of D slots (at most one edge per lane and slot) minimising the number of wavefronts
@@ -415,6 +470,8 @@ int assign_octet(const std::vector<std::vector<OEdge>>& rows, int D, int32_t (*t
 }
 
 } // namespace
+
+uint64_t ls_builtin_full_iters(uint64_t states);
 
 namespace {
 
@@ -556,6 +613,12 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
     plan->colour_cost_before = static_cast<uint64_t>(col.cost);
     anneal(col, sa_iters, 0x5eed0000ull + n * 131u + vindex, opts.cancel);
     if (opts.cancel != nullptr && *opts.cancel != 0) return false;
+    if (sa_iters >= ls_builtin_full_iters(n)) { // the full search only: the quick plan of a first batch skips it
+        uint64_t moves = 30000;
+        if (const char* env = std::getenv("SV_LS_ENDGAME_MOVES")) moves = std::strtoull(env, nullptr, 10);
+        endgame(col, moves, 0x5eed0000ull + n * 131u + vindex, opts.cancel);
+        if (opts.cancel != nullptr && *opts.cancel != 0) return false;
+    }
     plan->colour_cost_after = static_cast<uint64_t>(col.cost);
     plan->sa_iters = sa_iters;
 
@@ -713,8 +776,12 @@ bool ls_try_variant(const SvHostCsr& csr, const std::vector<float>& emis,
 
 } // namespace
 
+uint64_t ls_builtin_full_iters(uint64_t states) { return std::min<uint64_t>(2000000ull, 830ull * states); }
+
 uint64_t sv_ls_default_sa_iters(uint64_t states) {
-    uint64_t sa_iters = std::min<uint64_t>(8000000ull, 3300ull * states);
+    // annealing length of the FULL search; the min-conflicts end game that follows it does the rest (2 M + end game:
+    // 920 wavefronts per step and group on the synthetic 2405-state model, ideal 912; 8 M alone: 955, 40 M alone: 924)
+    uint64_t sa_iters = ls_builtin_full_iters(states);
     if (const char* env = std::getenv("SV_LS_SA_ITERS")) sa_iters = std::strtoull(env, nullptr, 10);
     return sa_iters;
 }

@@ -1851,10 +1851,40 @@ bool implicit_supported(sv_spec* s, SvPairDev* pd) {
 }
 } // namespace
 
+namespace {
+// K4c eligibility: level 2, chain + specials structure (K0, lazily), emission table fits one CTA's shared memory.
+bool chain_pair_supported(sv_spec* s) {
+    sv_model* m = s->m;
+    if (s->level != 2 || s->ondemand) return false;
+    if (m->chain_pair_state != 0) return m->chain_pair_state > 0;
+    m->chain_pair_state = -1;
+    if (!sv_model_ensure_chain(m)) return false;
+    const size_t smem = sv_chain_pair_smem(m->chain.threads, static_cast<int>(m->emits));
+    if (smem + 2048 > m->smem_optin) return false;
+    int per_sm = 0;
+    if (sv_chain_pair_prepare(m->chain.threads, m->chain.nonneg, smem, &per_sm) != 0) {
+        cudaGetLastError();
+        return false;
+    }
+    m->chain_pair_smem = smem;
+    m->chain_pair_ctas_per_sm = per_sm;
+    m->chain_pair_state = 1;
+    return true;
+}
+} // namespace
+
 extern "C" int sv_spec_set_run_mode(sv_spec* s, int mode) {
     SV_API_BEGIN
-    if (s == nullptr || (mode != SV_SPEC_RUN_AUTO && mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT))
+    if (s == nullptr || (mode != SV_SPEC_RUN_AUTO && mode != SV_SPEC_RUN_TABLE && mode != SV_SPEC_RUN_IMPLICIT &&
+                         mode != SV_SPEC_RUN_CHAIN))
         return sv_fail(SV_ERR_ARG, "sv_spec_set_run_mode: bad argument");
+    if (mode == SV_SPEC_RUN_CHAIN && s->level > 1) {
+        SV_CUDA(cudaSetDevice(s->m->device));
+        if (!chain_pair_supported(s))
+            return sv_fail(SV_ERR_UNSUPPORTED,
+                           "sv_spec_set_run_mode: chain run needs level 2, the chain + specials structure and an emission "
+                           "table that fits shared memory");
+    }
     if (mode == SV_SPEC_RUN_IMPLICIT && s->level > 1) {
         SV_CUDA(cudaSetDevice(s->m->device));
         SvPairDev pd;
@@ -1878,6 +1908,24 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
         return sv_fail(SV_ERR_ARG, "sv_spec_run_device: sequences live on another device");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SV_CUDA(cudaSetDevice(m->device));
+    // AUTO: chain + specials models run all their chunks in ONE persistent launch (K4c: identical bits, O(N) per chunk)
+    if (s->run_mode == SV_SPEC_RUN_CHAIN || s->run_mode == SV_SPEC_RUN_AUTO) {
+        const bool chain = seqs->dev.sym_bytes == 1 && chain_pair_supported(s);
+        if (!chain && s->run_mode == SV_SPEC_RUN_CHAIN)
+            return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_run: chain run needs level 2, the chain + specials structure, u8 symbols");
+        if (chain) {
+            // a private work-queue counter per launch, as in sv_viterbi_device: nothing else is shared between runs
+            unsigned* counter = m->d_counters + static_cast<size_t>(m->launch_seq++ % SV_COUNTER_RING) * 16;
+            SV_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), st));
+            const int64_t slots = static_cast<int64_t>(std::max(1, m->sm_count)) * std::max(1, m->chain_pair_ctas_per_sm);
+            const int grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(slots, static_cast<int64_t>(seqs->nseq))));
+            const int rc = sv_chain_pair_launch(m->chain.threads, m->chain.nonneg, m->chaindev, seqs->dev, d_out, d_best,
+                                                d_best_state, counter, grid, m->chain_pair_smem, st);
+            if (rc != 0) return sv_fail(SV_ERR_CUDA, std::string("chain pair kernel launch: ") + cudaGetErrorString(static_cast<cudaError_t>(rc)));
+            m->last_launches = 1;
+            return SV_OK;
+        }
+    }
     SvPairDev pd;
     // AUTO: the implicit run whenever the model is eligible (identical bits, ~5x faster, no table traffic)
     bool implicit = !s->ondemand && s->run_mode != SV_SPEC_RUN_TABLE && implicit_supported(s, &pd);

@@ -386,3 +386,147 @@ def test_implicit_run_unsupported(api):
         sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
     s = np.arange(9, dtype=np.uint64) % 20
     assert sp.run(s).shape == (60,)
+
+
+# ------------------------------------------------------------------ K4c: chain run ----
+CHAIN_MODELS = ["100", "200", "300", "400", "700", "1200", "2405"]
+
+
+@pytest.mark.parametrize("name", CHAIN_MODELS)
+def test_chain_run_equals_implicit_and_oracle(name, api, oracle, load_model):
+    """K4c (level 2 of a chain + specials model in one persistent launch, O(N) per chunk) against K4i (pinned to the
+    reference fixtures and the oracle above) and, on the smaller models, against the oracle itself: ragged lengths
+    1..7 (init only, tail only, odd / even chunking), all three CTA sizes (100/200: 128 threads, 300/400: 256,
+    700+: 512), 200.chmm and 400.chmm carry a negative weight (shuffle reduction instead of REDUX)."""
+    from spec_viterbi_b200 import _lib
+    hmm = load_model(name)
+    m = api.Model(hmm)
+    rng = np.random.default_rng(int(name))
+    seqs = [rng.integers(0, 20, L).astype(np.uint64) for L in (1, 2, 3, 4, 5, 6, 7, 50, 301, 1000, 8, 33)]
+    syms, offs = api.pack_sequences(seqs)
+    sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)  # nothing precomputed
+    sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+    exp, ebest, earg = sp.run_batch(syms, offs)
+    sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    got, best, arg = sp.run_batch(syms, offs)
+    assert m.last_launches() == 1
+    assert same_bits(got, exp)
+    assert np.array_equal(best, ebest) and np.array_equal(arg, earg)
+    # vectors only / best only; u8 symbols; AUTO picks the chain run
+    got2, _, _ = sp.run_batch(syms.astype(np.uint8), offs, want_best=False)
+    _, best2, arg2 = sp.run_batch(syms, offs, want_vectors=False)
+    assert same_bits(got2, exp) and np.array_equal(best2, ebest) and np.array_equal(arg2, earg)
+    sp.set_run_mode(_lib.SPEC_RUN_AUTO)
+    got3, _, _ = sp.run_batch(syms, offs)
+    assert m.last_launches() == 1 and same_bits(got3, exp)
+    if name in ("100", "200", "300"):
+        osp = oracle.spec(hmm, 2)
+        for k in (0, 1, 2, 3, 6, 8, 10):
+            assert same_bits(got[k], osp.run(seqs[k])), k
+
+
+def test_chain_run_reference_fixtures(api, load_model, load_seqs, golden):
+    """K4c against vectors produced by the reference's own GraphBLAS_spec_impl at level 2 (GraphBLAS_spec_impl.cpp:
+    50-97): 100.chmm / 200.chmm x emit_3_3500_20 and BASELINE.json configs[2] for real (2405.chmm x sequences 0 and 49
+    of emit_50_3500_20)."""
+    from spec_viterbi_b200 import _lib
+    for name in ("100", "200"):
+        m = api.Model(load_model(name))
+        sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)
+        sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+        out, best, arg = sp.run_batch(*api.pack_sequences(load_seqs("emit_3_3500_20")))
+        for k in range(3):
+            exp = golden[f"{name}_emit3_3500_seq{k}_spec2"]
+            assert same_bits(out[k], exp)
+            assert best[k] == exp.min() and arg[k] == exp.argmin()
+    m = api.Model(load_model("2405"))
+    sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)
+    sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    seqs = load_seqs("emit_50_3500_20")
+    out, best, arg = sp.run_batch(*api.pack_sequences([seqs[0], seqs[49]]))
+    for j, k in enumerate((0, 49)):
+        exp = golden[f"2405_emit50_3500_seq{k}_spec2"]
+        assert same_bits(out[j], exp), k
+        assert best[j] == exp.min() and arg[j] == exp.argmin()
+
+
+def test_chain_run_queue_and_covid(api, load_model, load_seqs):
+    """More sequences than resident CTAs (the persistent queue hands out the rest) and the ragged covid set on the
+    largest profile HMM, against K4i."""
+    from spec_viterbi_b200 import _lib
+    rng = np.random.default_rng(17)
+    m = api.Model(load_model("300"))
+    seqs = [rng.integers(0, 20, int(L)).astype(np.uint64) for L in rng.integers(1, 120, 1500)]
+    syms, offs = api.pack_sequences(seqs)
+    sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)
+    sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+    exp, ebest, earg = sp.run_batch(syms, offs)
+    sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    got, best, arg = sp.run_batch(syms, offs)
+    assert same_bits(got, exp) and np.array_equal(best, ebest) and np.array_equal(arg, earg)
+    m = api.Model(load_model("2405"))
+    syms, offs = api.pack_sequences(load_seqs("covid-19"))
+    sp = api.Spec(m, 2, tuple_begin=400, tuple_end=400)
+    sp.set_run_mode(_lib.SPEC_RUN_IMPLICIT)
+    exp, ebest, earg = sp.run_batch(syms, offs)
+    sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    got, best, arg = sp.run_batch(syms, offs)
+    assert same_bits(got, exp) and np.array_equal(best, ebest) and np.array_equal(arg, earg)
+
+
+def test_chain_run_variants(api, oracle):
+    """Chain structure with shuffled state numbering, broken chains, +inf band weights, non-uniform hub weights, a
+    hub -> C edge and a second start state, against the level-2 oracle; a model with no reachable state; and models
+    without the structure: CHAIN is refused, AUTO falls back to K4i / the table."""
+    from spec_viterbi_b200 import generators, _lib
+    rng = np.random.default_rng(3)
+    L = 700
+    n = L + 2
+    perm = rng.permutation(n)
+    N, C = 0, L + 1
+    src, dst, w = [N, C, N], [N, C, C], [0.3, 0.2, 4.5]
+    for k in range(1, L + 1):
+        src += [N, k, k]
+        dst += [k, N, C]
+        w += [float(rng.uniform(1, 9)), 1.0, 1.25]
+        if k < L and k % 211 != 0:
+            src += [k]
+            dst += [k + 1]
+            w += [float(rng.uniform(0.1, 3)) if k % 97 else np.inf]
+    src = perm[np.array(src)].astype(np.uint64)
+    dst = perm[np.array(dst)].astype(np.uint64)
+    em = rng.uniform(0.5, 7, (6, n)).astype(np.float32)
+    hmm = api.HMM(n, 6, src.size, src, dst, np.array(w, np.float32), em, 2,
+                  np.array([perm[N], perm[4]], np.uint64), np.array([0.0, 2.0], np.float32))
+    seqs = [rng.integers(0, 6, T).astype(np.uint64) for T in (1, 2, 3, 50, 401, 7, 1, 33, 120, 5, 64, 2)]
+    syms, offs = api.pack_sequences(seqs)
+    m = api.Model(hmm)
+    sp = api.Spec(m, 2, tuple_begin=36, tuple_end=36)
+    sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    out, best, arg = sp.run_batch(syms, offs)
+    osp = oracle.spec(hmm, 2)
+    for k in range(len(seqs)):
+        exp = osp.run(seqs[k])
+        assert same_bits(out[k], exp), k
+        assert best[k] == exp.min() and arg[k] == exp.argmin()
+    dead = api.HMM(n, 6, src.size, src, dst, np.array(w, np.float32), em, 0, np.zeros(0, np.uint64), np.zeros(0, np.float32))
+    sd = api.Spec(api.Model(dead), 2, tuple_begin=36, tuple_end=36)
+    sd.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    out, best, arg = sd.run_batch(syms, offs)
+    assert np.all(np.isposinf(out)) and np.all(np.isposinf(best)) and np.all(arg == -1)
+    # no chain structure
+    rnd = generators.random_hmm(states_num=130, seed=9)
+    mr = api.Model(rnd)
+    sr = api.Spec(mr, 2)
+    with pytest.raises(_lib.SvError):
+        sr.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    syms, offs = api.pack_sequences([rng.integers(0, 20, T).astype(np.uint64) for T in (1, 2, 9, 40)])
+    sr.set_run_mode(_lib.SPEC_RUN_TABLE)
+    exp, _, _ = sr.run_batch(syms, offs)
+    sr.set_run_mode(_lib.SPEC_RUN_AUTO)
+    got, _, _ = sr.run_batch(syms, offs)
+    assert same_bits(got, exp) and mr.last_launches() > 1
+    # level 3 of a chain model: CHAIN is level 2 only
+    s3 = api.Spec(api.Model(hmm), 3, tuple_begin=216, tuple_end=216)
+    with pytest.raises(_lib.SvError):
+        s3.set_run_mode(_lib.SPEC_RUN_CHAIN)

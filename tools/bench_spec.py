@@ -87,6 +87,34 @@ def main():
             prop = torch.cuda.get_device_properties(0)
             res["implicit_frac_of_fp32_issue"] = res["implicit_terms_per_s"] * 2.5 / (
                 prop.multi_processor_count * 128 * peaks.get("sm_max_mhz", 1965.0) * 1e6)
+            # K4c: chain + specials models, all chunks in ONE persistent launch, O(N) per chunk, bit-identical
+            try:
+                sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+                ct = []
+                for _ in range(5):
+                    t0 = time.perf_counter()
+                    cout, cbest, carg = sp.run_batch(syms, offs)
+                    ct.append((time.perf_counter() - t0) * 1e3)
+                res["run_ms_level2_chain"] = min(ct)
+                res["chain_bits_equal_table_run"] = bool(np.array_equal(cout.view(np.uint32), out.view(np.uint32)))
+                res["chain_launches"] = m.last_launches()
+                dsq = m.upload(syms.astype(np.uint8), offs)
+                import torch
+                d_out = torch.empty((len(seqs), n), dtype=torch.float32, device="cuda")
+                kt = []
+                for _ in range(5):
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    sp.run_device(dsq, d_out.data_ptr(), 0, 0, 0)
+                    torch.cuda.synchronize()
+                    kt.append((time.perf_counter() - t0) * 1e3)
+                res["run_ms_level2_chain_device_resident"] = min(kt)
+                res["chain_us_per_chunk"] = min(kt) * 1e3 / max(1, max((len(x) - 1) // 2 for x in seqs))
+                res["chain_state_updates_per_s"] = sum(len(x) for x in seqs) * n / (min(kt) * 1e-3)
+            except _lib.SvError as e:
+                res["run_ms_level2_chain"] = None
+                res["chain_unsupported"] = str(e)
+            sp.set_run_mode(_lib.SPEC_RUN_TABLE)
             # plain path on the same input for the honest comparison
             pt = []
             for _ in range(3):
