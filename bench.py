@@ -564,6 +564,38 @@ def run_b200(args):
             "timing": "wall clock around the synchronous sv_spec_create into a caller-owned table (every GPU holds "
                       "the whole table afterwards), min of 3, max over ranks; spec_with_ms = fresh sv_model_create + "
                       "sv_spec_create (what Viterbi_spec_impl::spec_with costs through the reference interface)"}
+        # BASELINE.json configs[2] for real: 2405.chmm x emit_50_3500_20, level-2 run through the C ABI with host buffers
+        # (wall clock, min of 5): K4c (chain + specials models: one persistent launch, O(N) per chunk) and K4i (chunks
+        # recomputed from the sparse factors, one launch per chunk); identical bits.  No table is built for either.
+        try:
+            gold = ROOT / "tests" / "golden"
+            hmm3 = api.read_HMM(str(gold / "models" / "2405.chmmb"))
+            seqs3 = api.read_emit_seq(str(gold / "seqs" / "emit_50_3500_20.essb"))
+            syms3, offs3 = api.pack_sequences(seqs3)
+            syms3 = syms3.astype(np.uint8)
+            m3 = api.Model(hmm3, device=local_rank)
+            E3 = int(hmm3.emit_num)
+            sp3 = api.Spec(m3, 2, _lib.SPEC_AUTO, E3 * E3, E3 * E3)  # empty tuple range: nothing precomputed
+            res3 = {}
+            for label, mode, reps in (("chain", _lib.SPEC_RUN_CHAIN, 5), ("implicit", _lib.SPEC_RUN_IMPLICIT, 2)):
+                sp3.set_run_mode(mode)
+                best_s = 1e30
+                for _ in range(reps + 1):
+                    t0 = time.perf_counter()
+                    o3, _, _ = sp3.run_batch(syms3, offs3)
+                    best_s = min(best_s, time.perf_counter() - t0)
+                res3[label] = (best_s, o3, int(m3.last_launches()))
+            line["spec_run"] = {
+                "config": "BASELINE.json configs[2]: 2405.chmm x emit_50_3500_20 (50 x 3500 symbols), level 2",
+                "run_ms": res3["chain"][0] * 1e3, "kernel": "sv_chain_pair_kernel (K4c)", "launches": res3["chain"][2],
+                "state_updates_per_s": float(len(syms3)) * hmm3.states_num / res3["chain"][0],
+                "implicit_run_ms": res3["implicit"][0] * 1e3, "implicit_launches": res3["implicit"][2],
+                "bits_equal": bool(np.array_equal(res3["chain"][1].view(np.uint32), res3["implicit"][1].view(np.uint32))),
+                "timing": "wall clock around sv_spec_run_batch_u8 (host symbols in, final vectors out), min of 5 / 2"}
+            sp3.close()
+            m3.close()
+        except Exception as e:  # the golden inputs are test data: a bench line without this leg is still valid
+            line["spec_run"] = {"unavailable": f"{type(e).__name__}: {e}"}
         if not args.no_cpu and world == 1:  # rank 0 at N = 1 only (the contract)
             line["cpu_baseline"] = cpu_port_baseline(hmm, syms, offs)
         emit_line(line)

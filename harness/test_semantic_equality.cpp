@@ -63,15 +63,28 @@ int main(int argc, char** argv) {
                 ++failures;
             }
         }
-        // level 2 again with the chunks recomputed from the sparse factors (K4i): same bits, no table reads
+        // level 2 again, every way a chunk can be applied (spec[1] runs in AUTO mode): the precomputed handlers (K4, the
+        // reference's GrB_mxm per chunk), the chunks recomputed from the sparse factors (K4i), and -- the shipped models
+        // all have the chain + specials structure -- the one-launch chain run (K4c): same bits
         if (spec.size() > 1) {
-            B200_spec_impl implicit(hmm, 2);
+            B200_spec_impl table(hmm, 2), implicit(hmm, 2), chain(hmm, 2);
+            table.set_run_mode(SV_SPEC_RUN_TABLE);
             implicit.set_run_mode(SV_SPEC_RUN_IMPLICIT);
-            for (const auto& sq : sequences)
-                if (!harness::bit_equal(spec[1]->run_Viterbi_spec(sq), implicit.run_Viterbi_spec(sq))) {
-                    std::cout << "MISMATCH implicit level-2 run " << f << "\n";
+            bool has_chain = true;
+            try {
+                chain.set_run_mode(SV_SPEC_RUN_CHAIN);
+            } catch (const std::exception&) {
+                has_chain = false; // not a chain + specials model
+            }
+            for (const auto& sq : sequences) {
+                const auto ref2 = table.run_Viterbi_spec(sq);
+                if (!harness::bit_equal(ref2, spec[1]->run_Viterbi_spec(sq)) ||
+                    !harness::bit_equal(ref2, implicit.run_Viterbi_spec(sq)) ||
+                    (has_chain && !harness::bit_equal(ref2, chain.run_Viterbi_spec(sq)))) {
+                    std::cout << "MISMATCH between level-2 run modes " << f << "\n";
                     ++failures;
                 }
+            }
         }
         // smallest model: the level-2 tables survive a save / attach round trip (not in the reference)
         if (&f == &files.front() && spec.size() > 1) {

@@ -305,6 +305,14 @@ int sv_k0_chain_check(uint64_t states, uint64_t emits, uint64_t trans, const uin
                       uint64_t nstart, const uint64_t* start_cols, const float* start_w,
                       const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]);
 
+/* The same for K4c, the level-2 run of a chain + specials model (SV_SPEC_RUN_CHAIN): first symbol, chunks of two
+ * symbols through the collapsed two-step paths, odd tail as one level-1 step, replayed on the host; to be compared
+ * with the level-2 semantics of GraphBLAS_spec_impl.cpp:15-36,50-97. */
+int sv_k0_chain_pair_check(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                           const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                           uint64_t nstart, const uint64_t* start_cols, const float* start_w,
+                           const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]);
+
 #ifdef __cplusplus
 }
 #endif

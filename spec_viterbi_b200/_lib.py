@@ -94,6 +94,8 @@ SIGNATURES = {
                                        C.c_uint64, u64p, f32p, u64p, C.c_uint64, f32p, u64p]),
     "sv_k0_chain_check": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
                                     C.c_uint64, u64p, f32p, u64p, C.c_uint64, f32p, u64p]),
+    "sv_k0_chain_pair_check": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
+                                         C.c_uint64, u64p, f32p, u64p, C.c_uint64, f32p, u64p]),
     "sv_multi_create": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, u64p, u64p, f32p, f32p,
                                   C.c_uint64, u64p, f32p, C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]),
     "sv_multi_destroy": (None, [vp]),

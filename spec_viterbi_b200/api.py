@@ -165,8 +165,9 @@ def k0_lockstep_check(hmm: "HMM", seq=None):
     return dict(zip(names, (int(x) for x in stats))), out
 
 
-def k0_chain_check(hmm: "HMM", seq=None):
-    """Host-only K0 diagnostic of the chain kernel: (stats dict, replayed final vector or None)."""
+def k0_chain_check(hmm: "HMM", seq=None, level: int = 1):
+    """Host-only K0 diagnostic of the chain kernel (level 1) or of K4c, the level-2 chain run (level 2):
+    (stats dict, replayed final vector or None)."""
     lib = L.lib()
     h = hmm.normalized()
     stats = np.zeros(8, np.uint64)
@@ -176,7 +177,7 @@ def k0_chain_check(hmm: "HMM", seq=None):
         s = np.ascontiguousarray(seq, np.uint64)
         out = np.empty(h.states_num, np.float32)
         sp, sl = _p(s, C.c_uint64), s.size
-    L.check(lib.sv_k0_chain_check(
+    L.check((lib.sv_k0_chain_pair_check if level == 2 else lib.sv_k0_chain_check)(
         h.states_num, h.emit_num, h.trans_num, _p(h.trans_rows, C.c_uint64), _p(h.trans_cols, C.c_uint64),
         _p(h.trans_probs, C.c_float), _p(h.emissions, C.c_float), h.non_zero_start_probs,
         _p(h.start_probabilities_cols, C.c_uint64), _p(h.start_probabilities, C.c_float),

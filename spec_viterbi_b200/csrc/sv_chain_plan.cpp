@@ -177,11 +177,11 @@ void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, c
 // broadcast, special rows through the chain minimum -- so that tests can check the transformation
 // against the oracle without a device.  stats = {valid, threads, chain states, specials, tmem cols,
 // nonneg, special 0, special 1}.
-extern "C" int sv_k0_chain_check(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
-                                 const uint64_t* trans_dst, const float* trans_w, const float* emissions,
-                                 uint64_t nstart, const uint64_t* start_cols, const float* start_w,
-                                 const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]) {
-    SV_API_BEGIN
+namespace {
+int chain_check_impl(int level, uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                     const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                     uint64_t nstart, const uint64_t* start_cols, const float* start_w,
+                     const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]) {
     if (states == 0 || emits == 0 || stats == nullptr) return sv_fail(SV_ERR_ARG, "sv_k0_chain_check: bad argument");
     SvHostCsr csr;
     {
@@ -230,8 +230,54 @@ extern "C" int sv_k0_chain_check(uint64_t states, uint64_t emits, uint64_t trans
     const int np = p.n_pos;
     std::vector<float> v(np, kInf), nv(np, kInf);
     float vs[SV_CHAIN_NSP] = {kInf, kInf}, nvs[SV_CHAIN_NSP];
-    for (uint64_t t = 0; t < len; ++t) {
+    for (uint64_t t = 0; t < len; ++t)
         if (seq[t] >= emits) return sv_fail(SV_ERR_ARG, "symbol >= emit_num");
+    for (uint64_t t = 0; t < len; ++t) {
+        if (level == 2 && t >= 1 && len - t >= 2) {
+            // K4c (sv_spec_chain.cu): one level-2 chunk (a, b) = the min over the two-step paths i <- j <- k of
+            // fl(fl(M_b[i][j] + M_a[j][k]) + v[k]), with the paths through the dense rows collapsed onto the chain
+            // minimum (GraphBLAS_spec_impl.cpp:15-36,69-79 are what it must reproduce)
+            const float* ea = &p.emis_p[seq[t] * np];
+            const float* eb = &p.emis_p[seq[t + 1] * np];
+            float mm = kInf;
+            for (int k = 0; k < np; ++k) mm = std::fmin(mm, v[k]);
+            auto at = [&](int k) { return k >= 0 ? v[k] : kInf; };
+            float Ua[SV_CHAIN_NSP], Ub[SV_CHAIN_NSP], Sa[SV_CHAIN_NSP][SV_CHAIN_NSP], Sb[SV_CHAIN_NSP][SV_CHAIN_NSP];
+            for (int x = 0; x < SV_CHAIN_NSP; ++x) {
+                const float xa = p.emis_s[x * emits + seq[t]], xb = p.emis_s[x * emits + seq[t + 1]];
+                Ua[x] = xa + p.u[x];
+                Ub[x] = xb + p.u[x];
+                for (int y = 0; y < SV_CHAIN_NSP; ++y) {
+                    Sa[x][y] = xa + p.ss[x][y];
+                    Sb[x][y] = xb + p.ss[x][y];
+                }
+            }
+            for (int x = 0; x < SV_CHAIN_NSP; ++x) nvs[x] = kInf;
+            for (int k = 0; k < np; ++k) {
+                const float Pa = ea[k] + p.w_pred[k], Ha = ea[k] + p.w_hub[k];
+                const float Pb = eb[k] + p.w_pred[k], Hb = eb[k] + p.w_hub[k];
+                const float Pam1 = k > 0 ? ea[k - 1] + p.w_pred[k - 1] : kInf;
+                const float Ham1 = k > 0 ? ea[k - 1] + p.w_hub[k - 1] : kInf;
+                float x = (Pb + Pam1) + at(k - 2);
+                x = std::fmin(x, (Pb + Ham1) + vs[0]);
+                x = std::fmin(x, (Hb + Ua[0]) + mm);
+                for (int y = 0; y < SV_CHAIN_NSP; ++y) x = std::fmin(x, (Hb + Sa[0][y]) + vs[y]);
+                nv[k] = x;
+                for (int y = 0; y < SV_CHAIN_NSP; ++y) {
+                    nvs[y] = std::fmin(nvs[y], (Ub[y] + Pa) + at(k - 1));
+                    nvs[y] = std::fmin(nvs[y], (Ub[y] + Ha) + vs[0]);
+                }
+            }
+            for (int x = 0; x < SV_CHAIN_NSP; ++x)
+                for (int y = 0; y < SV_CHAIN_NSP; ++y) {
+                    nvs[x] = std::fmin(nvs[x], (Sb[x][y] + Ua[y]) + mm);
+                    for (int z = 0; z < SV_CHAIN_NSP; ++z) nvs[x] = std::fmin(nvs[x], (Sb[x][y] + Sa[y][z]) + vs[z]);
+                }
+            v.swap(nv);
+            for (int x = 0; x < SV_CHAIN_NSP; ++x) vs[x] = nvs[x];
+            ++t; // two symbols consumed
+            continue;
+        }
         const float* em = &p.emis_p[seq[t] * np];
         float mm = kInf; // min over the chain of the PREVIOUS step's scores
         for (int k = 0; k < np; ++k) mm = std::fmin(mm, v[k]);
@@ -263,5 +309,28 @@ extern "C" int sv_k0_chain_check(uint64_t states, uint64_t emits, uint64_t trans
         if (p.orig_of_pos[k] >= 0) out[p.orig_of_pos[k]] = v[k];
     for (int s = 0; s < p.nsp; ++s) out[p.special[s]] = vs[s];
     return SV_OK;
+}
+} // namespace
+
+extern "C" int sv_k0_chain_check(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                                 const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                                 uint64_t nstart, const uint64_t* start_cols, const float* start_w,
+                                 const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]) {
+    SV_API_BEGIN
+    return chain_check_impl(1, states, emits, trans, trans_src, trans_dst, trans_w, emissions, nstart, start_cols, start_w, seq,
+                            len, out, stats);
+    SV_API_END
+}
+
+// The same for K4c (sv_spec_chain.cu): replays the level-2 specialised run -- first symbol, chunks of two symbols through
+// the collapsed two-step paths, odd tail as one level-1 step -- so that the algebra can be checked against the level-2
+// oracle without a device.
+extern "C" int sv_k0_chain_pair_check(uint64_t states, uint64_t emits, uint64_t trans, const uint64_t* trans_src,
+                                      const uint64_t* trans_dst, const float* trans_w, const float* emissions,
+                                      uint64_t nstart, const uint64_t* start_cols, const float* start_w,
+                                      const uint64_t* seq, uint64_t len, float* out, uint64_t stats[8]) {
+    SV_API_BEGIN
+    return chain_check_impl(2, states, emits, trans, trans_src, trans_dst, trans_w, emissions, nstart, start_cols, start_w, seq,
+                            len, out, stats);
     SV_API_END
 }

@@ -210,7 +210,9 @@ class B200_spec_impl : public Viterbi_spec_impl {
 
     // Not in the reference: how a level-2 chunk is applied (sv_spec_set_run_mode) -- SV_SPEC_RUN_TABLE reads the
     // precomputed handler (the reference's GrB_mxm per chunk), SV_SPEC_RUN_IMPLICIT recomputes the entries from
-    // the sparse factors (bit-identical, no table traffic).  Throws if the model / level is not eligible.
+    // the sparse factors (bit-identical, no table traffic), SV_SPEC_RUN_CHAIN runs level 2 of a chain + specials
+    // model (every profile HMM the reference ships) in one persistent launch at O(N) per chunk (bit-identical);
+    // SV_SPEC_RUN_AUTO (the default) picks the fastest eligible one.  Throws if the model / level is not eligible.
     void set_run_mode(int mode) {
         if (spec == nullptr) throw std::runtime_error("B200_spec_impl: spec_with(hmm) must be called first");
         b200_detail::check(sv_spec_set_run_mode(spec, mode), "sv_spec_set_run_mode");

@@ -60,6 +60,37 @@ def test_chain_plan_profile_models(name, api, oracle, load_model, load_seqs):
         assert same_bits(out, oracle.plain(hmm, seq))
 
 
+@pytest.mark.parametrize("name", ["100", "200", "300"])
+def test_chain_pair_replay_vs_oracle(name, api, oracle, load_model):
+    """K4c's algebra (level-2 chunks through the collapsed two-step paths, sv_k0_chain_pair_check) replayed on the host
+    against the level-2 oracle: lengths 1..8 cover init only, tail only and odd / even chunking; 200.chmm carries a
+    negative weight."""
+    hmm = load_model(name)
+    osp = oracle.spec(hmm, 2)
+    rng = np.random.default_rng(int(name))
+    for T in (1, 2, 3, 4, 5, 6, 7, 8, 61, 200):
+        seq = rng.integers(0, 20, T).astype(np.uint64)
+        stats, out = api.k0_chain_check(hmm, seq, level=2)
+        assert stats["valid"] == 1
+        assert same_bits(out, osp.run(seq)), T
+
+
+def test_chain_pair_replay_config3_fixture(api, load_model, load_seqs, golden):
+    """BASELINE.json configs[2] without a device: the K4c algebra replayed on the host reproduces, bit for bit, the
+    vectors the reference's own GraphBLAS_spec_impl produced for 2405.chmm x emit_50_3500_20 at level 2
+    (tools/make_fixtures.py --config3), and the level-2 fixtures of 100.chmm / 200.chmm."""
+    hmm = load_model("2405")
+    seqs = load_seqs("emit_50_3500_20")
+    for k in (0, 49):
+        stats, out = api.k0_chain_check(hmm, seqs[k], level=2)
+        assert stats["valid"] == 1 and same_bits(out, golden[f"2405_emit50_3500_seq{k}_spec2"]), k
+    for name in ("100", "200"):
+        hmm = load_model(name)
+        for k, seq in enumerate(load_seqs("emit_3_3500_20")):
+            _, out = api.k0_chain_check(hmm, seq, level=2)
+            assert same_bits(out, golden[f"{name}_emit3_3500_seq{k}_spec2"]), (name, k)
+
+
 def test_chain_plan_rejects_other_structures(api):
     from spec_viterbi_b200 import generators
     # random sparse graph: no specials
