@@ -419,15 +419,107 @@ int slot_wavefronts(const int32_t (*tab)[8], int slot, const std::vector<std::ve
     return worst; // 0 for an empty slot
 }
 
+// Exact start for assign_octet: the edges of an octet form a bipartite multigraph lanes x colours (colour = source
+// position mod 8 = bank group); a proper edge colouring with `ncol` = max degree colours exists and is found by
+// alternating-path recolouring (Koenig).  A colour class is a slot in which every lane reads at most once and every
+// bank group is hit at most once: conflict free.  When the colouring search left an over-full (octet, colour) cell,
+// ncol > D and the classes beyond D are folded into the first D slots (least conflict first); the caller's local search
+// then only has those few edges to improve.  Returns false (tab untouched) when two lanes read the same position --
+// they could share a slot, which the plain edge colouring does not model; the greedy start handles that case.
+bool koenig_start(const std::vector<std::vector<OEdge>>& rows, int D, int32_t (*tab)[8]) {
+    struct E {
+        int l, c, k, col;
+    };
+    std::vector<E> es;
+    int dl[8] = {0}, dc[8] = {0};
+    for (int l = 0; l < 8; ++l)
+        for (size_t k = 0; k < rows[l].size(); ++k) {
+            for (const E& o : es)
+                if (rows[o.l][o.k].pos == rows[l][k].pos) return false;
+            es.push_back(E{l, static_cast<int>(rows[l][k].pos & 7u), static_cast<int>(k), -1});
+            ++dl[l];
+            ++dc[rows[l][k].pos & 7u];
+        }
+    int ncol = D;
+    for (int i = 0; i < 8; ++i) ncol = std::max(ncol, std::max(dl[i], dc[i]));
+    if (ncol > 16) return false;
+    int at_l[8][16], at_c[8][16]; // edge id holding colour x at lane l / colour node c, -1 = free
+    for (int i = 0; i < 8; ++i)
+        for (int x = 0; x < 16; ++x) at_l[i][x] = at_c[i][x] = -1;
+    for (int e = 0; e < static_cast<int>(es.size()); ++e) {
+        int a = 0, b = 0;
+        while (at_l[es[e].l][a] >= 0) ++a; // free at the lane
+        while (at_c[es[e].c][b] >= 0) ++b; // free at the colour node
+        if (a != b) {
+            // alternating a / b path from the colour node: it cannot reach the lane (which has no a-edge)
+            std::vector<int> path;
+            bool right = true;
+            int node = es[e].c, want = a, other = b;
+            for (;;) {
+                const int f = right ? at_c[node][want] : at_l[node][want];
+                if (f < 0) break;
+                path.push_back(f);
+                node = right ? es[f].l : es[f].c;
+                right = !right;
+                std::swap(want, other);
+            }
+            for (const int f : path) {
+                at_l[es[f].l][es[f].col] = -1;
+                at_c[es[f].c][es[f].col] = -1;
+            }
+            for (const int f : path) {
+                es[f].col = es[f].col == a ? b : a;
+                at_l[es[f].l][es[f].col] = f;
+                at_c[es[f].c][es[f].col] = f;
+            }
+        }
+        es[e].col = a;
+        at_l[es[e].l][a] = e;
+        at_c[es[e].c][a] = e;
+    }
+    for (int l = 0; l < 8; ++l)
+        for (int x = 0; x < 8; ++x) tab[l][x] = -1;
+    for (const E& e : es)
+        if (e.col < D) tab[e.l][e.col] = e.k;
+    for (const E& e : es) { // fold the classes beyond D
+        if (e.col < D) continue;
+        int best_s = -1, best_c = 1 << 30;
+        for (int x = 0; x < D; ++x) {
+            if (tab[e.l][x] >= 0) continue;
+            const int before = slot_wavefronts(tab, x, rows);
+            tab[e.l][x] = e.k;
+            const int after = slot_wavefronts(tab, x, rows);
+            tab[e.l][x] = -1;
+            const int c = (after - std::max(before, 1)) * 16 + before;
+            if (c < best_c) {
+                best_c = c;
+                best_s = x;
+            }
+        }
+        if (best_s < 0) return false; // cannot happen: the lane has at most D edges
+        tab[e.l][best_s] = e.k;
+    }
+    return true;
+}
+
 // tab[l][slot] = index into rows[l] or -1.  Returns total wavefronts (empty slots cost 1: the
 // padded loads still issue).
 int assign_octet(const std::vector<std::vector<OEdge>>& rows, int D, int32_t (*tab)[8], Rng& rng) {
     for (int l = 0; l < 8; ++l)
         for (int s = 0; s < 8; ++s) tab[l][s] = -1;
+    static const bool kExact = [] { const char* e = std::getenv("SV_LS_SLOT_EXACT"); return !(e && e[0] == '0'); }();
+    bool started = false;
+    if (kExact && D >= 1) {
+        int32_t t2[8][8];
+        if (koenig_start(rows, D, t2)) {
+            std::memcpy(tab, t2, sizeof(t2));
+            started = true;
+        }
+    }
     // greedy: lanes with most edges first; each edge to the free slot with the least conflict
     int order[8] = {0, 1, 2, 3, 4, 5, 6, 7};
     std::stable_sort(order, order + 8, [&](int a, int b) { return rows[a].size() > rows[b].size(); });
-    for (int oi = 0; oi < 8; ++oi) {
+    for (int oi = 0; oi < 8 && !started; ++oi) {
         const int l = order[oi];
         for (size_t k = 0; k < rows[l].size(); ++k) {
             int best_s = -1, best_c = 1 << 30;
@@ -453,7 +545,27 @@ int assign_octet(const std::vector<std::vector<OEdge>>& rows, int D, int32_t (*t
     };
     int cur = total();
     if (cur == D || D < 2) return cur;
-    for (int it = 0; it < 4000 && cur > D; ++it) {
+    // lower bound: D slots, plus the overflow of the fullest colour (its distinct sources beyond one per slot; overflows of
+    // DIFFERENT colours can share a slot's extra wavefronts, so they do not add up)
+    int lb = D;
+    {
+        uint32_t seen[64];
+        int ns = 0, cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int l = 0; l < 8; ++l)
+            for (const OEdge& e : rows[l]) {
+                bool dup = false;
+                for (int a = 0; a < ns; ++a) dup |= seen[a] == e.pos;
+                if (dup || ns == 64) continue;
+                seen[ns++] = e.pos;
+                ++cnt[e.pos & 7u];
+            }
+        int over = 0;
+        for (int c = 0; c < 8; ++c) over = std::max(over, cnt[c] - D);
+        lb += over;
+    }
+    if (cur <= lb) return cur;
+    static const int kSlotIters = [] { const char* e = std::getenv("SV_LS_SLOT_ITERS"); return e ? std::atoi(e) : 4000; }();
+    for (int it = 0; it < kSlotIters && cur > lb; ++it) {
         const int l = static_cast<int>(rng.below(8));
         const int s1 = static_cast<int>(rng.below(D)), s2 = static_cast<int>(rng.below(D));
         if (s1 == s2 || (tab[l][s1] < 0 && tab[l][s2] < 0)) continue;

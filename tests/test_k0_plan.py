@@ -153,7 +153,7 @@ def test_quick_plan_is_fast_and_exact(api, oracle, monkeypatch):
     from spec_viterbi_b200 import generators
     hmm = generators.random_hmm(states_num=2405, seed=2405)
     seq = np.random.default_rng(1).integers(0, 20, 60).astype(np.uint64)
-    monkeypatch.setenv("SV_LS_SA_ITERS", str(60 * 2405))
+    monkeypatch.setenv("SV_LS_SA_ITERS", str(20 * 2405))  # the quick search of sv_model_ensure_ls
     t0 = time.perf_counter()
     stats, out = api.k0_lockstep_check(hmm, seq)
     dt = time.perf_counter() - t0
