@@ -215,7 +215,12 @@ enum {
  * tuple in [tuple_begin, tuple_end) (pass 0, 0 for all emits^level tuples).  Tuple index =
  * sum_j k_j * emits^(level-j), k_1 = first consumed symbol.  If d_table is not NULL it is a device
  * buffer the caller owns and handler `tuple_begin` is written at d_table[0] (so it needs
- * (tuple_end-tuple_begin)*states*states floats); otherwise the table is allocated internally. */
+ * (tuple_end-tuple_begin)*states*states floats); otherwise the table is allocated internally.
+ * Deferred table: with method AUTO, level 2, all tuples and no caller buffer, a model with the chain + specials
+ * structure gets its table on FIRST USE (SV_SPEC_RUN_TABLE, sv_spec_table, sv_spec_get_handler, sv_spec_save) instead
+ * of here, because its default run (SV_SPEC_RUN_CHAIN) never reads it: spec_with then costs a model upload and
+ * 4*states^2*emits^2 bytes of device memory stay free.  SV_SPEC_LAZY_TABLE=0 in the environment, or any explicit
+ * method, builds it here as the reference's spec_with does (GraphBLAS_spec_impl.cpp:168-181). */
 int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t tuple_begin,
                    uint64_t tuple_end, float* d_table, void* stream, sv_spec** out);
 void sv_spec_destroy(sv_spec* s);

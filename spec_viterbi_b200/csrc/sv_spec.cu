@@ -32,6 +32,11 @@ struct sv_spec {
     float* d_table = nullptr; // [(t_end-t_begin)][n][n]
     uint64_t table_first = 0; // tuple index stored at d_table[0]
     bool owns_table = false;
+    // Level 2 of a chain + specials model in AUTO mode runs without the table (K4c), so the table is built by the first
+    // call that needs it (SV_SPEC_RUN_TABLE, sv_spec_table, sv_spec_get_handler, sv_spec_save) instead of by
+    // sv_spec_create: spec_with costs a model upload, and 4 N^2 emits^2 bytes (9.27 GB for 2405.chmm) stay free.
+    bool deferred = false;
+    void* stream_at_create = nullptr;
     int method = SV_SPEC_SPARSE_LHS;
     int run_mode = SV_SPEC_RUN_AUTO;  // AUTO: K4i (level-2 chunks recomputed from the sparse factors) when eligible, else K4
     cudaEvent_t ev_done = nullptr;    // end of the last run on this spec: runs share d_v and serialise on it
@@ -1486,6 +1491,53 @@ int build_dense_level2(sv_model* m, uint64_t tb, uint64_t te, float* dst, cudaSt
 
 } // namespace
 
+namespace {
+// K4c eligibility of a MODEL at level 2: chain + specials structure (K0, lazily), emission table fits one CTA's shared memory.
+bool chain_pair_model_ok(sv_model* m) {
+    if (m->chain_pair_state != 0) return m->chain_pair_state > 0;
+    m->chain_pair_state = -1;
+    if (!sv_model_ensure_chain(m)) return false;
+    const size_t smem = sv_chain_pair_smem(m->chain.threads, static_cast<int>(m->emits));
+    if (smem + 2048 > m->smem_optin) return false;
+    int per_sm = 0;
+    if (sv_chain_pair_prepare(m->chain.threads, m->chain.nonneg, smem, &per_sm) != 0) {
+        cudaGetLastError();
+        return false;
+    }
+    m->chain_pair_smem = smem;
+    m->chain_pair_ctas_per_sm = per_sm;
+    m->chain_pair_state = 1;
+    return true;
+}
+
+// Builds a deferred level-2 table now (see sv_spec::deferred).
+int ensure_table(sv_spec* s) {
+    if (!s->deferred) return SV_OK;
+    sv_model* m = s->m;
+    SV_CUDA(cudaSetDevice(m->device));
+    const size_t mat = static_cast<size_t>(m->n) * m->n;
+    if (cudaMalloc(&s->d_table, s->ntuples * mat * sizeof(float)) != cudaSuccess) {
+        cudaGetLastError();
+        s->d_table = nullptr;
+        return sv_fail(SV_ERR_MEMORY, "sv_spec: handler table does not fit device memory");
+    }
+    s->owns_table = true;
+    cudaStream_t st = static_cast<cudaStream_t>(s->stream_at_create);
+    SvPairDev pairdev;
+    int rc = s->method == SV_SPEC_PAIR_ROWS && pair_prepare(m, &pairdev) ? build_pair_level2(m, pairdev, 0, s->ntuples, s->d_table, st)
+                                                                        : build_sparse(m, s->level, 0, s->ntuples, s->d_table, st);
+    if (rc == SV_OK && cudaStreamSynchronize(st) != cudaSuccess) rc = sv_fail(SV_ERR_CUDA, "sv_spec: precompute failed");
+    if (rc != SV_OK) {
+        cudaFree(s->d_table);
+        s->d_table = nullptr;
+        s->owns_table = false;
+        return rc;
+    }
+    s->deferred = false;
+    return SV_OK;
+}
+} // namespace
+
 extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t tuple_begin,
                               uint64_t tuple_end, float* d_table, void* stream, sv_spec** out) {
     SV_API_BEGIN
@@ -1517,6 +1569,13 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
             return sv_fail(SV_ERR_ARG, "sv_spec_create: the on-demand mode has no level-L table (no tuple shards, no caller table)");
         }
     }
+    // AUTO, the whole level-2 table, library-owned, chain + specials model: the run does not read it (K4c) -- defer it
+    static const bool lazy_on = [] {
+        const char* e = std::getenv("SV_SPEC_LAZY_TABLE");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    const bool defer = lazy_on && method == SV_SPEC_AUTO && level == 2 && d_table == nullptr && tuple_begin == 0 &&
+                       tuple_end == ntuples && chain_pair_model_ok(m);
     if (method == SV_SPEC_AUTO) method = (level == 2 && pair_prepare(m, &pairdev)) ? SV_SPEC_PAIR_ROWS : SV_SPEC_SPARSE_LHS;
     if (method != SV_SPEC_SPARSE_LHS && method != SV_SPEC_DENSE_GEMM && method != SV_SPEC_PAIR_ROWS && method != SV_SPEC_ONDEMAND)
         return sv_fail(SV_ERR_ARG, "sv_spec_create: unknown method");
@@ -1546,6 +1605,14 @@ extern "C" int sv_spec_create(sv_model* m, uint64_t level, int method, uint64_t 
             sv_spec_destroy(s);
             return rc;
         }
+        *out = s;
+        return SV_OK;
+    }
+    s->stream_at_create = stream;
+    if (defer) {
+        s->table_first = s->t_begin = 0;
+        s->t_end = ntuples; // the logical range; the handlers appear on first use (ensure_table)
+        s->deferred = true;
         *out = s;
         return SV_OK;
     }
@@ -1605,7 +1672,7 @@ extern "C" int sv_spec_set_range(sv_spec* s, float* d_table, uint64_t table_firs
     if (s == nullptr || tuple_begin > tuple_end || tuple_end > s->ntuples || tuple_begin < table_first)
         return sv_fail(SV_ERR_ARG, "sv_spec_set_range: bad argument (need table_first <= tuple_begin <= tuple_end <= emits^level)");
     if (s->level < 2) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: level 1 has no handler table");
-    if (s->owns_table) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: table is library-owned");
+    if (s->owns_table || s->deferred) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: table is library-owned");
     if (d_table == nullptr && tuple_end > tuple_begin) return sv_fail(SV_ERR_ARG, "sv_spec_set_range: NULL table");
     s->d_table = d_table;
     s->table_first = table_first;
@@ -1617,6 +1684,11 @@ extern "C" int sv_spec_set_range(sv_spec* s, float* d_table, uint64_t table_firs
 
 extern "C" float* sv_spec_table(const sv_spec* s, uint64_t* tuple_begin, uint64_t* tuple_end) {
     if (s == nullptr) return nullptr;
+    try {
+        if (ensure_table(const_cast<sv_spec*>(s)) != SV_OK) return nullptr; // deferred level-2 table: built on first use
+    } catch (...) {
+        return nullptr;
+    }
     if (tuple_begin) *tuple_begin = s->t_begin;
     if (tuple_end) *tuple_end = s->t_end;
     return s->d_table;
@@ -1627,6 +1699,7 @@ extern "C" int sv_spec_get_handler(const sv_spec* s, uint64_t tuple_index, float
     if (s == nullptr || out == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_get_handler: NULL");
     if (s->level < 2 || tuple_index < s->t_begin || tuple_index >= s->t_end)
         return sv_fail(SV_ERR_ARG, "sv_spec_get_handler: tuple not in the table");
+    if (const int rc = ensure_table(const_cast<sv_spec*>(s)); rc != SV_OK) return rc;
     const size_t mat = static_cast<size_t>(s->m->n) * s->m->n;
     SV_CUDA(cudaSetDevice(s->m->device));
     SV_CUDA(cudaMemcpy(out, s->d_table + (tuple_index - s->table_first) * mat, mat * sizeof(float),
@@ -1696,6 +1769,7 @@ extern "C" int sv_spec_save(const sv_spec* s, const char* path) {
     SV_API_BEGIN
     if (s == nullptr || path == nullptr) return sv_fail(SV_ERR_ARG, "sv_spec_save: NULL");
     if (s->level < 2) return sv_fail(SV_ERR_ARG, "sv_spec_save: level 1 has no handler table (K2 forms E+T' on the fly)");
+    if (const int rc = ensure_table(const_cast<sv_spec*>(s)); rc != SV_OK) return rc; // deferred level-2 table
     const sv_model* m = s->m;
     SV_CUDA(cudaSetDevice(m->device));
     SV_CUDA(cudaDeviceSynchronize()); // the table may still be under construction on a caller's stream
@@ -1854,22 +1928,8 @@ bool implicit_supported(sv_spec* s, SvPairDev* pd) {
 namespace {
 // K4c eligibility: level 2, chain + specials structure (K0, lazily), emission table fits one CTA's shared memory.
 bool chain_pair_supported(sv_spec* s) {
-    sv_model* m = s->m;
     if (s->level != 2 || s->ondemand) return false;
-    if (m->chain_pair_state != 0) return m->chain_pair_state > 0;
-    m->chain_pair_state = -1;
-    if (!sv_model_ensure_chain(m)) return false;
-    const size_t smem = sv_chain_pair_smem(m->chain.threads, static_cast<int>(m->emits));
-    if (smem + 2048 > m->smem_optin) return false;
-    int per_sm = 0;
-    if (sv_chain_pair_prepare(m->chain.threads, m->chain.nonneg, smem, &per_sm) != 0) {
-        cudaGetLastError();
-        return false;
-    }
-    m->chain_pair_smem = smem;
-    m->chain_pair_ctas_per_sm = per_sm;
-    m->chain_pair_state = 1;
-    return true;
+    return chain_pair_model_ok(s->m);
 }
 } // namespace
 
@@ -1932,6 +1992,8 @@ extern "C" int sv_spec_run_device(sv_spec* s, const sv_seqs* seqs, float* d_out,
     if (s->run_mode == SV_SPEC_RUN_IMPLICIT && !implicit)
         return sv_fail(SV_ERR_UNSUPPORTED, "sv_spec_run: implicit run needs level 2 and at most 4 dense rows");
     if (!implicit) cudaGetLastError();
+    if (!implicit && !s->ondemand)
+        if (const int rc = ensure_table(s); rc != SV_OK) return rc; // deferred level-2 table: the table run needs it
     if (!implicit && !s->ondemand && (s->t_begin != 0 || s->t_end != s->ntuples))
         return sv_fail(SV_ERR_ARG, "sv_spec_run: the handler table is not complete on this device");
     // runs on one spec share its state vectors: order this run after the previous one, whatever its stream

@@ -530,3 +530,38 @@ def test_chain_run_variants(api, oracle):
     s3 = api.Spec(api.Model(hmm), 3, tuple_begin=216, tuple_end=216)
     with pytest.raises(_lib.SvError):
         s3.set_run_mode(_lib.SPEC_RUN_CHAIN)
+
+
+def test_deferred_level2_table(api, oracle, load_model):
+    """spec_with at level 2 of a chain + specials model (AUTO) defers the handler table -- the run (K4c) does not read it:
+    no device memory is taken until something needs the handlers (the table run, sv_spec_get_handler, sv_spec_table,
+    sv_spec_save), and what is then built is the same table."""
+    import torch
+    from spec_viterbi_b200 import _lib
+    hmm = load_model("1200")
+    m = api.Model(hmm)
+    n = hmm.states_num
+    table_bytes = 400 * n * n * 4
+    rng = np.random.default_rng(2)
+    syms, offs = api.pack_sequences([rng.integers(0, 20, T).astype(np.uint64) for T in (1, 2, 7, 40, 301)])
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    sp = api.Spec(m, 2)                                   # AUTO: deferred
+    got, best, arg = sp.run_batch(syms, offs)             # K4c
+    assert m.last_launches() == 1
+    assert free0 - torch.cuda.mem_get_info()[0] < table_bytes // 4
+    sp.set_run_mode(_lib.SPEC_RUN_TABLE)                  # the table run builds it
+    exp, ebest, earg = sp.run_batch(syms, offs)
+    assert free0 - torch.cuda.mem_get_info()[0] >= table_bytes
+    assert same_bits(got, exp) and np.array_equal(best, ebest) and np.array_equal(arg, earg)
+    ptr, tb, te = sp.table()
+    assert ptr and (tb, te) == (0, 400)
+    sp.close()
+    # get_handler on a deferred spec; an explicit method is never deferred
+    hmm = load_model("100")
+    m = api.Model(hmm)
+    lazy = api.Spec(m, 2)
+    eager = api.Spec(m, 2, _lib.SPEC_PAIR_ROWS)
+    osp = oracle.spec(hmm, 2)
+    for t in (0, 57, 399):
+        assert same_bits(lazy.handler(t), osp.handler(t)) and same_bits(eager.handler(t), osp.handler(t))
