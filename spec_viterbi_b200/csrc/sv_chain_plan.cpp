@@ -157,9 +157,16 @@ void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, c
         p.start_p[k] = start[x];
         for (uint64_t e = 0; e < emits; ++e) p.emis_p[e * p.n_pos + k] = emis[e * n + x];
     }
-    p.emis_s.assign(static_cast<size_t>(SV_CHAIN_NSP) * emits, 0.f);
+    // rows 0 .. NSP-1: emissions of the special states; row NSP: min over the chain of fl(E[o][p] + w_hub[p]), the smallest
+    // level-1 entry of the hub column per symbol -- K4c folds "special row <- chain state p <- hub" through it (monotonicity)
+    p.emis_s.assign(static_cast<size_t>(SV_CHAIN_NSP + 1) * emits, 0.f);
     for (int a = 0; a < p.nsp; ++a)
         for (uint64_t e = 0; e < emits; ++e) p.emis_s[a * emits + e] = emis[e * n + sp[a]];
+    for (uint64_t e = 0; e < emits; ++e) {
+        float mh = kInf;
+        for (int k = 0; k < p.n_pos; ++k) mh = std::fmin(mh, p.emis_p[e * p.n_pos + k] + p.w_hub[k]);
+        p.emis_s[static_cast<size_t>(SV_CHAIN_NSP) * emits + e] = mh;
+    }
     {
         auto ok = [](float x) { return !(x < 0.0f) && x == x; };
         bool nn = true;

@@ -226,7 +226,7 @@ struct SvChainPlan {
     float start_s[SV_CHAIN_NSP];
     std::vector<float> w_pred, w_hub;               // [n_pos] weight of (p-1) -> p and of special 0 -> p
     std::vector<float> emis_p, start_p;             // [emits][n_pos], [n_pos]
-    std::vector<float> emis_s;                      // [NSP][emits]
+    std::vector<float> emis_s;                      // [NSP + 1][emits]: special states, then min_p fl(E[o][p] + w_hub[p])
     std::vector<int32_t> orig_of_pos;               // [n_pos] original state, -1 = padding
 };
 

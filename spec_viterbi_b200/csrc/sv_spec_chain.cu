@@ -16,9 +16,10 @@
 //
 //     min_k fl( fl(M_b[i][hub] + fl(E_a[hub] + u_hub)) + v[k] ) = fl( fl(M_b[i][hub] + fl(E_a[hub] + u_hub)) + min_k v[k] )
 //
-// bit for bit.  What is left per chunk: five terms per chain row, four per chain position for the two special rows,
-// a handful of special <-> special terms, one block-wide reduction of three values (chain minimum of v', the two
-// special rows' minima over the chain) -- about 9 N terms, 22 k for 2405.chmm.
+// bit for bit.  The same argument folds "special row <- chain state p <- hub" through min_p M_a[p][hub], which depends on
+// the symbol only and is tabulated by K0.  What is left per chunk: four or five terms per chain row, two per chain
+// position for the two special rows, a handful of special <-> special terms, one block-wide reduction of three values
+// (chain minimum of v', the two special rows' minima over the chain) -- about 7 N terms, 17 k for 2405.chmm.
 //
 // One CTA walks ALL chunks of a sequence (and then takes the next sequence from a longest-first queue): a thread
 // owns SV_CHAIN_RPT = 5 consecutive chain positions with v in registers; the emission table lives in shared memory
@@ -59,7 +60,7 @@ sv_chain_pair_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* 
     float* sE = reinterpret_cast<float*>(smem_raw);        // [emits][NPOS]
     float* sV = sE + static_cast<size_t>(m.emits) * NPOS;  // [2][VS]
     float* sP = sV + 2 * VS;                               // [2][3][32] per-warp partial minima
-    float* sEs = sP + 2 * 3 * 32;                          // [NSP][emits] emissions of the special states
+    float* sEs = sP + 2 * 3 * 32;                          // [NSP + 1][emits] emissions of the special states, min_p M_o[p][hub]
     __shared__ unsigned s_w;
     __shared__ float s_bv[NW];
     __shared__ int s_bi[NW];
@@ -74,7 +75,7 @@ sv_chain_pair_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* 
         float4* dst = reinterpret_cast<float4*>(sE);
         const int n4 = emits * NPOS / 4;
         for (int i = tid; i < n4; i += TPB) dst[i] = src[i];
-        for (int i = tid; i < NSP * emits; i += TPB) sEs[i] = m.emis_s[i];
+        for (int i = tid; i < (NSP + 1) * emits; i += TPB) sEs[i] = m.emis_s[i];
         for (int i = tid; i < 2 * 3 * 32; i += TPB) sP[i] = pinf();
         if (tid < 2) {
             sV[tid] = pinf();
@@ -98,6 +99,7 @@ sv_chain_pair_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* 
 #pragma unroll
         for (int b = 0; b < NSP; ++b) ss[a][b] = m.ss[a][b];
     }
+    const bool has_s1_to_hub = ss[0][1] < pinf();
     const unsigned long long* __restrict__ sym64 = static_cast<const unsigned long long*>(s.sym);
     __syncthreads();
 
@@ -211,19 +213,21 @@ sv_chain_pair_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* 
                 x = fminf(x, (Pb[r] + pH) + h[0]);
                 x = fminf(x, (Hb[r] + Ua[0]) + cm);
                 x = fminf(x, (Hb[r] + Sa[0][0]) + h[0]);
-                x = fminf(x, (Hb[r] + Sa[0][1]) + h[1]);
                 vn[r] = x;
-                // special rows through chain state p
+                // special rows through chain state p and its predecessor (through p and the hub: below, once per thread)
 #pragma unroll
-                for (int y = 0; y < NSP; ++y) {
-                    part[y] = fminf(part[y], (Ub[y] + Pa[r]) + v1);
-                    part[y] = fminf(part[y], (Ub[y] + Ha[r]) + h[0]);
-                }
+                for (int y = 0; y < NSP; ++y) part[y] = fminf(part[y], (Ub[y] + Pa[r]) + v1);
             }
-            // special rows through the special states
+            if (has_s1_to_hub) { // chain row <- hub <- special 1: absent in the reference's models (no C -> N edge)
+#pragma unroll
+                for (int r = 0; r < R; ++r) vn[r] = fminf(vn[r], (Hb[r] + Sa[0][1]) + h[1]);
+            }
+            // special rows through the special states, and through (chain state p, hub): x -> fl(U + x) and x -> fl(x + h)
+            // are monotone, so min_p fl(fl(U_b + M_a[p][hub]) + h_0) = fl(fl(U_b + min_p M_a[p][hub]) + h_0), bit for bit
+            const float min_ha = sEs[NSP * emits + a];
 #pragma unroll
             for (int x = 0; x < NSP; ++x) {
-                float acc = pinf();
+                float acc = (Ub[x] + min_ha) + h[0];
 #pragma unroll
                 for (int y = 0; y < NSP; ++y) {
                     acc = fminf(acc, (Sb[x][y] + Ua[y]) + cm);
@@ -337,7 +341,7 @@ const void* pair_variant(int threads, bool nonneg) {
 
 size_t sv_chain_pair_smem(int threads, int emits) {
     const size_t npos = static_cast<size_t>(threads) * R;
-    return (static_cast<size_t>(emits) * npos + 2 * (npos + 4) + 2 * 3 * 32 + static_cast<size_t>(NSP) * emits) * sizeof(float);
+    return (static_cast<size_t>(emits) * npos + 2 * (npos + 4) + 2 * 3 * 32 + static_cast<size_t>(NSP + 1) * emits) * sizeof(float);
 }
 
 int sv_chain_pair_prepare(int threads, bool nonneg, size_t smem, int* ctas_per_sm_out) {
