@@ -1041,6 +1041,26 @@ extern "C" int sv_viterbi_device(sv_model* m, const sv_seqs* seqs, float* d_out,
 }
 
 namespace {
+// The caller's result array, as a pointer the kernels can store to: page-locked host memory (cudaMallocHost /
+// cudaHostAlloc / cudaHostRegister) is device-accessible under unified addressing, so the step kernels write every
+// final vector straight into it when its sequence finishes -- 4 N bytes per sequence trickle over PCIe behind the
+// computation instead of one S x N x 4 byte device-to-host copy after it (39 MB = 0.7 ms of a 40 ms batch for BASELINE
+// config 5).  Pageable memory (or SV_DIRECT_HOST_OUT=0) keeps the device staging buffer and the copy.
+float* direct_host_out(float* out) {
+    static const bool on = [] {
+        const char* e = std::getenv("SV_DIRECT_HOST_OUT");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    if (!on || out == nullptr) return nullptr;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, out) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) return nullptr;
+    return static_cast<float*>(at.devicePointer);
+}
+
 template <typename SrcT>
 int viterbi_batch_impl(sv_model* m, const SrcT* symbols, const uint64_t* offsets, uint64_t nseq,
                        float* out, float* best, int32_t* best_state) {
@@ -1048,13 +1068,14 @@ int viterbi_batch_impl(sv_model* m, const SrcT* symbols, const uint64_t* offsets
     std::lock_guard<std::mutex> lock(*static_cast<std::mutex*>(m->ws_mutex)); // one workspace per model
     int rc = sv_ws_upload(m, symbols, offsets, nseq);
     if (rc != SV_OK) return rc;
+    float* const direct = direct_host_out(out);
     float *d_out, *d_best;
     int32_t* d_arg;
-    if ((rc = sv_ws_results(m, nseq, out != nullptr, &d_out, &d_best, &d_arg)) != SV_OK) return rc;
-    rc = sv_viterbi_device(m, m->ws.seqs, d_out, best ? d_best : nullptr,
+    if ((rc = sv_ws_results(m, nseq, out != nullptr && direct == nullptr, &d_out, &d_best, &d_arg)) != SV_OK) return rc;
+    rc = sv_viterbi_device(m, m->ws.seqs, direct != nullptr ? direct : d_out, best ? d_best : nullptr,
                            best_state ? d_arg : nullptr, m->stream);
     if (rc != SV_OK) return rc;
-    return sv_ws_download(m, nseq, d_out, d_best, d_arg, out, best, best_state);
+    return sv_ws_download(m, nseq, d_out, d_best, d_arg, direct != nullptr ? nullptr : out, best, best_state);
 }
 } // namespace
 

@@ -285,3 +285,27 @@ def test_argument_errors(api, load_model):
             m.viterbi_batch(syms, np.array([0, 20, 41], np.uint64))
     out, _, _ = m.viterbi_batch(np.zeros(41, np.uint8), np.array([0, 20, 41], np.uint64))  # still usable
     assert out.shape[0] == 2
+
+
+@pytest.mark.parametrize("kernel", ["generic", "es", "ls", "chain"])
+def test_results_written_straight_to_pinned_host_memory(kernel, api, oracle, load_model):
+    """A page-locked result array is device-accessible: sv_viterbi_batch* hands it to the step kernel, which stores every
+    final vector when its sequence finishes (no staging buffer, no device-to-host copy afterwards).  Same bits as the
+    staged path (pageable array) and as the oracle; one full wave + a tail (two launches for equal lengths)."""
+    import torch
+    from spec_viterbi_b200 import generators
+    hmm = load_model("300") if kernel == "chain" else generators.random_hmm(states_num=300, seed=31)
+    rng = np.random.default_rng(9)
+    for lens in (rng.integers(1, 70, 333), np.full(8 * 148 + 300, 23)):
+        offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        syms = rng.integers(0, 20, int(offs[-1])).astype(np.uint8)
+        m = _model(api, hmm, kernel, must_fit=True)
+        nseq, n = len(lens), hmm.states_num
+        pinned = torch.full((nseq, n), float("nan"), dtype=torch.float32).pin_memory()
+        out_p, best_p, arg_p = m.viterbi_batch(syms, offs, out=pinned.numpy())
+        assert _ran(m, kernel)
+        out_s, best_s, arg_s = m.viterbi_batch(syms, offs)           # pageable: staged through the device buffer
+        exp = oracle.plain_batch(hmm, syms.astype(np.uint64), offs, threads=8)
+        assert same_bits(out_p, exp) and same_bits(out_s, exp)
+        assert np.array_equal(best_p, best_s) and np.array_equal(arg_p, arg_s)
+        assert out_p.ctypes.data == pinned.numpy().ctypes.data      # the caller's array, filled in place
