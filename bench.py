@@ -514,8 +514,9 @@ def run_b200(args):
                     "relax_per_clk_per_sm": relax / kernel_s / (sm_count * mhz * 1e6),
                     "peak_source": f"non-tensor FP32 issue: {sm_count} SMs x 128 lanes x {mhz:.0f} MHz (NVML median during the "
                                    "run) x 2 ops / 1.5 issue slots per (min,+) MAC (1 FADD + 1/2 FMNMX3); algorithmic ops = 2 per "
-                                   "relaxation.  The oracle's association needs 2 FADD per relaxation (2.5 slots), so 0.6 is the "
-                                   f"highest fraction any bit-exact kernel can reach.  MEASURED_PEAKS.json ({peak_kind}) holds "
+                                   "relaxation.  The oracle's association needs 2 FADD per relaxation (2.5 slots) wherever the inner add "
+                                   "fl(E + T') depends on the edge (lockstep kernel: 0.6 is then the highest reachable fraction); the "
+                                   f"chain kernel tabulates it.  MEASURED_PEAKS.json ({peak_kind}) holds "
                                    "HBM/bf16 peaks only; neither bounds this kernel (bound is not 'hbm'/'tensor': the working set "
                                    "lives on chip and (min,+) is not an MMA contraction)",
                     "smem": {"achieved_GBs": xbar_bytes / kernel_s / 1e9, "peak_GBs": xbar_peak / 1e9,

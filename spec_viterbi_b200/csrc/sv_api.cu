@@ -408,7 +408,7 @@ bool sv_model_ensure_chain(sv_model* m) {
     for (const int q : {8, 4, 2, 1}) {
         size_t smem = 0;
         int per_sm = 0;
-        if (sv_chain_prepare(m->chain.threads, q, m->chain.nonneg, &smem, &per_sm) != 0) {
+        if (sv_chain_prepare(m->chain.threads, q, m->chain.nonneg, static_cast<int>(m->emits), &smem, &per_sm) != 0) {
             cudaGetLastError();
             m->chain.valid = false;
             return false;
@@ -1068,7 +1068,9 @@ int viterbi_batch_impl(sv_model* m, const SrcT* symbols, const uint64_t* offsets
     std::lock_guard<std::mutex> lock(*static_cast<std::mutex*>(m->ws_mutex)); // one workspace per model
     int rc = sv_ws_upload(m, symbols, offsets, nseq);
     if (rc != SV_OK) return rc;
-    float* const direct = direct_host_out(out);
+    // not for the chain kernel: a thread owns five CONSECUTIVE positions there, so a warp's store covers 640 bytes with
+    // 20-byte strides -- fine for L2, but over PCIe it becomes many small writes (measured: e2e 3.0e12 -> 2.35e12)
+    float* const direct = chosen_kernel(m, nseq) == SV_KERNEL_CHAIN ? nullptr : direct_host_out(out);
     float *d_out, *d_best;
     int32_t* d_arg;
     if ((rc = sv_ws_results(m, nseq, out != nullptr && direct == nullptr, &d_out, &d_best, &d_arg)) != SV_OK) return rc;

@@ -125,8 +125,8 @@ void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, c
             break;
         }
     if (threads == 0) return;
-    // + 3: the kernel fetches a symbol's five columns with one 8-column load
-    const size_t tcols_need = static_cast<size_t>(threads / 128) * emits * SV_CHAIN_RPT + 3;
+    // + 2: the one- and two-sequence kernels fetch a symbol's six columns with one 8-column load
+    const size_t tcols_need = static_cast<size_t>(threads / 128) * emits * SV_CHAIN_TMEM_CS + 2;
     if (tcols_need > 512) return;
     int tcols = 32;
     while (static_cast<size_t>(tcols) < tcols_need) tcols *= 2;

@@ -211,6 +211,7 @@ int sv_ls_launch(int index, int nq4, const SvLsDev& m, const SvSeqsDev& s, float
 // No per-relaxation shared-memory gather is left, so the kernel is FP32-issue bound.
 constexpr int SV_CHAIN_RPT = 5;  // chain positions per thread (= TMEM columns per symbol)
 constexpr int SV_CHAIN_NSP = 2;  // special states supported
+constexpr int SV_CHAIN_TMEM_CS = SV_CHAIN_RPT + 1; // TMEM columns per symbol: fl(E + w_pred) of 5 positions, fl(E + w_hub) of one
 
 struct SvChainPlan {
     bool valid = false;
@@ -246,7 +247,7 @@ struct SvChainDev {
 void sv_chain_build_plan(const SvHostCsr& csr, const std::vector<float>& emis, const std::vector<float>& start,
                          uint64_t emits, SvChainPlan* plan);
 // sequences per CTA that are compiled: 8, 4, 2, 1
-int sv_chain_prepare(int threads, int q, bool nonneg, size_t* smem_out, int* ctas_per_sm_out);
+int sv_chain_prepare(int threads, int q, bool nonneg, int emits, size_t* smem_out, int* ctas_per_sm_out);
 int sv_chain_launch(int threads, int q, const SvChainDev& m, const SvSeqsDev& s, float* d_out, float* d_best,
                     int32_t* d_arg, unsigned* d_counter, int grid, size_t smem, cudaStream_t st);
 

@@ -15,14 +15,17 @@
 //     new scores into a running minimum, one integer REDUX per sequence reduces it over the warp
 //     (scores >= 0: float order = signed-int order; else through an order-preserving key), warp w < Q finishes sequence w's two
 //     special rows in the NEXT step from the per-warp partials -- one barrier per step;
-//   * the emission table lives in TENSOR MEMORY (lane = thread's lane in its warp quadrant, column =
-//     (warp group, symbol, rank)); E[o][own positions] is one tcgen05.ld.x4 + .x1 with a run-time
-//     column, issued one sequence ahead of its use;
+//   * the inner add of fl(fl(E + T') + v) does not depend on the sequence, so A = fl(E[o][p] + w_pred[p]) and
+//     B = fl(E[o][p] + w_hub[p]) are TABULATED once per CTA (same IEEE add, same bits): A and the first B of a thread
+//     live in TENSOR MEMORY (lane = thread's lane in its warp quadrant, column = (warp group, symbol, 6 entries)),
+//     fetched as one tcgen05.ld.x4 + .x2 with a run-time column one sequence ahead of its use; the other four B live
+//     in shared memory as one float4 per (symbol, thread), fetched two sequences ahead (the two tables are 385 KB for
+//     2405.chmm; tensor memory holds 256 KB);
 //   * sequence managers (lane q of the last warp) stream the symbols and publish a control block two
 //     steps ahead, exactly as in the lockstep kernel (sv_plain_ls.cu); finished sequences are
 //     written out with their (best, argmin) and replaced from a global longest-first queue.
 //
-// Per (position, sequence) and step: 4 IEEE adds (16 of 20 per sequence as packed FADD2) + 1 FMNMX + 0.4
+// Per (position, sequence) and step: 2 IEEE adds (8 of 10 per sequence as packed FADD2) + 1 FMNMX + 0.4
 // FMNMX3 for FOUR transitions -- no per-relaxation shared-memory traffic is left, so the kernel is bound by
 // FP32 issue.
 // Tensor cores are not used ((min,+) is not an MMA contraction); only their memory is.
@@ -32,7 +35,10 @@
 
 namespace {
 
-constexpr int kChainHeStride = 256 * SV_CHAIN_RPT; // special-row emissions indexed by symbol * RPT
+constexpr int kChainHeStride = 256; // special-row emissions indexed by symbol
+// Tensor-memory columns per symbol (see "tabulated level-1 entries" below): A of positions 1,2,3,4,0 and B of position 0
+constexpr int kChainCS = SV_CHAIN_TMEM_CS;
+static_assert(kChainCS == SV_CHAIN_RPT + 1, "layout");
 
 // N consecutive floats of shared memory as ONE load / store (N = 1, 2, 4; p aligned to 4 N bytes)
 template <int N> __device__ __forceinline__ void lds_vec(const float* p, float (&x)[N]) {
@@ -91,6 +97,15 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
                  : "memory");
 }
 
+// A of the thread's five positions and B of its first one for one sequence: 6 consecutive TMEM columns
+__device__ __forceinline__ void tmem_ld6(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr)
+                 : "memory");
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r[4]), "=r"(r[5]) : "r"(taddr + 4u) : "memory");
+}
+
 template <int TPG, int Q, bool NN, bool PK>
 __global__ void __launch_bounds__(TPG, 512 / TPG)
 sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __restrict__ best,
@@ -98,7 +113,8 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     constexpr int NW = TPG / 32;
     constexpr int MW = NW - 1; // manager warp (its chain positions are mostly padding)
     constexpr int R = SV_CHAIN_RPT;
-    constexpr int RS = SV_CHAIN_RPT;
+    constexpr int CS = kChainCS;
+    static_assert(PK, "the tabulated layout is the packed one");
     constexpr int QS = 8; // stride of the per-sequence shared arrays
     // one tcgen05.ld.x8 per sequence (5 % off the single-sequence step) where registers allow, else .x4 + .x1
     constexpr bool X8 = Q <= 2;
@@ -115,6 +131,9 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     __shared__ __align__(16) float s_top[2][NG][(TPG + 1) * QV];
     __shared__ __align__(16) float s_vs[2][SV_CHAIN_NSP][QS]; // [parity][special][q]
     __shared__ float s_he[SV_CHAIN_NSP * kChainHeStride];
+    // B = fl(E + w_hub) of positions 1..4 of every thread, per symbol: [symbol][thread] float4 (dynamic shared memory)
+    extern __shared__ __align__(16) unsigned char chain_dyn_smem[];
+    float4* const sB = reinterpret_cast<float4*>(chain_dyn_smem);
     __shared__ float s_bv[NW];
     __shared__ int s_bi[NW];
 
@@ -130,30 +149,38 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tbase = s_taddr;
     const uint32_t tE = tbase + (static_cast<uint32_t>(warp & 3) << 21) +
-                        static_cast<uint32_t>(warp >> 2) * static_cast<uint32_t>(m.emits * RS);
-    // column order of a symbol's five scores: positions 0..4, or (packed adds) 1,2,3,4,0 so that the x4 load
-    // delivers the pairs (1,2) and (3,4) in aligned register pairs
-    for (int o = 0; o < m.emits; ++o)
-        for (int r = 0; r < R; ++r)
-            tmem_st1(tE + static_cast<uint32_t>(o * RS + (PK ? (r == 0 ? R - 1 : r - 1) : r)),
-                     m.emis_p[static_cast<size_t>(o) * n_pos + tid * R + r]);
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-    for (int i = tid; i < SV_CHAIN_NSP * m.emits; i += TPG) {
-        const int h = i / m.emits, o = i % m.emits;
-        s_he[h * kChainHeStride + o * RS] = m.emis_s[i];
-    }
-    for (int i = tid; i < 2 * NW * QS; i += TPG) (&s_red[0][0][0])[i] = pos_inf();
-    for (int i = tid; i < 2 * NG * (TPG + 1) * QV; i += TPG) (&s_top[0][0][0])[i] = pos_inf();
-    if (tid < 2 * SV_CHAIN_NSP * QS) (&s_vs[0][0][0])[tid] = pos_inf();
-
+                        static_cast<uint32_t>(warp >> 2) * static_cast<uint32_t>(m.emits * CS);
+    // Tabulated level-1 entries: the step needs E only inside A = fl(E[o][p] + w_pred[p]) and B = fl(E[o][p] + w_hub[p])
+    // (GraphBLAS_impl.cpp:65,69: the inner add of fl(fl(E + T') + v)), which do not depend on the sequence -- so they are
+    // formed ONCE here, with the same IEEE add the step used to issue per sequence and step, and the step is left with
+    // one add per transition.  Both tables are 4 N emits bytes (192 KB each for 2405.chmm): A lives in tensor memory
+    // (column order of a symbol: positions 1,2,3,4,0, so that the x4 load delivers the pairs (1,2) and (3,4) in aligned
+    // register pairs) together with B of position 0; B of positions 1..4 lives in shared memory as one float4 per
+    // (symbol, thread) -- tensor memory holds 256 KB, the two tables need 385 KB.
     float wp[R], wh[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         wp[r] = m.w_pred[tid * R + r];
         wh[r] = m.w_hub[tid * R + r];
     }
-    [[maybe_unused]] const f32x2 wp12 = pack2(wp[1], wp[2]), wp34 = pack2(wp[3], wp[4]);
-    [[maybe_unused]] const f32x2 wh12 = pack2(wh[1], wh[2]), wh34 = pack2(wh[3], wh[4]);
+    for (int o = 0; o < m.emits; ++o) {
+        float e[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) e[r] = m.emis_p[static_cast<size_t>(o) * n_pos + tid * R + r];
+#pragma unroll
+        for (int r = 0; r < R; ++r) tmem_st1(tE + static_cast<uint32_t>(o * CS + (r == 0 ? R - 1 : r - 1)), e[r] + wp[r]);
+        tmem_st1(tE + static_cast<uint32_t>(o * CS + R), e[0] + wh[0]);
+        sB[o * TPG + tid] = make_float4(e[1] + wh[1], e[2] + wh[2], e[3] + wh[3], e[4] + wh[4]);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    for (int i = tid; i < SV_CHAIN_NSP * m.emits; i += TPG) {
+        const int h = i / m.emits, o = i % m.emits;
+        s_he[h * kChainHeStride + o] = m.emis_s[i];
+    }
+    for (int i = tid; i < 2 * NW * QS; i += TPG) (&s_red[0][0][0])[i] = pos_inf();
+    for (int i = tid; i < 2 * NG * (TPG + 1) * QV; i += TPG) (&s_top[0][0][0])[i] = pos_inf();
+    if (tid < 2 * SV_CHAIN_NSP * QS) (&s_vs[0][0][0])[tid] = pos_inf();
+
     // special rows: lane s of a warp finishes special s
     // (no run-time indexing into the kernel parameters: that would move the whole struct to local memory)
     static_assert(SV_CHAIN_NSP == 2, "two specials");
@@ -200,11 +227,11 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
                 mg_cur = *mg_ptr++;
                 mg_nxt = *mg_ptr++;
                 mg_pos = static_cast<uint32_t>(b & 7u);
-                col0 = next_symbol() * RS;
+                col0 = next_symbol();
                 started = true;
                 one = mg_len == 1;
                 if (mg_len > 1) {
-                    col1 = next_symbol() * RS;
+                    col1 = next_symbol();
                     second = true;
                     two = mg_len == 2;
                     mg_t = 1;
@@ -235,14 +262,24 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
     __syncthreads();
 
     // flags and TMEM columns of the coming step, fetched before the barrier that ends the current one
-    uint4 fl, cA, cB;
-    uint32_t eA[8], eB[8]; // E[o_q][own positions] (+3 ignored columns), double buffered over q
+    uint4 fl, cA, cB;  // cA, cB: the symbols of sequences 0-3, 4-7
+    uint32_t eA[8], eB[8]; // A[o_q][positions 1,2,3,4,0], B[o_q][position 0] (+2 ignored columns), double buffered over q
+    // B[o_q][positions 1..4]: a ring of three over q, fetched TWO sequences ahead (a shared-memory load under this
+    // kernel's load takes longer than one sequence's arithmetic: one ahead left 0.9 short-scoreboard stalls per issue)
+    float4 bR[3];
+    const uint32_t sB_own = static_cast<uint32_t>(__cvta_generic_to_shared(sB)) + static_cast<uint32_t>(tid) * 16u;
+    auto fetch_a = [&](uint32_t sym, uint32_t (&e)[8]) {
+        if constexpr (X8) tmem_ld8(tE + sym * CS, e);
+        else tmem_ld6(tE + sym * CS, e);
+    };
+    auto fetch_b = [&](uint32_t sym, float4& b) { b = lds128<0>(sB_own + sym * static_cast<uint32_t>(TPG * 16)); };
     auto prefetch_step = [&](const LsCtl& nc) {
         fl = *reinterpret_cast<const uint4*>(&nc.init_mask);
         cA = *reinterpret_cast<const uint4*>(&nc.col[0]);
         cB = *reinterpret_cast<const uint4*>(&nc.col[4]);
-        if constexpr (X8) tmem_ld8(tE + cA.x, eA);
-        else tmem_ld5(tE + cA.x, reinterpret_cast<uint32_t(&)[5]>(eA));
+        fetch_a(cA.x, eA);
+        fetch_b(cA.x, bR[0]);
+        if constexpr (Q > 1) fetch_b(cA.y, bR[1]);
     };
     prefetch_step(ctl[0]);
 
@@ -260,7 +297,7 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             uint32_t colv = 0;
             if (lane < Q && mg_t + 1u < mg_len) {
                 cont = true;
-                colv = next_symbol() * RS;
+                colv = next_symbol();
                 last = mg_t + 2u == mg_len;
                 ++mg_t;
             }
@@ -298,23 +335,23 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             constexpr int q = decltype(qc)::value;
             uint32_t(&ec)[8] = (q & 1) ? eB : eA;
             uint32_t(&en)[8] = (q & 1) ? eA : eB;
+            const float4 bc = bR[q % 3];
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]));
-            if constexpr (q + 1 < Q) {
-                if constexpr (X8) tmem_ld8(tE + cols[q + 1 < Q ? q + 1 : 0], en);
-                else tmem_ld5(tE + cols[q + 1 < Q ? q + 1 : 0], reinterpret_cast<uint32_t(&)[5]>(en));
-            }
-            if constexpr (PK) {
-                // ec = E of positions 1,2,3,4,0.  Band predecessors of (1,2) are (0,1), of (3,4) are (2,3).
-                const f32x2 e12 = pack2(__uint_as_float(ec[0]), __uint_as_float(ec[1]));
-                const f32x2 e34 = pack2(__uint_as_float(ec[2]), __uint_as_float(ec[3]));
-                const float e0 = __uint_as_float(ec[4]);
+            asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]), "+r"(ec[5]));
+            if constexpr (q + 1 < Q) fetch_a(cols[q + 1 < Q ? q + 1 : 0], en);
+            if constexpr (q + 2 < Q) fetch_b(cols[q + 2 < Q ? q + 2 : 0], bR[(q + 2) % 3]);
+            {
+                // ec = A = fl(E + w_pred) of positions 1,2,3,4,0 and B = fl(E + w_hub) of position 0; bc = B of positions
+                // 1..4.  v'[p] = min(fl(A[p] + v[p-1]), fl(B[p] + v[hub])): the oracle's fl(fl(E + T') + v), inner add tabulated.
+                // Band predecessors of (1,2) are (0,1), of (3,4) are (2,3).
+                const f32x2 A12 = pack2(__uint_as_float(ec[0]), __uint_as_float(ec[1]));
+                const f32x2 A34 = pack2(__uint_as_float(ec[2]), __uint_as_float(ec[3]));
                 const f32x2 hh = pack2(hub, hub);
-                const f32x2 a12 = add2(add2(e12, wp12), pack2(v[q][0], v[q][1]));
-                const f32x2 a34 = add2(add2(e34, wp34), pack2(v[q][2], v[q][3]));
-                const f32x2 b12 = add2(add2(e12, wh12), hh);
-                const f32x2 b34 = add2(add2(e34, wh34), hh);
-                const float a0 = relax1(e0, wp[0], pv), b0 = relax1(e0, wh[0], hub);
+                const f32x2 a12 = add2(A12, pack2(v[q][0], v[q][1]));
+                const f32x2 a34 = add2(A34, pack2(v[q][2], v[q][3]));
+                const f32x2 b12 = add2(pack2(bc.x, bc.y), hh);
+                const f32x2 b34 = add2(pack2(bc.z, bc.w), hh);
+                const float a0 = __uint_as_float(ec[4]) + pv, b0 = __uint_as_float(ec[5]) + hub;
                 float a1, a2, a3, a4, b1, b2, b3, b4;
                 unpack2(a12, a1, a2);
                 unpack2(a34, a3, a4);
@@ -325,15 +362,6 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
                 v[q][2] = fminf(a2, b2);
                 v[q][3] = fminf(a3, b3);
                 v[q][4] = fminf(a4, b4);
-            } else {
-                float e[R];
-#pragma unroll
-                for (int r = 0; r < R; ++r) e[r] = __uint_as_float(ec[r]);
-#pragma unroll
-                for (int r = R - 1; r >= 0; --r) {
-                    const float prev = r > 0 ? v[q][r - 1] : pv;
-                    v[q][r] = fminf(relax1(e[r], wp[r], prev), relax1(e[r], wh[r], hub));
-                }
             }
             float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
             mq = fminf(mq, fminf(v[q][3], v[q][4]));
@@ -374,7 +402,7 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             auto init_fix = [&](auto qc) {
                 constexpr int q = decltype(qc)::value;
                 if (!((init_mask >> q) & 1u)) return;
-                const float* __restrict__ em = m.emis_p + static_cast<size_t>(cols[q] / RS) * n_pos + tid * R;
+                const float* __restrict__ em = m.emis_p + static_cast<size_t>(cols[q]) * n_pos + tid * R;
 #pragma unroll
                 for (int r = 0; r < R; ++r) v[q][r] = em[r] + start_p[r];
                 float mq = fminf(v[q][0], fminf(v[q][1], v[q][2]));
@@ -518,7 +546,7 @@ const void* chain_fn(int threads, int q, bool nn) {
 // Tensor memory is allocated once per CTA for its lifetime: at most 512 / tmem_cols CTAs may share an
 // SM, otherwise a CTA would spin in tcgen05.alloc until a neighbour exits.  The dynamic shared-memory
 // request is padded so that the hardware never co-schedules more than that.
-int sv_chain_prepare(int threads, int q, bool nonneg, size_t* smem_out, int* ctas_per_sm_out) {
+int sv_chain_prepare(int threads, int q, bool nonneg, int emits, size_t* smem_out, int* ctas_per_sm_out) {
     const void* fn = chain_fn(threads, q, nonneg);
     if (fn == nullptr) return cudaErrorInvalidValue;
     const int want = threads == 512 ? 1 : threads == 256 ? 2 : 4;
@@ -529,8 +557,10 @@ int sv_chain_prepare(int threads, int q, bool nonneg, size_t* smem_out, int* cta
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
     cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    // grow the dynamic request until the occupancy calculator agrees
-    size_t dyn = 0;
+    // dynamic shared memory = the fl(E + w_hub) table of positions 1..4 (one float4 per symbol and thread); then grow the
+    // request until the occupancy calculator agrees
+    size_t dyn = static_cast<size_t>(emits) * threads * 16;
+    if (fa.sharedSizeBytes + dyn > static_cast<size_t>(smem_optin)) return cudaErrorLaunchOutOfResources;
     int occ = 0;
     for (;;) {
         e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dyn));

@@ -291,7 +291,8 @@ def test_argument_errors(api, load_model):
 def test_results_written_straight_to_pinned_host_memory(kernel, api, oracle, load_model):
     """A page-locked result array is device-accessible: sv_viterbi_batch* hands it to the step kernel, which stores every
     final vector when its sequence finishes (no staging buffer, no device-to-host copy afterwards).  Same bits as the
-    staged path (pageable array) and as the oracle; one full wave + a tail (two launches for equal lengths)."""
+    staged path (pageable array) and as the oracle; one full wave + a tail (two launches for equal lengths).  (The chain
+    kernel keeps the staging buffer -- its stores are strided -- and must give the same result through it.)"""
     import torch
     from spec_viterbi_b200 import generators
     hmm = load_model("300") if kernel == "chain" else generators.random_hmm(states_num=300, seed=31)
