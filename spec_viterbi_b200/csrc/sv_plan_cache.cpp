@@ -24,7 +24,7 @@ namespace {
 
 constexpr char kMagic[8] = {'S', 'V', 'L', 'S', 'P', 'L', 'N', '3'};
 // bump when SvLsPlan's meaning changes (planner, variant table, kernel register layout)
-constexpr uint64_t kPlanVersion = 0x20261105ull;
+constexpr uint64_t kPlanVersion = 0x20261106ull; // end-game colouring search: plans cached by the older search are rebuilt
 
 inline uint64_t mix(uint64_t h, uint64_t x) {
     h ^= x;
