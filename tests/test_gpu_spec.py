@@ -565,3 +565,27 @@ def test_deferred_level2_table(api, oracle, load_model):
     osp = oracle.spec(hmm, 2)
     for t in (0, 57, 399):
         assert same_bits(lazy.handler(t), osp.handler(t)) and same_bits(eager.handler(t), osp.handler(t))
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_chain_models_plain_and_level2(seed, api, oracle):
+    """The randomized chain + specials models of tests/conftest.py::random_chain_hmm on the GPU: the chain kernel
+    (tabulated inner adds) against the plain oracle and K4c against the level-2 oracle, ragged lengths."""
+    from conftest import random_chain_hmm
+    from spec_viterbi_b200 import _lib
+    hmm, E, rng = random_chain_hmm(api, seed)
+    seqs = [rng.integers(0, E, T).astype(np.uint64) for T in (1, 2, 3, 4, 5, 8, 33, 2, 17, 64)]
+    syms, offs = api.pack_sequences(seqs)
+    m = api.Model(hmm)
+    m.set_kernel(_lib.KERNEL_CHAIN)
+    out, best, arg = m.viterbi_batch(syms, offs)
+    assert m.info().kernel == _lib.KERNEL_CHAIN
+    assert same_bits(out, oracle.plain_batch(hmm, syms, offs))
+    sp = api.Spec(m, 2)
+    sp.set_run_mode(_lib.SPEC_RUN_CHAIN)
+    out2, best2, arg2 = sp.run_batch(syms, offs)
+    osp = oracle.spec(hmm, 2)
+    for k, seq in enumerate(seqs):
+        exp = osp.run(seq)
+        assert same_bits(out2[k], exp), (seed, k)
+        assert best2[k] == exp.min() and arg2[k] == exp.argmin()

@@ -231,32 +231,8 @@ def test_chain_pair_replay_random_chain_models(seed, api, oracle):
     weights, optional C -> N and N -> C edges, one or two specials, a negative weight, several start states -- through
     the K4c algebra (host replay) against the level-2 oracle, and through the plain chain algebra against the plain
     oracle."""
-    rng = np.random.default_rng(100 + seed)
-    L = int(rng.integers(7, 60))
-    two = seed % 3 != 0                       # seeds 0, 3: a single special state
-    n = L + (2 if two else 1)
-    E = int(rng.integers(2, 6))
-    N, C = 0, L + 1
-    src, dst, w = [N], [N], [float(rng.uniform(0.1, 2))]
-    if two:
-        src += [C]; dst += [C]; w += [float(rng.uniform(0.1, 2))]
-        if seed % 2:
-            src += [C, N]; dst += [N, C]; w += [float(rng.uniform(1, 5)), float(rng.uniform(1, 5))]
-    uN, uC = float(rng.uniform(0.5, 2)), float(rng.uniform(0.5, 2))
-    for k in range(1, L + 1):
-        src += [N, k]; dst += [k, N]
-        w += [float(rng.uniform(1, 9)) if rng.random() > 0.15 else np.inf, uN]
-        if two:
-            src += [k]; dst += [C]; w += [uC]
-        if k < L and rng.random() > 0.2:
-            src += [k]; dst += [k + 1]
-            w += [float(rng.uniform(0.1, 3)) if rng.random() > 0.1 else np.inf]
-    if seed == 4:
-        w[2] = -0.25                           # a "probability" > 1 on the first hub -> chain edge (index 2: N -> 1)
-    perm = rng.permutation(n)
-    hmm = api.HMM(n, E, len(src), perm[np.array(src)].astype(np.uint64), perm[np.array(dst)].astype(np.uint64),
-                  np.array(w, np.float32), rng.uniform(0.2, 7, (E, n)).astype(np.float32), 2,
-                  np.array([perm[N], perm[min(3, L)]], np.uint64), np.array([0.0, 1.5], np.float32))
+    from conftest import random_chain_hmm
+    hmm, E, rng = random_chain_hmm(api, seed)
     osp = oracle.spec(hmm, 2)
     for T in (1, 2, 3, 4, 5, 8, 33):
         seq = rng.integers(0, E, T).astype(np.uint64)
