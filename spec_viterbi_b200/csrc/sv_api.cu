@@ -756,7 +756,7 @@ int seqs_assign(sv_seqs* s, const sv_model* m, const SrcT* symbols, const uint64
             *worst_out = w;
         };
         auto pack_all = [&](auto* dst) {
-            const int nthr = total >= (1ull << 21) ? std::min(8, host_threads()) : 1;
+            const int nthr = total >= (1ull << 21) ? host_threads() : 1; // up to 16: the narrowing copy is bound by host memory bandwidth
             std::vector<unsigned long long> w(nthr, 0);
             std::vector<std::thread> pool;
             for (int t = 1; t < nthr; ++t)
