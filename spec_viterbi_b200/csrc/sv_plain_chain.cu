@@ -263,7 +263,11 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
 
     // flags and TMEM columns of the coming step, fetched before the barrier that ends the current one
     uint4 fl, cA, cB;  // cA, cB: the symbols of sequences 0-3, 4-7
-    uint32_t eA[8], eB[8]; // A[o_q][positions 1,2,3,4,0], B[o_q][position 0] (+2 ignored columns), double buffered over q
+    // A[o_q][positions 1,2,3,4,0], B[o_q][position 0] (+2 ignored columns with the x8 load).  Fetched in PAIRS of sequences:
+    // tcgen05.wait::ld retires every fetch in flight, so the way to give a fetch more than one sequence's arithmetic of
+    // cover is to wait once per two sequences -- the pair (q, q+1) in use, the pair (q+2, q+3) in flight.
+    constexpr int NE = Q >= 4 ? 4 : 2;
+    uint32_t eR[NE][8];
     // B[o_q][positions 1..4]: a ring of three over q, fetched TWO sequences ahead (a shared-memory load under this
     // kernel's load takes longer than one sequence's arithmetic: one ahead left 0.9 short-scoreboard stalls per issue)
     float4 bR[3];
@@ -277,7 +281,8 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
         fl = *reinterpret_cast<const uint4*>(&nc.init_mask);
         cA = *reinterpret_cast<const uint4*>(&nc.col[0]);
         cB = *reinterpret_cast<const uint4*>(&nc.col[4]);
-        fetch_a(cA.x, eA);
+        fetch_a(cA.x, eR[0]);
+        if constexpr (Q > 1) fetch_a(cA.y, eR[1]);
         fetch_b(cA.x, bR[0]);
         if constexpr (Q > 1) fetch_b(cA.y, bR[1]);
     };
@@ -333,12 +338,18 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
         //      predecessor of this thread's first position ----
         auto seq_step = [&](auto qc, float hub, float pv, float& red) {
             constexpr int q = decltype(qc)::value;
-            uint32_t(&ec)[8] = (q & 1) ? eB : eA;
-            uint32_t(&en)[8] = (q & 1) ? eA : eB;
+            uint32_t(&ec)[8] = eR[q % NE];
             const float4 bc = bR[q % 3];
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]), "+r"(ec[5]));
-            if constexpr (q + 1 < Q) fetch_a(cols[q + 1 < Q ? q + 1 : 0], en);
+            if constexpr ((q & 1) == 0) {
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                asm volatile("" : "+r"(ec[0]), "+r"(ec[1]), "+r"(ec[2]), "+r"(ec[3]), "+r"(ec[4]), "+r"(ec[5]));
+                if constexpr (q + 1 < Q) {
+                    uint32_t(&e1)[8] = eR[(q + 1) % NE];
+                    asm volatile("" : "+r"(e1[0]), "+r"(e1[1]), "+r"(e1[2]), "+r"(e1[3]), "+r"(e1[4]), "+r"(e1[5]));
+                }
+                if constexpr (q + 2 < Q) fetch_a(cols[q + 2 < Q ? q + 2 : 0], eR[(q + 2) % NE]);
+                if constexpr (q + 3 < Q) fetch_a(cols[q + 3 < Q ? q + 3 : 0], eR[(q + 3) % NE]);
+            }
             if constexpr (q + 2 < Q) fetch_b(cols[q + 2 < Q ? q + 2 : 0], bR[(q + 2) % 3]);
             {
                 // ec = A = fl(E + w_pred) of positions 1,2,3,4,0 and B = fl(E + w_hub) of position 0; bc = B of positions
@@ -390,10 +401,11 @@ sv_chain_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* __res
             if ((fl.z & 0xf0u) != 0) {
                 group_step(std::integral_constant<int, (NG > 1 ? 1 : 0)>{});
             } else {
-                // sequence 3 issued the fetch for sequence 4 into eA: wait with eA still allocated (an asynchronous
-                // tcgen05.ld must never land in registers the compiler has handed to something else)
+                // sequence 2 issued the fetches for sequences 4 and 5: wait with their registers still allocated (an
+                // asynchronous tcgen05.ld must never land in registers the compiler has handed to something else)
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                asm volatile("" ::"r"(eA[0]), "r"(eA[1]), "r"(eA[2]), "r"(eA[3]), "r"(eA[4]), "r"(eA[5]), "r"(eA[6]), "r"(eA[7]));
+                asm volatile("" ::"r"(eR[0][0]), "r"(eR[0][1]), "r"(eR[0][2]), "r"(eR[0][3]), "r"(eR[0][4]), "r"(eR[0][5]), "r"(eR[0][6]), "r"(eR[0][7]));
+                asm volatile("" ::"r"(eR[1][0]), "r"(eR[1][1]), "r"(eR[1][2]), "r"(eR[1][3]), "r"(eR[1][4]), "r"(eR[1][5]), "r"(eR[1][6]), "r"(eR[1][7]));
             }
         }
         // ---- rare: first step of a sequence, v_0 = E[o_0] + start replaces the relaxed scores (a real
