@@ -125,7 +125,7 @@ sv_chain_pair_kernel(SvChainDev m, SvSeqsDev s, float* __restrict__ out, float* 
         };
 
         float v[R];          // scores of the own positions
-        float hp[NSP];       // special rows: the terms every thread can form itself (pending the block minimum)
+        float hp[NSP] = {pinf(), pinf()}; // special rows: the terms every thread can form itself (pending the block minimum)
         float h[NSP], cm;    // scores of the special states, chain minimum (valid after phase_begin)
         uint32_t par = 0;    // buffer the LAST phase wrote
 
